@@ -1,0 +1,192 @@
+/*
+ * include/bandcu.h -- C-ABI of the CUDA shim (libbandcu.so).
+ *
+ * This is the thin boundary the C++ host layer (band_b200/csrc/band/...) calls
+ * instead of libyuv: plain pointers, sizes and POD structs; no C++ types, no
+ * exceptions, no torch types. It replaces, for the GPU backing, what
+ * /root/reference/band/buffer/libyuv_image_operator.h:28-60
+ * (LibyuvImageOperator::{Crop,Resize,Rotate,FlipHorizontally,FlipVertically,
+ * ColorSpaceConvert}) and band/buffer/common_operator.cc:24-40
+ * (NormalizeFromTo) provide on the CPU -- but as ONE fused launch per frame
+ * batch instead of one materialised pass per operator.
+ *
+ * Every function returns 0 on success or a non-zero cudaError_t / BANDCU_E_*
+ * code; bandcu_last_error_string() describes the last failure on the calling
+ * thread. There is no CPU fallback: without a CUDA device every compute entry
+ * point fails.
+ */
+#ifndef BAND_INCLUDE_BANDCU_H_
+#define BAND_INCLUDE_BANDCU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BANDCU_API __attribute__((visibility("default")))
+
+enum {
+  BANDCU_OK = 0,
+  BANDCU_E_INVALID = 10001,     /* malformed descriptor / null pointer */
+  BANDCU_E_UNSUPPORTED = 10002, /* combination the kernels do not implement */
+};
+
+/* Source pixel layouts. YUV420 covers NV12/NV21/YV12/YV21 uniformly: separate
+ * U and V base pointers plus a chroma pixel stride (2 = interleaved, 1 =
+ * planar), exactly how GetYuvDataFromBuffer (libyuv_image_operator.cc:51-88)
+ * describes them. */
+enum { BANDCU_SRC_GRAY = 0, BANDCU_SRC_RGB = 1, BANDCU_SRC_RGBA = 2, BANDCU_SRC_YUV420 = 3 };
+
+/* Per-pixel conversion applied when a source pixel is fetched. */
+enum {
+  BANDCU_CVT_NONE = 0,      /* keep the source channels (GRAY:1, RGB:3, RGBA:4) */
+  BANDCU_CVT_YUV2RGB = 1,   /* NV12ToRAW / NV21ToRAW / I420ToRAW  (:102,:190,:278) */
+  BANDCU_CVT_YUV2RGBA = 2,  /* ...ToABGR, A = 255                 (:114,:202,:291) */
+  BANDCU_CVT_YUV2GRAY = 3,  /* Y-plane copy                       (:163-170)       */
+  BANDCU_CVT_RGB2GRAY = 4,  /* RAWToJ400                          (:526)           */
+  BANDCU_CVT_RGBA2GRAY = 5, /* ABGRToARGB + ARGBToJ400            (:592-619)       */
+  BANDCU_CVT_RGBA2RGB = 6,  /* ARGBToRGB24 on RGBA bytes          (:675-687)       */
+};
+
+/* Which libyuv scaler family the Resize stage follows. */
+enum {
+  BANDCU_FLAVOR_ARGB = 0,  /* ARGBScale: RGB / RGBA (libyuv_image_operator.cc:1175,:1219) */
+  BANDCU_FLAVOR_PLANE = 1, /* ScalePlane: gray (:1373) */
+};
+
+/* Scaler code path, chosen on the host by the libyuv dispatch rules
+ * (scale_argb.cc ScaleARGB / scale.cc ScalePlane). */
+enum {
+  BANDCU_SCALE_COPY = 0,          /* no Resize stage */
+  BANDCU_SCALE_POINT = 1,         /* Scale*Simple */
+  BANDCU_SCALE_BILINEAR_DOWN = 2, /* Scale*BilinearDown (rows then columns) */
+  BANDCU_SCALE_BILINEAR_UP = 3,   /* Scale*BilinearUp (columns then rows) */
+  BANDCU_SCALE_BOX2 = 4,          /* ScaleARGBDown2/DownEven box, ScalePlaneDown2 box */
+  BANDCU_SCALE_VERTICAL = 5,      /* ScalePlaneVertical */
+  BANDCU_SCALE_DOWN34 = 6,        /* ScalePlaneDown34 (plane only) */
+  BANDCU_SCALE_DOWN38 = 7,        /* ScalePlaneDown38 (plane only) */
+  BANDCU_SCALE_UP2_LINEAR = 8,    /* ScalePlaneUp2_Linear (plane only) */
+  BANDCU_SCALE_UP2_BILINEAR = 9,  /* ScalePlaneUp2_Bilinear (plane only) */
+};
+
+/* Output element types (Normalize / DataTypeConvert targets,
+ * common_operator.cc:42-65). Values follow band::DataType (common.h:115-128). */
+enum {
+  BANDCU_DT_F32 = 1,
+  BANDCU_DT_I32 = 2,
+  BANDCU_DT_U8 = 3,
+  BANDCU_DT_I16 = 7,
+  BANDCU_DT_I8 = 9,
+  BANDCU_DT_F64 = 11,
+};
+
+/* Integer affine index map: row = r0 + rr*r + rc*c ; col = c0 + cr*r + cc*c.
+ * Crop / Rotate / Flip compose into these on the host. */
+typedef struct BandCuAffine {
+  int r0, rr, rc;
+  int c0, cr, cc;
+} BandCuAffine;
+
+/* A fused plan: [index maps] -> [pixel conversion] -> [Resize] -> [Normalize]
+ * evaluated lazily per output element; results are identical to running the
+ * reference's operator chain stage by stage. */
+typedef struct BandCuPlanDesc {
+  /* source planes */
+  int src_kind;        /* BANDCU_SRC_* */
+  int stride0;         /* bytes between rows of plane 0 (Y or packed) */
+  int stride_uv;       /* bytes between chroma rows */
+  int pixel_stride_uv; /* 1 planar, 2 interleaved */
+  /* virtual image seen by the arithmetic stages (after all index maps) */
+  int vw, vh;
+  BandCuAffine luma_map;   /* virtual (r,c) -> plane-0 (row, col) */
+  BandCuAffine pre_map;    /* virtual (r,c) -> coordinate (r1,c1) in the image the colour conversion ran on */
+  BandCuAffine chroma_map; /* (r1>>1, c1>>1) -> chroma plane (row, col) */
+  int cvt;                 /* BANDCU_CVT_* */
+  /* Resize stage */
+  int flavor;     /* BANDCU_FLAVOR_* */
+  int scale_mode; /* BANDCU_SCALE_* */
+  int linear;     /* filter reduced to kFilterLinear: no vertical blend */
+  int x0, y0, dx, dy; /* 16.16 */
+  int max_y;          /* clamp for y (mode dependent) */
+  int dst_width, dst_height;
+  /* output */
+  int channels;       /* 1, 3 or 4 channels per output pixel */
+  int out_dtype;      /* BANDCU_DT_* */
+  int normalize;      /* 0: store u8 results; 1: out = (T)((T)(v - mean) / std) */
+  float mean, std_;
+  long long dst_row_stride; /* bytes between output rows (contiguous NHWC: dst_width*channels*sizeof(T)) */
+} BandCuPlanDesc;
+
+typedef struct BandCuPlan BandCuPlan;
+
+/* Per-frame pointers (device memory). pu/pv unused for packed sources. */
+typedef struct BandCuFrame {
+  const void* p0;
+  const void* pu;
+  const void* pv;
+  void* out;
+} BandCuFrame;
+
+/* ---- plans ---------------------------------------------------------------- */
+BANDCU_API int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan);
+BANDCU_API int bandcu_plan_destroy(BandCuPlan* plan);
+/* 1 if the plan runs on the staged/specialised fast kernel, 0 for the generic one. */
+BANDCU_API int bandcu_plan_is_fast(const BandCuPlan* plan);
+/* Run n frames whose pointers advance by a fixed stride (bytes). */
+BANDCU_API int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* first, long long in_stride,
+                                       long long out_stride, int n, void* stream);
+/* Run n frames with arbitrary device pointers (host array; uploaded internally). */
+BANDCU_API int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* stream);
+/* number of kernel launches issued by this library on the calling process so far */
+BANDCU_API long long bandcu_launch_count(void);
+
+/* ---- 4:2:0 -> 4:2:0 index-mapped copy (Crop/Rotate/Flip/ColorSpaceConvert with a
+ * YUV output: CropNv/CropYv :950-1037, RotateYv/RotateNv :786-887, YUV<->YUV
+ * repacks :125-162,:213-250,:302-367, Flip* :1232-1363) -------------------- */
+typedef struct BandCuYuvMapDesc {
+  int src_stride_y, src_stride_uv, src_pixel_stride_uv;
+  int dst_stride_y, dst_stride_uv, dst_pixel_stride_uv;
+  int dst_width, dst_height;   /* luma dims of the output; chroma dims = (d+1)/2 */
+  int chroma_width_override;   /* >0: copy this many chroma samples per row instead of (dst_width+1)/2 */
+  BandCuAffine luma_map;       /* dst (r,c) -> src luma (row, col) */
+  BandCuAffine chroma_map;     /* dst chroma (r,c) -> src chroma (row, col) */
+} BandCuYuvMapDesc;
+typedef struct BandCuYuvPtrs {
+  const void *sy, *su, *sv;
+  void *dy, *du, *dv;
+} BandCuYuvPtrs;
+BANDCU_API int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void* stream);
+
+/* ---- element-wise Normalize / DataTypeConvert on an arbitrary dtype pair
+ * (common_operator.cc:24-65); n elements, contiguous. ----------------------- */
+BANDCU_API int bandcu_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean,
+                                float std_, void* stream);
+
+/* ---- device plumbing ------------------------------------------------------ */
+BANDCU_API int bandcu_device_count(int* count);
+BANDCU_API int bandcu_set_device(int device);
+BANDCU_API int bandcu_malloc(void** ptr, size_t bytes);
+BANDCU_API int bandcu_free(void* ptr);
+BANDCU_API int bandcu_host_alloc(void** ptr, size_t bytes); /* pinned */
+BANDCU_API int bandcu_host_free(void* ptr);
+BANDCU_API int bandcu_memcpy_h2d(void* dst, const void* src, size_t bytes, void* stream);
+BANDCU_API int bandcu_memcpy_d2h(void* dst, const void* src, size_t bytes, void* stream);
+BANDCU_API int bandcu_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
+BANDCU_API int bandcu_memset(void* dst, int value, size_t bytes, void* stream);
+BANDCU_API int bandcu_stream_create(void** stream);
+BANDCU_API int bandcu_stream_destroy(void* stream);
+BANDCU_API int bandcu_stream_sync(void* stream);
+BANDCU_API int bandcu_event_create(void** ev);
+BANDCU_API int bandcu_event_destroy(void* ev);
+BANDCU_API int bandcu_event_record(void* ev, void* stream);
+BANDCU_API int bandcu_event_elapsed_ms(void* start, void* stop, float* ms);
+/* 1 if ptr is device (or managed) memory, 0 if host, <0 on error. */
+BANDCU_API int bandcu_pointer_is_device(const void* ptr);
+BANDCU_API const char* bandcu_last_error_string(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BAND_INCLUDE_BANDCU_H_ */
