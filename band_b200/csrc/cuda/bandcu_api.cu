@@ -1,0 +1,307 @@
+// band_b200/csrc/cuda/bandcu_api.cu -- extern "C" surface of libbandcu.so
+// (declared in include/bandcu.h). POD in, int out; no C++ types or exceptions
+// cross this boundary.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "bandcu_device.cuh"
+#include "bandcu_internal.h"
+
+namespace bandcu {
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* what) {
+  if (code >= 10000) {
+    snprintf(g_err, sizeof(g_err), "bandcu: %s", what);
+  } else {
+    snprintf(g_err, sizeof(g_err), "bandcu: %s: %s (%s)", what, cudaGetErrorName((cudaError_t)code),
+             cudaGetErrorString((cudaError_t)code));
+    (void)cudaGetLastError();  // clear the sticky-less error state
+  }
+  return code;
+}
+#define CU_TRY(expr, what)                      \
+  do {                                          \
+    cudaError_t _e = (expr);                    \
+    if (_e != cudaSuccess) return fail((int)_e, what); \
+  } while (0)
+
+}  // namespace bandcu
+
+using namespace bandcu;
+
+struct BandCuPlan {
+  BandCuPlanDesc d;
+  FastPlan* fast;
+  // pointer-table staging for bandcu_plan_run()
+  BandCuFrame* table_dev;
+  BandCuFrame* table_host;  // pinned
+  int table_cap;
+  cudaEvent_t table_free;   // recorded after the launch that consumed the table
+  bool table_pending;
+};
+
+static int validate_desc(const BandCuPlanDesc* d) {
+  if (!d) return BANDCU_E_INVALID;
+  if (d->src_kind < BANDCU_SRC_GRAY || d->src_kind > BANDCU_SRC_YUV420) return BANDCU_E_INVALID;
+  if (d->vw <= 0 || d->vh <= 0 || d->dst_width <= 0 || d->dst_height <= 0) return BANDCU_E_INVALID;
+  if (d->channels != 1 && d->channels != 3 && d->channels != 4) return BANDCU_E_INVALID;
+  if (d->scale_mode < BANDCU_SCALE_COPY || d->scale_mode > BANDCU_SCALE_UP2_BILINEAR) return BANDCU_E_INVALID;
+  if (d->scale_mode >= BANDCU_SCALE_DOWN34 && (d->flavor != BANDCU_FLAVOR_PLANE || d->channels != 1))
+    return BANDCU_E_UNSUPPORTED;
+  if (d->flavor == BANDCU_FLAVOR_PLANE && d->channels != 1) return BANDCU_E_UNSUPPORTED;
+  if (d->normalize) {
+    switch (d->out_dtype) {
+      case BANDCU_DT_F32: case BANDCU_DT_U8: case BANDCU_DT_I8: case BANDCU_DT_I16: case BANDCU_DT_I32: break;
+      default: return BANDCU_E_UNSUPPORTED;
+    }
+  }
+  // channel count must agree with the conversion
+  int ch;
+  switch (d->cvt) {
+    case BANDCU_CVT_NONE:
+      ch = d->src_kind == BANDCU_SRC_GRAY ? 1 : d->src_kind == BANDCU_SRC_RGB ? 3 : d->src_kind == BANDCU_SRC_RGBA ? 4 : -1;
+      break;
+    case BANDCU_CVT_YUV2RGB: ch = d->src_kind == BANDCU_SRC_YUV420 ? 3 : -1; break;
+    case BANDCU_CVT_YUV2RGBA: ch = d->src_kind == BANDCU_SRC_YUV420 ? 4 : -1; break;
+    case BANDCU_CVT_YUV2GRAY: ch = d->src_kind == BANDCU_SRC_YUV420 ? 1 : -1; break;
+    case BANDCU_CVT_RGB2GRAY: ch = d->src_kind == BANDCU_SRC_RGB ? 1 : -1; break;
+    case BANDCU_CVT_RGBA2GRAY: ch = d->src_kind == BANDCU_SRC_RGBA ? 1 : -1; break;
+    case BANDCU_CVT_RGBA2RGB: ch = d->src_kind == BANDCU_SRC_RGBA ? 3 : -1; break;
+    default: ch = -1;
+  }
+  if (ch != d->channels) return BANDCU_E_INVALID;
+  return BANDCU_OK;
+}
+
+extern "C" {
+
+int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan) {
+  if (!plan) return fail(BANDCU_E_INVALID, "plan_create: null out pointer");
+  *plan = nullptr;
+  int v = validate_desc(desc);
+  if (v != BANDCU_OK) return fail(v, "plan_create: invalid or unsupported descriptor");
+  BandCuPlan* p = new (std::nothrow) BandCuPlan();
+  if (!p) return fail(BANDCU_E_INVALID, "plan_create: out of host memory");
+  memset(p, 0, sizeof(*p));
+  p->d = *desc;
+  if (fast_plan_supported(p->d)) {
+    int e = fast_plan_create(p->d, &p->fast);
+    if (e != BANDCU_OK) {
+      delete p;
+      return fail(e, "plan_create: fast plan setup");
+    }
+  }
+  *plan = p;
+  return BANDCU_OK;
+}
+
+int bandcu_plan_destroy(BandCuPlan* plan) {
+  if (!plan) return BANDCU_OK;
+  if (plan->table_pending) (void)cudaEventSynchronize(plan->table_free);
+  if (plan->table_free) (void)cudaEventDestroy(plan->table_free);
+  if (plan->table_dev) (void)cudaFree(plan->table_dev);
+  if (plan->table_host) (void)cudaFreeHost(plan->table_host);
+  if (plan->fast) fast_plan_destroy(plan->fast);
+  delete plan;
+  return BANDCU_OK;
+}
+
+int bandcu_plan_is_fast(const BandCuPlan* plan) { return plan && plan->fast ? 1 : 0; }
+
+static int run_batch(BandCuPlan* plan, const BatchArgs& b, int n, cudaStream_t s) {
+  if (plan->fast) {
+    int e = launch_fast(plan->fast, plan->d, b, n, s);
+    if (e == BANDCU_OK) return BANDCU_OK;
+    if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: fast kernel launch");
+    // this batch's pointers/strides do not meet the staged kernel's alignment
+    // rules: the generic kernel computes the identical result.
+  }
+  int e = launch_generic(plan->d, b, n, s);
+  if (e != 0) return fail(e, "plan_run: generic kernel launch");
+  return BANDCU_OK;
+}
+
+int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* first, long long in_stride, long long out_stride,
+                            int n, void* stream) {
+  if (!plan || !first || n < 0) return fail(BANDCU_E_INVALID, "plan_run_strided: bad arguments");
+  if (n == 0) return BANDCU_OK;
+  if (!first->p0 || !first->out) return fail(BANDCU_E_INVALID, "plan_run_strided: null plane/output pointer");
+  if (plan->d.src_kind == BANDCU_SRC_YUV420 && plan->d.cvt != BANDCU_CVT_YUV2GRAY && (!first->pu || !first->pv))
+    return fail(BANDCU_E_INVALID, "plan_run_strided: null chroma pointer");
+  BatchArgs b;
+  b.first.p0 = (const uint8_t*)first->p0;
+  b.first.pu = (const uint8_t*)first->pu;
+  b.first.pv = (const uint8_t*)first->pv;
+  b.first.out = (uint8_t*)first->out;
+  b.in_stride = in_stride;
+  b.out_stride = out_stride;
+  b.table = nullptr;
+  return run_batch(plan, b, n, (cudaStream_t)stream);
+}
+
+int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* stream) {
+  if (!plan || !frames || n < 0) return fail(BANDCU_E_INVALID, "plan_run: bad arguments");
+  if (n == 0) return BANDCU_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n == 1) return bandcu_plan_run_strided(plan, frames, 0, 0, 1, stream);
+  // uniform stride? then no table is needed
+  {
+    long long is = (const char*)frames[1].p0 - (const char*)frames[0].p0;
+    long long os = (const char*)frames[1].out - (const char*)frames[0].out;
+    bool uniform = true;
+    for (int i = 1; i < n && uniform; ++i) {
+      uniform = ((const char*)frames[i].p0 - (const char*)frames[0].p0 == is * i) &&
+                ((const char*)frames[i].out - (const char*)frames[0].out == os * i) &&
+                (!frames[0].pu || (const char*)frames[i].pu - (const char*)frames[0].pu == is * i) &&
+                (!frames[0].pv || (const char*)frames[i].pv - (const char*)frames[0].pv == is * i);
+    }
+    if (uniform) return bandcu_plan_run_strided(plan, frames, is, os, n, stream);
+  }
+  if (plan->table_pending) {  // previous launch may still read the table
+    CU_TRY(cudaEventSynchronize(plan->table_free), "plan_run: wait for pointer table");
+    plan->table_pending = false;
+  }
+  if (n > plan->table_cap) {
+    if (plan->table_dev) (void)cudaFree(plan->table_dev);
+    if (plan->table_host) (void)cudaFreeHost(plan->table_host);
+    plan->table_dev = nullptr;
+    plan->table_host = nullptr;
+    plan->table_cap = 0;
+    int cap = n < 64 ? 64 : n;
+    CU_TRY(cudaMalloc((void**)&plan->table_dev, sizeof(BandCuFrame) * cap), "plan_run: table alloc");
+    CU_TRY(cudaMallocHost((void**)&plan->table_host, sizeof(BandCuFrame) * cap), "plan_run: pinned table alloc");
+    plan->table_cap = cap;
+  }
+  if (!plan->table_free) CU_TRY(cudaEventCreateWithFlags(&plan->table_free, cudaEventDisableTiming), "plan_run: event");
+  memcpy(plan->table_host, frames, sizeof(BandCuFrame) * n);
+  CU_TRY(cudaMemcpyAsync(plan->table_dev, plan->table_host, sizeof(BandCuFrame) * n, cudaMemcpyHostToDevice, s),
+         "plan_run: table upload");
+  BatchArgs b;
+  memset(&b, 0, sizeof(b));
+  b.table = plan->table_dev;
+  int e = run_batch(plan, b, n, s);
+  if (e != BANDCU_OK) return e;
+  CU_TRY(cudaEventRecord(plan->table_free, s), "plan_run: event record");
+  plan->table_pending = true;
+  return BANDCU_OK;
+}
+
+long long bandcu_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void* stream) {
+  if (!desc || !ptrs || !ptrs->sy || !ptrs->su || !ptrs->sv || !ptrs->du || !ptrs->dv)
+    return fail(BANDCU_E_INVALID, "yuv_map: null argument");
+  if (desc->dst_width <= 0 || desc->dst_height <= 0) return fail(BANDCU_E_INVALID, "yuv_map: bad dims");
+  int e = launch_yuv_map(*desc, *ptrs, (cudaStream_t)stream);
+  if (e != 0) return fail(e, "yuv_map: launch");
+  return BANDCU_OK;
+}
+
+int bandcu_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean, float std_,
+                     void* stream) {
+  if (!in || !out || n < 0) return fail(BANDCU_E_INVALID, "normalize: bad arguments");
+  if (n == 0) return BANDCU_OK;
+  int e = launch_normalize(in, in_dtype, out, out_dtype, n, mean, std_, (cudaStream_t)stream);
+  if (e >= 10000) return fail(e, "normalize: unsupported dtype pair");
+  if (e != 0) return fail(e, "normalize: launch");
+  return BANDCU_OK;
+}
+
+int bandcu_device_count(int* count) {
+  if (!count) return fail(BANDCU_E_INVALID, "device_count: null");
+  CU_TRY(cudaGetDeviceCount(count), "cudaGetDeviceCount");
+  return BANDCU_OK;
+}
+int bandcu_set_device(int device) {
+  CU_TRY(cudaSetDevice(device), "cudaSetDevice");
+  return BANDCU_OK;
+}
+int bandcu_malloc(void** ptr, size_t bytes) {
+  if (!ptr) return fail(BANDCU_E_INVALID, "malloc: null");
+  CU_TRY(cudaMalloc(ptr, bytes ? bytes : 1), "cudaMalloc");
+  return BANDCU_OK;
+}
+int bandcu_free(void* ptr) {
+  if (ptr) CU_TRY(cudaFree(ptr), "cudaFree");
+  return BANDCU_OK;
+}
+int bandcu_host_alloc(void** ptr, size_t bytes) {
+  if (!ptr) return fail(BANDCU_E_INVALID, "host_alloc: null");
+  CU_TRY(cudaMallocHost(ptr, bytes ? bytes : 1), "cudaMallocHost");
+  return BANDCU_OK;
+}
+int bandcu_host_free(void* ptr) {
+  if (ptr) CU_TRY(cudaFreeHost(ptr), "cudaFreeHost");
+  return BANDCU_OK;
+}
+int bandcu_memcpy_h2d(void* dst, const void* src, size_t bytes, void* stream) {
+  CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream), "memcpy h2d");
+  return BANDCU_OK;
+}
+int bandcu_memcpy_d2h(void* dst, const void* src, size_t bytes, void* stream) {
+  CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream), "memcpy d2h");
+  return BANDCU_OK;
+}
+int bandcu_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream) {
+  CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream), "memcpy d2d");
+  return BANDCU_OK;
+}
+int bandcu_memset(void* dst, int value, size_t bytes, void* stream) {
+  CU_TRY(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream), "memset");
+  return BANDCU_OK;
+}
+int bandcu_stream_create(void** stream) {
+  if (!stream) return fail(BANDCU_E_INVALID, "stream_create: null");
+  cudaStream_t s;
+  CU_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "cudaStreamCreate");
+  *stream = (void*)s;
+  return BANDCU_OK;
+}
+int bandcu_stream_destroy(void* stream) {
+  if (stream) CU_TRY(cudaStreamDestroy((cudaStream_t)stream), "cudaStreamDestroy");
+  return BANDCU_OK;
+}
+int bandcu_stream_sync(void* stream) {
+  CU_TRY(cudaStreamSynchronize((cudaStream_t)stream), "cudaStreamSynchronize");
+  return BANDCU_OK;
+}
+int bandcu_event_create(void** ev) {
+  if (!ev) return fail(BANDCU_E_INVALID, "event_create: null");
+  cudaEvent_t e;
+  CU_TRY(cudaEventCreate(&e), "cudaEventCreate");
+  *ev = (void*)e;
+  return BANDCU_OK;
+}
+int bandcu_event_destroy(void* ev) {
+  if (ev) CU_TRY(cudaEventDestroy((cudaEvent_t)ev), "cudaEventDestroy");
+  return BANDCU_OK;
+}
+int bandcu_event_record(void* ev, void* stream) {
+  CU_TRY(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)stream), "cudaEventRecord");
+  return BANDCU_OK;
+}
+int bandcu_event_elapsed_ms(void* start, void* stop, float* ms) {
+  if (!ms) return fail(BANDCU_E_INVALID, "event_elapsed: null");
+  CU_TRY(cudaEventSynchronize((cudaEvent_t)stop), "cudaEventSynchronize");
+  CU_TRY(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop), "cudaEventElapsedTime");
+  return BANDCU_OK;
+}
+int bandcu_pointer_is_device(const void* ptr) {
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, ptr);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? 1 : 0;
+}
+const char* bandcu_last_error_string(void) { return g_err; }
+
+}  // extern "C"

@@ -1,0 +1,336 @@
+// band_b200/csrc/cuda/bandcu_generic.cu
+//
+// Generic fused kernel: one thread per output pixel, every scaler code path,
+// every source layout and any Crop/Rotate/Flip index map. It is the
+// always-correct path (and the one C3's rotated 4K YV12 chain runs on); the
+// staged fast kernel in bandcu_fast.cu overrides it for the NV12/NV21 ->
+// bilinear-down hot chain.
+//
+// Replaces, fused into one pass: LibyuvImageOperator::ColorSpaceConvert
+// (libyuv_image_operator.cc:1709-1727), ::Resize (:1627-1646), ::Crop
+// (:1609-1625), ::Rotate (:1648-1667), ::Flip* (:1669-1707) with a packed
+// output, and Normalize/DataTypeConvert (common_operator.cc:24-175).
+#include "bandcu_device.cuh"
+#include "bandcu_internal.h"
+
+namespace bandcu {
+
+struct GenericParams {
+  BandCuPlanDesc d;
+  BatchArgs batch;
+};
+
+__device__ __forceinline__ int map_row(const BandCuAffine& m, int r, int c) { return m.r0 + m.rr * r + m.rc * c; }
+__device__ __forceinline__ int map_col(const BandCuAffine& m, int r, int c) { return m.c0 + m.cr * r + m.cc * c; }
+
+// Fetch one pixel of the virtual image (after index maps and colour
+// conversion) as packed channels c0 | c1<<8 | c2<<16 | c3<<24.
+__device__ __forceinline__ uint32_t fetch_px(const BandCuPlanDesc& d, const FramePtrs& f, int r, int c) {
+  r = min(max(r, 0), d.vh - 1);
+  c = min(max(c, 0), d.vw - 1);
+  const int row = map_row(d.luma_map, r, c);
+  const int col = map_col(d.luma_map, r, c);
+  const uint8_t* p = f.p0 + (long long)row * d.stride0;
+  switch (d.src_kind) {
+    case BANDCU_SRC_GRAY:
+      return p[col];
+    case BANDCU_SRC_RGB: {
+      const uint8_t* q = p + col * 3;
+      uint32_t R = q[0], G = q[1], B = q[2];
+      if (d.cvt == BANDCU_CVT_RGB2GRAY) return rgb_to_yj(R, G, B);
+      return R | (G << 8) | (B << 16);
+    }
+    case BANDCU_SRC_RGBA: {
+      const uint8_t* q = p + col * 4;
+      uint32_t R = q[0], G = q[1], B = q[2], A = q[3];
+      if (d.cvt == BANDCU_CVT_RGBA2GRAY) return rgb_to_yj(R, G, B);
+      if (d.cvt == BANDCU_CVT_RGBA2RGB) return R | (G << 8) | (B << 16);
+      return R | (G << 8) | (B << 16) | (A << 24);
+    }
+    default: {  // BANDCU_SRC_YUV420
+      const int Y = p[col];
+      if (d.cvt == BANDCU_CVT_YUV2GRAY) return (uint32_t)Y;
+      // chroma is NEAREST: sample (r1>>1, c1>>1) of the image the conversion ran on
+      const int r1 = map_row(d.pre_map, r, c), c1 = map_col(d.pre_map, r, c);
+      const int cr = map_row(d.chroma_map, r1 >> 1, c1 >> 1);
+      const int cc = map_col(d.chroma_map, r1 >> 1, c1 >> 1);
+      const long long off = (long long)cr * d.stride_uv + (long long)cc * d.pixel_stride_uv;
+      const int U = f.pu[off], V = f.pv[off];
+      uint32_t rgb = yuv_to_rgb_packed(yuv_luma_term(Y), yuv_chroma_terms(U, V));
+      if (d.cvt == BANDCU_CVT_YUV2RGBA) rgb |= 0xFF000000u;
+      return rgb;
+    }
+  }
+}
+
+// One output pixel of the Resize stage (packed channels).
+__device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy, int ox) {
+  const bool plane = (d.flavor == BANDCU_FLAVOR_PLANE);
+  switch (d.scale_mode) {
+    case BANDCU_SCALE_COPY:
+      return fetch_px(d, f, oy, ox);
+    case BANDCU_SCALE_POINT: {  // ScaleARGBSimple / ScalePlaneSimple
+      long long y = (long long)d.y0 + (long long)oy * d.dy;
+      long long x = (long long)d.x0 + (long long)ox * d.dx;
+      return fetch_px(d, f, (int)(y >> 16), (int)(x >> 16));
+    }
+    case BANDCU_SCALE_BILINEAR_DOWN: {  // ScaleARGBBilinearDown / ScalePlaneBilinearDown
+      long long y = (long long)d.y0 + (long long)oy * d.dy;
+      if (y > d.max_y) y = d.max_y;
+      const int yi = (int)(y >> 16);
+      const int yf = d.linear ? 0 : (int)((y >> 8) & 255);
+      const long long x = (long long)d.x0 + (long long)ox * d.dx;
+      const int xi = (int)(x >> 16);
+      uint32_t a = fetch_px(d, f, yi, xi);
+      uint32_t b = fetch_px(d, f, yi, xi + 1);
+      if (yf) {
+        a = interp_rows4(a, fetch_px(d, f, yi + 1, xi), yf);
+        b = interp_rows4(b, fetch_px(d, f, yi + 1, xi + 1), yf);
+      }
+      if (plane) return blend_cols1_round7(a, b, (int)(x & 0xffff));
+      return blend_cols4_trunc7(a, b, (int)((x >> 9) & 0x7f));
+    }
+    case BANDCU_SCALE_BILINEAR_UP: {  // Scale*BilinearUp: columns first, then rows
+      long long y = (long long)d.y0 + (long long)oy * d.dy;
+      if (y > d.max_y) y = d.max_y;
+      const int yi = (int)(y >> 16);
+      const int yf = d.linear ? 0 : (int)((y >> 8) & 255);
+      const long long x = (long long)d.x0 + (long long)ox * d.dx;
+      const int xi = (int)(x >> 16);
+      const int xf7 = (int)((x >> 9) & 0x7f), xf16 = (int)(x & 0xffff);
+      uint32_t a0 = fetch_px(d, f, yi, xi), b0 = fetch_px(d, f, yi, xi + 1);
+      uint32_t top = plane ? blend_cols1_round7(a0, b0, xf16) : blend_cols4_trunc7(a0, b0, xf7);
+      if (!yf) return top;
+      uint32_t a1 = fetch_px(d, f, yi + 1, xi), b1 = fetch_px(d, f, yi + 1, xi + 1);
+      uint32_t bot = plane ? blend_cols1_round7(a1, b1, xf16) : blend_cols4_trunc7(a1, b1, xf7);
+      return interp_rows4(top, bot, yf);
+    }
+    case BANDCU_SCALE_BOX2: {  // 2x2 box at (y0>>16 + oy*(dy>>16), x0>>16 + ox*(dx>>16))
+      const int r = (d.y0 >> 16) + oy * (d.dy >> 16);
+      const int c = (d.x0 >> 16) + ox * (d.dx >> 16);
+      return box2x2_4(fetch_px(d, f, r, c), fetch_px(d, f, r, c + 1), fetch_px(d, f, r + 1, c),
+                      fetch_px(d, f, r + 1, c + 1));
+    }
+    case BANDCU_SCALE_VERTICAL: {  // ScalePlaneVertical (its own max_y, passed in d.max_y)
+      long long y = (long long)d.y0 + (long long)oy * d.dy;
+      if (y > d.max_y) y = d.max_y;
+      const int yi = (int)(y >> 16);
+      const int yf = d.linear ? 0 : (int)((y >> 8) & 255);  // d.linear here = "filtering == None"
+      const int c = ox + (d.x0 >> 16);
+      uint32_t a = fetch_px(d, f, yi, c);
+      if (!yf) return a;
+      return interp_rows4(a, fetch_px(d, f, yi + 1, c), yf);
+    }
+    case BANDCU_SCALE_DOWN34: {  // ScalePlaneDown34 with ScaleRowDown34_{0,1}_Box_C
+      const int g = oy / 3, k = oy - 3 * g;
+      const int m = ox / 3, j = ox - 3 * m;
+      int rs, rt;  // s row, t row
+      if (k == 0) { rs = 4 * g; rt = 4 * g + 1; }
+      else if (k == 1) { rs = 4 * g + 1; rt = 4 * g + 2; }
+      else { rs = 4 * g + 3; rt = 4 * g + 2; }
+      int hs, ht;
+      const int c = 4 * m;
+      if (j == 0) {
+        hs = ((int)fetch_px(d, f, rs, c) * 3 + (int)fetch_px(d, f, rs, c + 1) + 2) >> 2;
+        ht = ((int)fetch_px(d, f, rt, c) * 3 + (int)fetch_px(d, f, rt, c + 1) + 2) >> 2;
+      } else if (j == 1) {
+        hs = ((int)fetch_px(d, f, rs, c + 1) + (int)fetch_px(d, f, rs, c + 2) + 1) >> 1;
+        ht = ((int)fetch_px(d, f, rt, c + 1) + (int)fetch_px(d, f, rt, c + 2) + 1) >> 1;
+      } else {
+        hs = ((int)fetch_px(d, f, rs, c + 2) + (int)fetch_px(d, f, rs, c + 3) * 3 + 2) >> 2;
+        ht = ((int)fetch_px(d, f, rt, c + 2) + (int)fetch_px(d, f, rt, c + 3) * 3 + 2) >> 2;
+      }
+      return (k == 1) ? (uint32_t)((hs + ht + 1) >> 1) : (uint32_t)((hs * 3 + ht + 2) >> 2);
+    }
+    case BANDCU_SCALE_DOWN38: {  // ScalePlaneDown38 with ScaleRowDown38_{3,2}_Box_C
+      const int g = oy / 3, k = oy - 3 * g;
+      const int m = ox / 3, j = ox - 3 * m;
+      const int r0 = 8 * g + 3 * k, nr = (k == 2) ? 2 : 3;
+      const int c0 = 8 * m + 3 * j, nc = (j == 2) ? 2 : 3;
+      int sum = 0;
+      for (int rr = 0; rr < nr; ++rr)
+        for (int cc = 0; cc < nc; ++cc) sum += (int)fetch_px(d, f, r0 + rr, c0 + cc);
+      const int n = nr * nc;
+      const int mul = (n == 9) ? (65536 / 9) : (n == 6) ? (65536 / 6) : (65536 / 4);
+      return (uint32_t)((sum * mul) >> 16) & 0xFFu;
+    }
+    case BANDCU_SCALE_UP2_LINEAR:
+    case BANDCU_SCALE_UP2_BILINEAR: {  // ScalePlaneUp2_{Linear,Bilinear} + *_Any_C edges
+      const int dw = d.dst_width, dh = d.dst_height, sh = d.vh;
+      int cn, cf;  // near / far source column
+      if (ox == 0) { cn = cf = 0; }
+      else if (ox == dw - 1) { cn = cf = (dw - 1) / 2; }
+      else { const int xx = (ox - 1) >> 1; if (ox & 1) { cn = xx; cf = xx + 1; } else { cn = xx + 1; cf = xx; } }
+      if (d.scale_mode == BANDCU_SCALE_UP2_LINEAR) {
+        int row;
+        if (dh == 1) row = (sh - 1) / 2;
+        else row = (int)(((long long)32767 + (long long)oy * d.dy) >> 16);  // d.dy = FixedDiv(sh-1, dh-1)
+        const int n = (int)fetch_px(d, f, row, cn), fr = (int)fetch_px(d, f, row, cf);
+        return (uint32_t)((3 * n + fr + 2) >> 2);
+      }
+      int rn, rf;  // near / far source row
+      if (oy == 0) { rn = rf = 0; }
+      else if (oy == dh - 1 && !(dh & 1)) { rn = rf = sh - 1; }
+      else { const int yy = (oy - 1) >> 1; if (oy & 1) { rn = yy; rf = yy + 1; } else { rn = yy + 1; rf = yy; } }
+      const int A = (int)fetch_px(d, f, rn, cn), B = (int)fetch_px(d, f, rn, cf);
+      const int C = (int)fetch_px(d, f, rf, cn), D = (int)fetch_px(d, f, rf, cf);
+      return (uint32_t)((9 * A + 3 * B + 3 * C + D + 8) >> 4);
+    }
+    default:
+      return 0;
+  }
+}
+
+template <typename OT>
+__device__ __forceinline__ void store_norm(uint8_t* out_row, int ox, int ch, uint32_t px, float mean, float sd) {
+  OT* o = reinterpret_cast<OT*>(out_row) + (long long)ox * ch;
+  for (int k = 0; k < ch; ++k) o[k] = normalize_elem<OT>((float)((px >> (8 * k)) & 0xFFu), mean, sd);
+}
+
+__global__ void __launch_bounds__(256) fused_generic_kernel(const __grid_constant__ GenericParams P) {
+  const BandCuPlanDesc& d = P.d;
+  const int ox = blockIdx.x * blockDim.x + threadIdx.x;
+  const int oy = blockIdx.y * blockDim.y + threadIdx.y;
+  if (ox >= d.dst_width || oy >= d.dst_height) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  const uint32_t px = scale_px(d, f, oy, ox);
+  uint8_t* out_row = f.out + (long long)oy * d.dst_row_stride;
+  const int ch = d.channels;
+  if (!d.normalize) {
+    uint8_t* o = out_row + (long long)ox * ch;
+    if (ch == 4) {
+      if ((reinterpret_cast<uintptr_t>(o) & 3) == 0) *reinterpret_cast<uint32_t*>(o) = px;
+      else { o[0] = px & 0xFF; o[1] = (px >> 8) & 0xFF; o[2] = (px >> 16) & 0xFF; o[3] = px >> 24; }
+    } else {
+      for (int k = 0; k < ch; ++k) o[k] = (uint8_t)((px >> (8 * k)) & 0xFFu);
+    }
+    return;
+  }
+  switch (d.out_dtype) {
+    case BANDCU_DT_F32: store_norm<float>(out_row, ox, ch, px, d.mean, d.std_); break;
+    case BANDCU_DT_U8: store_norm<uint8_t>(out_row, ox, ch, px, d.mean, d.std_); break;
+    case BANDCU_DT_I8: store_norm<int8_t>(out_row, ox, ch, px, d.mean, d.std_); break;
+    case BANDCU_DT_I16: store_norm<int16_t>(out_row, ox, ch, px, d.mean, d.std_); break;
+    case BANDCU_DT_I32: store_norm<int32_t>(out_row, ox, ch, px, d.mean, d.std_); break;
+    default: break;
+  }
+}
+
+int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream) {
+  GenericParams P;
+  P.d = d;
+  P.batch = batch;
+  dim3 block(32, 8, 1);
+  dim3 grid((d.dst_width + 31) / 32, (d.dst_height + 7) / 8, 1);
+  // gridDim.z is limited to 65535: chunk very large batches
+  for (int done = 0; done < n;) {
+    int chunk = n - done > 65535 ? 65535 : n - done;
+    GenericParams Q = P;
+    if (Q.batch.table) {
+      Q.batch.table += done;
+    } else {
+      long long o = (long long)done * Q.batch.in_stride;
+      Q.batch.first.p0 += o;
+      if (Q.batch.first.pu) Q.batch.first.pu += o;
+      if (Q.batch.first.pv) Q.batch.first.pv += o;
+      Q.batch.first.out += (long long)done * Q.batch.out_stride;
+    }
+    grid.z = chunk;
+    fused_generic_kernel<<<grid, block, 0, stream>>>(Q);
+    count_launch();
+    done += chunk;
+  }
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// 4:2:0 -> 4:2:0 index-mapped copy: CropNv/CropYv (:950-1037), RotateYv/RotateNv
+// (:786-887), YUV<->YUV ColorSpaceConvert (:125-162,:213-250,:302-367), Flip*
+// (:1232-1363). Pure permutation of luma and chroma samples.
+// ---------------------------------------------------------------------------
+struct YuvMapParams {
+  BandCuYuvMapDesc d;
+  BandCuYuvPtrs p;
+};
+__global__ void __launch_bounds__(256) yuv_map_kernel(const __grid_constant__ YuvMapParams P) {
+  const BandCuYuvMapDesc& d = P.d;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = blockIdx.y * blockDim.y + threadIdx.y;
+  if (blockIdx.z == 0) {
+    if (c >= d.dst_width || r >= d.dst_height || !P.p.dy) return;
+    const int sr = map_row(d.luma_map, r, c), sc = map_col(d.luma_map, r, c);
+    ((uint8_t*)P.p.dy)[(long long)r * d.dst_stride_y + c] = ((const uint8_t*)P.p.sy)[(long long)sr * d.src_stride_y + sc];
+  } else {
+    const int cw = d.chroma_width_override > 0 ? d.chroma_width_override : (d.dst_width + 1) / 2;
+    const int chh = (d.dst_height + 1) / 2;
+    if (c >= cw || r >= chh) return;
+    const int sr = map_row(d.chroma_map, r, c), sc = map_col(d.chroma_map, r, c);
+    const long long so = (long long)sr * d.src_stride_uv + (long long)sc * d.src_pixel_stride_uv;
+    const long long dof = (long long)r * d.dst_stride_uv + (long long)c * d.dst_pixel_stride_uv;
+    ((uint8_t*)P.p.du)[dof] = ((const uint8_t*)P.p.su)[so];
+    ((uint8_t*)P.p.dv)[dof] = ((const uint8_t*)P.p.sv)[so];
+  }
+}
+int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream_t stream) {
+  YuvMapParams P;
+  P.d = d;
+  P.p = p;
+  dim3 block(32, 8, 1);
+  dim3 grid((d.dst_width + 31) / 32, (d.dst_height + 7) / 8, 2);
+  yuv_map_kernel<<<grid, block, 0, stream>>>(P);
+  count_launch();
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Element-wise Normalize / DataTypeConvert over any dtype pair
+// (common_operator.cc:24-65): out[i] = static_cast<Out>((in[i] - mean)) / std.
+// The difference is computed in float for integer/float inputs and in double for
+// a double input (usual arithmetic conversions against the float mean).
+// ---------------------------------------------------------------------------
+template <typename IT, typename OT>
+__global__ void __launch_bounds__(256) normalize_kernel(const IT* __restrict__ in, OT* __restrict__ out, long long n,
+                                                        float mean, float sd) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += step) {
+    if constexpr (sizeof(IT) == 8) {  // double input
+      double diff = __dsub_rn((double)in[i], (double)mean);
+      OT t = (OT)diff;
+      out[i] = (OT)__fdiv_rn((float)t, sd);
+    } else {
+      out[i] = normalize_elem<OT>((float)in[i], mean, sd);
+    }
+  }
+}
+template <typename IT>
+static int normalize_from(const void* in, void* out, int out_dtype, long long n, float mean, float sd,
+                          cudaStream_t stream) {
+  int block = 256;
+  long long want = (n + block - 1) / block;
+  int grid = (int)(want > 148LL * 16 ? 148LL * 16 : (want < 1 ? 1 : want));
+  switch (out_dtype) {
+    case BANDCU_DT_F32: normalize_kernel<IT, float><<<grid, block, 0, stream>>>((const IT*)in, (float*)out, n, mean, sd); break;
+    case BANDCU_DT_U8: normalize_kernel<IT, uint8_t><<<grid, block, 0, stream>>>((const IT*)in, (uint8_t*)out, n, mean, sd); break;
+    case BANDCU_DT_I8: normalize_kernel<IT, int8_t><<<grid, block, 0, stream>>>((const IT*)in, (int8_t*)out, n, mean, sd); break;
+    case BANDCU_DT_I16: normalize_kernel<IT, int16_t><<<grid, block, 0, stream>>>((const IT*)in, (int16_t*)out, n, mean, sd); break;
+    case BANDCU_DT_I32: normalize_kernel<IT, int32_t><<<grid, block, 0, stream>>>((const IT*)in, (int32_t*)out, n, mean, sd); break;
+    default: return BANDCU_E_UNSUPPORTED;
+  }
+  count_launch();
+  return (int)cudaGetLastError();
+}
+int launch_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean, float sd,
+                     cudaStream_t stream) {
+  switch (in_dtype) {
+    case BANDCU_DT_U8: return normalize_from<uint8_t>(in, out, out_dtype, n, mean, sd, stream);
+    case BANDCU_DT_I8: return normalize_from<int8_t>(in, out, out_dtype, n, mean, sd, stream);
+    case BANDCU_DT_I16: return normalize_from<int16_t>(in, out, out_dtype, n, mean, sd, stream);
+    case BANDCU_DT_I32: return normalize_from<int32_t>(in, out, out_dtype, n, mean, sd, stream);
+    case BANDCU_DT_F32: return normalize_from<float>(in, out, out_dtype, n, mean, sd, stream);
+    case BANDCU_DT_F64: return normalize_from<double>(in, out, out_dtype, n, mean, sd, stream);
+    default: return BANDCU_E_UNSUPPORTED;
+  }
+}
+
+}  // namespace bandcu

@@ -1,0 +1,24 @@
+// band_b200/csrc/cuda/bandcu_internal.h -- host-side declarations shared by the
+// .cu translation units of libbandcu.so (not part of the C-ABI).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "bandcu.h"
+
+namespace bandcu {
+struct BatchArgs;
+
+void count_launch();
+int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream);
+int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream_t stream);
+int launch_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean, float sd,
+                     cudaStream_t stream);
+
+// Fast (staged) path for the NV12/NV21 -> RGB -> bilinear-down [-> Normalize] chain.
+struct FastPlan;
+bool fast_plan_supported(const BandCuPlanDesc& d);
+int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out);
+void fast_plan_destroy(FastPlan* p);
+// returns BANDCU_E_UNSUPPORTED if this particular batch (alignment) cannot use it
+int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream);
+}  // namespace bandcu
