@@ -73,9 +73,26 @@ def build_band_c(force=False):
         return out
     cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
     cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fno-exceptions", "-Wall", "-Wextra",
-           "-Wno-unused-parameter", "-fvisibility=hidden", "-I" + CSRC, "-I" + os.path.join(CSRC, "compat"),
+           "-Wno-unused-parameter", "-I" + CSRC, "-I" + os.path.join(CSRC, "compat"),
            "-I" + INCLUDE, "-o", out] + srcs + ["-L" + LIBDIR, "-lbandcu", "-Wl,-rpath,$ORIGIN", "-lpthread"]
     _run(cmd)
+    return out
+
+
+def build_testing(force=False):
+    """lib/libband_testing.so: C entry points that replay the reference tests' C++ call sequences
+    (tests/cc/band_testing.cc) against libband_c.so. Test support only."""
+    out = os.path.join(LIBDIR, "libband_testing.so")
+    src = os.path.join(ROOT, "tests", "cc", "band_testing.cc")
+    if not os.path.exists(src):
+        return None
+    host = os.path.join(LIBDIR, "libband_c.so")
+    if not force and not _stale(out, [src, host]):
+        return out
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    _run([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fno-exceptions", "-Wall", "-I" + CSRC,
+          "-I" + os.path.join(CSRC, "compat"), "-I" + INCLUDE, "-o", out, src, "-L" + LIBDIR, "-lband_c", "-lbandcu",
+          "-Wl,-rpath,$ORIGIN"])
     return out
 
 
@@ -100,6 +117,9 @@ def build_all(force=False, verbose=False):
     b = build_band_c(force)
     if b:
         libs.append(b)
+    t = build_testing(force)
+    if t:
+        libs.append(t)
     libs.append(build_oracle(force))
     return libs
 

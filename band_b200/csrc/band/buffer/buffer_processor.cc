@@ -1,0 +1,95 @@
+// band/buffer/buffer_processor.cc -- see buffer_processor.h
+// (/root/reference/band/buffer/buffer_processor.cc:22-64).
+#include "band/buffer/buffer_processor.h"
+
+#include "band/buffer/buffer.h"
+#include "band/buffer/fused_plan.h"
+#include "band/logger.h"
+
+namespace band {
+
+BufferProcessor::BufferProcessor(std::vector<IBufferOperator*> operations) : operations_(std::move(operations)) {
+  // intermediates between operators are never materialised: shapes only
+  for (IBufferOperator* op : operations_) op->virtual_outputs_ = true;
+}
+
+BufferProcessor::~BufferProcessor() {
+  plan_.reset();
+  for (IBufferOperator* op : operations_) delete op;
+}
+
+absl::Status BufferProcessor::Prepare(const Buffer& input, Buffer& output) {
+  if (operations_.empty()) return absl::InternalError("IProcessor: no operations are specified.");
+  // the last operation writes the caller's buffer (buffer_processor.cc:28)
+  operations_.back()->SetOutput(&output);
+
+  const Buffer* next_input = &input;
+  for (size_t i = 0; i < operations_.size(); ++i) {
+    if (next_input == nullptr) return absl::InternalError("an in-place operator has no output to pass on");
+    IBufferOperator* op = operations_[i];
+    absl::Status status = op->ValidateInput(*next_input);
+    if (status.ok()) status = op->ValidateOrCreateOutput(*next_input);
+    if (!status.ok()) {
+      BAND_LOG(LogSeverity::kError, "BufferProcessor::Process failed %s", status.ToString().c_str());
+      return status;
+    }
+    next_input = op->GetOutput();
+  }
+
+  const cuda::ImageLayout in = cuda::ImageLayout::Of(input);
+  if (plan_ && plan_->input_layout() == in &&
+      (!plan_->writes_output() || plan_->output_layout() == cuda::ImageLayout::Of(output)))
+    return absl::OkStatus();
+
+  plan_.reset();
+  cuda::ChainLowering lowering(input);
+  next_input = &input;
+  for (IBufferOperator* op : operations_) {
+    absl::Status status = lowering.LowerNested(*op, *next_input);
+    if (!status.ok()) {
+      BAND_LOG(LogSeverity::kError, "BufferProcessor::Process failed %s", status.ToString().c_str());
+      return status;
+    }
+    next_input = op->GetOutput();
+  }
+  absl::StatusOr<std::unique_ptr<cuda::FusedPlan>> plan = lowering.Finish(&output);
+  if (!plan.ok()) {
+    BAND_LOG(LogSeverity::kError, "BufferProcessor::Process failed %s", plan.status().ToString().c_str());
+    return plan.status();
+  }
+  plan_ = std::move(plan).value();
+  return absl::OkStatus();
+}
+
+absl::Status BufferProcessor::Process(const Buffer& input, Buffer& output) {
+  RETURN_IF_ERROR(Prepare(input, output));
+  const Buffer* in = &input;
+  Buffer* out = &output;
+  absl::Status status = plan_->Run(&in, &out, 1);
+  if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::Process failed %s", status.ToString().c_str());
+  return status;
+}
+
+absl::Status BufferProcessor::ProcessBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n) {
+  if (n == 0) return absl::OkStatus();
+  if (inputs == nullptr || outputs == nullptr || inputs[0] == nullptr || outputs[0] == nullptr)
+    return absl::InvalidArgumentError("ProcessBatch: null buffer list");
+  RETURN_IF_ERROR(Prepare(*inputs[0], *outputs[0]));
+  absl::Status status = plan_->Run(inputs, outputs, static_cast<int>(n));
+  if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::ProcessBatch failed %s", status.ToString().c_str());
+  return status;
+}
+
+size_t BufferProcessor::GetNumLaunchSegments() const { return plan_ ? plan_->NumSegments() : 0; }
+bool BufferProcessor::IsSingleFastLaunch() const { return plan_ && plan_->IsSingleFastLaunch(); }
+
+IBufferProcessorBuilder& IBufferProcessorBuilder::AddOperation(std::unique_ptr<IBufferOperator> operation) {
+  operations_.emplace_back(std::move(operation));
+  return *this;
+}
+
+std::unique_ptr<BufferProcessor> IBufferProcessorBuilder::CreateProcessor(std::vector<IBufferOperator*> operations) {
+  return std::unique_ptr<BufferProcessor>(new BufferProcessor(std::move(operations)));
+}
+
+}  // namespace band

@@ -1,0 +1,73 @@
+// band/buffer/buffer_processor.h -- BufferProcessor / IBufferProcessorBuilder
+// with the reference's surface (/root/reference/band/buffer/buffer_processor.h:29-72).
+// Process(input, output) keeps its meaning -- run the operator chain, the last
+// operator writes into `output` -- but the chain is compiled once per
+// (input layout, output layout) into a cuda::FusedPlan and replayed as fused
+// launches. Additive: ProcessBatch for n independent frames in one call.
+#ifndef BAND_BUFFER_BUFFER_PROCESSOR_H_
+#define BAND_BUFFER_BUFFER_PROCESSOR_H_
+
+#include <memory>
+#include <vector>
+
+#include "absl/status/status.h"
+#include "absl/status/statusor.h"
+#include "band/buffer/operator.h"
+
+namespace band {
+
+class Buffer;
+class IBufferOperator;
+class BufferProcessor;
+namespace cuda {
+class FusedPlan;
+}
+
+class IBufferProcessorBuilder {
+ public:
+  IBufferProcessorBuilder() = default;
+  virtual ~IBufferProcessorBuilder() = default;
+  // Build a processor from the operations added to this builder.
+  virtual absl::StatusOr<std::unique_ptr<BufferProcessor>> Build() = 0;
+
+  // e.g. builder.AddOperation(std::make_unique<buffer::Resize>(224, 224));
+  IBufferProcessorBuilder& AddOperation(std::unique_ptr<IBufferOperator> operation);
+
+ protected:
+  std::unique_ptr<BufferProcessor> CreateProcessor(std::vector<IBufferOperator*> operations);
+
+  IBufferProcessorBuilder(const IBufferProcessorBuilder&) = delete;
+  IBufferProcessorBuilder& operator=(const IBufferProcessorBuilder&) = delete;
+
+  std::vector<std::unique_ptr<IBufferOperator>> operations_;
+};
+
+// Not re-entrant (like the reference: Process mutates operator state); use one
+// processor per thread and per GPU.
+class BufferProcessor {
+ public:
+  virtual ~BufferProcessor();
+  virtual absl::Status Process(const Buffer& input, Buffer& output);
+  // Additive: n frames sharing one layout, each written to its own output.
+  // Frames may be host or device memory; returns after all results are in place.
+  virtual absl::Status ProcessBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n);
+  // Additive introspection for tests / benchmarks.
+  size_t GetNumLaunchSegments() const;
+  bool IsSingleFastLaunch() const;
+
+ protected:
+  friend class IBufferProcessorBuilder;
+  BufferProcessor(std::vector<IBufferOperator*> operations);
+  BufferProcessor(const BufferProcessor&) = delete;
+  BufferProcessor& operator=(const BufferProcessor&) = delete;
+
+  // Runs the operator protocol (ValidateInput / ValidateOrCreateOutput) down the
+  // chain with shape-only intermediates and compiles the plan if the layouts changed.
+  absl::Status Prepare(const Buffer& input, Buffer& output);
+
+  std::vector<IBufferOperator*> operations_;
+  std::unique_ptr<cuda::FusedPlan> plan_;
+};
+}  // namespace band
+
+#endif  // BAND_BUFFER_BUFFER_PROCESSOR_H_

@@ -44,6 +44,7 @@ class Tensor : public interface::ITensor {
   char* data_ = nullptr;
   std::string name_;
   MemorySpace space_ = MemorySpace::kHost;
+  bool pinned_ = false;
 };
 }  // namespace band
 #endif  // BAND_TENSOR_H_

@@ -279,6 +279,17 @@ int bandcu_event_create(void** ev) {
   *ev = (void*)e;
   return BANDCU_OK;
 }
+int bandcu_event_create_sync(void** ev) {
+  if (!ev) return fail(BANDCU_E_INVALID, "event_create_sync: null");
+  cudaEvent_t e;
+  CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreateWithFlags");
+  *ev = (void*)e;
+  return BANDCU_OK;
+}
+int bandcu_stream_wait_event(void* stream, void* ev) {
+  CU_TRY(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)ev, 0), "cudaStreamWaitEvent");
+  return BANDCU_OK;
+}
 int bandcu_event_destroy(void* ev) {
   if (ev) CU_TRY(cudaEventDestroy((cudaEvent_t)ev), "cudaEventDestroy");
   return BANDCU_OK;

@@ -96,6 +96,8 @@ def lib():
     L.bandcu_stream_destroy.argtypes = [vp]
     L.bandcu_stream_sync.argtypes = [vp]
     L.bandcu_event_create.argtypes = [C.POINTER(vp)]
+    L.bandcu_event_create_sync.argtypes = [C.POINTER(vp)]
+    L.bandcu_stream_wait_event.argtypes = [vp, vp]
     L.bandcu_event_destroy.argtypes = [vp]
     L.bandcu_event_record.argtypes = [vp, vp]
     L.bandcu_event_elapsed_ms.argtypes = [vp, vp, C.POINTER(C.c_float)]
@@ -115,6 +117,6 @@ EXPORTED = [
     "bandcu_launch_count", "bandcu_yuv_map", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
     "bandcu_malloc", "bandcu_free", "bandcu_host_alloc", "bandcu_host_free", "bandcu_memcpy_h2d", "bandcu_memcpy_d2h",
     "bandcu_memcpy_d2d", "bandcu_memset", "bandcu_stream_create", "bandcu_stream_destroy", "bandcu_stream_sync",
-    "bandcu_event_create", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",
+    "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",
     "bandcu_pointer_is_device", "bandcu_last_error_string",
 ]

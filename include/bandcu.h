@@ -179,9 +179,11 @@ BANDCU_API int bandcu_stream_create(void** stream);
 BANDCU_API int bandcu_stream_destroy(void* stream);
 BANDCU_API int bandcu_stream_sync(void* stream);
 BANDCU_API int bandcu_event_create(void** ev);
+BANDCU_API int bandcu_event_create_sync(void** ev); /* ordering only (timing disabled) */
 BANDCU_API int bandcu_event_destroy(void* ev);
 BANDCU_API int bandcu_event_record(void* ev, void* stream);
 BANDCU_API int bandcu_event_elapsed_ms(void* start, void* stop, float* ms);
+BANDCU_API int bandcu_stream_wait_event(void* stream, void* ev);
 /* 1 if ptr is device (or managed) memory, 0 if host, <0 on error. */
 BANDCU_API int bandcu_pointer_is_device(const void* ptr);
 BANDCU_API const char* bandcu_last_error_string(void);
