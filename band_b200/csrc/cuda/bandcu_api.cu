@@ -45,6 +45,8 @@ struct BandCuPlan {
   int table_cap;
   cudaEvent_t table_free;   // recorded after the launch that consumed the table
   bool table_pending;
+  cudaStream_t table_stream;  // stream the upload was ordered on
+  int table_valid_n;        // >0: table_dev holds exactly table_host[0..n) (reused when the next call repeats it)
 };
 
 static int validate_desc(const BandCuPlanDesc* d) {
@@ -115,9 +117,9 @@ int bandcu_plan_destroy(BandCuPlan* plan) {
 
 int bandcu_plan_is_fast(const BandCuPlan* plan) { return plan && plan->fast ? 1 : 0; }
 
-static int run_batch(BandCuPlan* plan, const BatchArgs& b, int n, cudaStream_t s) {
+static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hints, int n, cudaStream_t s) {
   if (plan->fast) {
-    int e = launch_fast(plan->fast, plan->d, b, n, s);
+    int e = launch_fast(plan->fast, plan->d, b, hints, n, s);
     if (e == BANDCU_OK) return BANDCU_OK;
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: fast kernel launch");
     // this batch's pointers/strides do not meet the staged kernel's alignment
@@ -143,7 +145,7 @@ int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* first, long lon
   b.in_stride = in_stride;
   b.out_stride = out_stride;
   b.table = nullptr;
-  return run_batch(plan, b, n, (cudaStream_t)stream);
+  return run_batch(plan, b, TableHints(), n, (cudaStream_t)stream);
 }
 
 int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* stream) {
@@ -164,10 +166,36 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
     }
     if (uniform) return bandcu_plan_run_strided(plan, frames, is, os, n, stream);
   }
+  // what the staged kernel needs to know about the table, established on the host
+  TableHints hints;
+  hints.valid = true;
+  hints.semi_planar = frames[0].pu && frames[0].pv;
+  hints.aligned16 = true;
+  if (hints.semi_planar) {
+    const long long d0 = (const char*)frames[0].pv - (const char*)frames[0].pu;
+    hints.semi_planar = (d0 == 1 || d0 == -1);
+    hints.vu = (d0 == -1);
+    for (int i = 0; i < n && hints.semi_planar; ++i) {
+      hints.semi_planar = frames[i].pu && frames[i].pv && ((const char*)frames[i].pv - (const char*)frames[i].pu == d0);
+      const void* uv0 = hints.vu ? frames[i].pv : frames[i].pu;
+      if ((reinterpret_cast<uintptr_t>(frames[i].p0) & 15) || (reinterpret_cast<uintptr_t>(uv0) & 15))
+        hints.aligned16 = false;
+    }
+  }
+  // same pointers as the previous call: the table already in device memory is still right
+  const bool same_table = plan->table_valid_n == n && plan->table_host && plan->table_stream == s &&
+                          memcmp(plan->table_host, frames, sizeof(BandCuFrame) * n) == 0;
+  if (same_table) {
+    BatchArgs b;
+    memset(&b, 0, sizeof(b));
+    b.table = plan->table_dev;
+    return run_batch(plan, b, hints, n, s);
+  }
   if (plan->table_pending) {  // previous launch may still read the table
     CU_TRY(cudaEventSynchronize(plan->table_free), "plan_run: wait for pointer table");
     plan->table_pending = false;
   }
+  plan->table_valid_n = 0;
   if (n > plan->table_cap) {
     if (plan->table_dev) (void)cudaFree(plan->table_dev);
     if (plan->table_host) (void)cudaFreeHost(plan->table_host);
@@ -186,10 +214,12 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
   BatchArgs b;
   memset(&b, 0, sizeof(b));
   b.table = plan->table_dev;
-  int e = run_batch(plan, b, n, s);
+  int e = run_batch(plan, b, hints, n, s);
   if (e != BANDCU_OK) return e;
   CU_TRY(cudaEventRecord(plan->table_free, s), "plan_run: event record");
   plan->table_pending = true;
+  plan->table_valid_n = n;
+  plan->table_stream = s;
   return BANDCU_OK;
 }
 

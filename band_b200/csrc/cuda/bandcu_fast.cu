@@ -343,14 +343,19 @@ static int launch_fast_t(FastPlan* p, FastParams& P, bool vu, int grid, size_t s
   return (int)cudaGetLastError();
 }
 
-int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream) {
-  if (batch.table) return BANDCU_E_UNSUPPORTED;  // pointer tables take the generic kernel (rare path)
-  const uint8_t* pu = batch.first.pu;
-  const uint8_t* pv = batch.first.pv;
+int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
+                cudaStream_t stream) {
   bool vu;
-  if (pv == pu + 1) vu = false;       // NV12: U first
-  else if (pu == pv + 1) vu = true;   // NV21: V first
-  else return BANDCU_E_UNSUPPORTED;
+  if (batch.table) {
+    if (!hints.valid || !hints.semi_planar) return BANDCU_E_UNSUPPORTED;
+    vu = hints.vu;
+  } else {
+    const uint8_t* pu = batch.first.pu;
+    const uint8_t* pv = batch.first.pv;
+    if (pv == pu + 1) vu = false;       // NV12: U first
+    else if (pu == pv + 1) vu = true;   // NV21: V first
+    else return BANDCU_E_UNSUPPORTED;
+  }
   FastParams P;
   memset(&P, 0, sizeof(P));
   P.W = d.vw; P.H = d.vh;
@@ -369,10 +374,14 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, in
   P.n_items = (long long)n * P.groups_per_frame;
   P.lut = p->lut_dev;
   P.batch = batch;
-  const uint8_t* uv0 = vu ? pv : pu;
-  const bool aligned = (d.vw % 16 == 0) && (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0) &&
-                       ((reinterpret_cast<uintptr_t>(batch.first.p0) & 15) == 0) &&
-                       ((reinterpret_cast<uintptr_t>(uv0) & 15) == 0) && (n == 1 || batch.in_stride % 16 == 0);
+  bool aligned = (d.vw % 16 == 0) && (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0);
+  if (batch.table) {
+    aligned = aligned && hints.aligned16;
+  } else {
+    const uint8_t* uv0 = vu ? batch.first.pv : batch.first.pu;
+    aligned = aligned && ((reinterpret_cast<uintptr_t>(batch.first.p0) & 15) == 0) &&
+              ((reinterpret_cast<uintptr_t>(uv0) & 15) == 0) && (n == 1 || batch.in_stride % 16 == 0);
+  }
   P.use_bulk = aligned ? 1 : 0;
   const char* nb = getenv("BANDCU_FAST_NO_BULK");
   if (nb && nb[0] == '1') P.use_bulk = 0;

@@ -19,6 +19,14 @@ struct FastPlan;
 bool fast_plan_supported(const BandCuPlanDesc& d);
 int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out);
 void fast_plan_destroy(FastPlan* p);
-// returns BANDCU_E_UNSUPPORTED if this particular batch (alignment) cannot use it
-int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream);
+// What the host knows about a pointer-table batch (the table itself lives in device memory).
+struct TableHints {
+  bool valid = false;    // false: strided batch, derive everything from BatchArgs::first
+  bool semi_planar = false;  // every frame has |pu - pv| == 1 with the same order
+  bool vu = false;       // V first (NV21)
+  bool aligned16 = false;  // every luma / chroma base pointer is 16-byte aligned
+};
+// returns BANDCU_E_UNSUPPORTED if this particular batch (layout) cannot use it
+int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
+                cudaStream_t stream);
 }  // namespace bandcu
