@@ -1,0 +1,139 @@
+"""GPU parity: edge cases the domain has (odd / tiny / ragged dims, saturating inputs, every YUV triple,
+dtype pairs of Normalize, status codes) and size-independent properties at BASELINE's full sizes."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from gpu_util import assert_same_bits, gpu_chain, gpu_image_chain, gpu_op, oracle_chain, rand_frames
+
+pytestmark = pytest.mark.gpu
+NORM = (5, 0, 0, 0, 0, 127.5, 127.5)
+
+
+@pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21"])
+@pytest.mark.parametrize("W,H,dw,dh", [(641, 479, 224, 224), (3, 5, 2, 3), (2, 2, 1, 1), (17, 9, 5, 4), (642, 482, 225, 223),
+                                       (1921, 1081, 300, 300)])
+def test_odd_and_tiny_yuv_frames(O, fmt_name, W, H, dw, dh):
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh), NORM]
+    fr = rand_frames(O, 2, W, H, fmt, W * 7 + H)
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, O.DT_F32, (1, dh, dw, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, dh, dw, 3))
+    assert st == 0
+    assert_same_bits(got, want, "%s %dx%d" % (fmt_name, W, H))
+
+
+@pytest.mark.parametrize("fill", [0, 255, "checker", "ramp"])
+def test_saturating_frames(O, fill):
+    W, H = 1920, 1080
+    fb = O.frame_bytes(W, H, O.FMT_NV12)
+    if fill == "checker":
+        fr = ((np.arange(fb) + (np.arange(fb) // W)) % 2 * 255).astype(np.uint8)
+    elif fill == "ramp":
+        fr = (np.arange(fb) % 256).astype(np.uint8)
+    else:
+        fr = np.full(fb, fill, dtype=np.uint8)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
+    st, want = oracle_chain(O, ops, fr, W, H, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+    st2, got = gpu_chain(ops, fr, W, H, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, str(fill))
+
+
+def test_every_yuv_triple(O):
+    """All 2^24 (Y,U,V) triples once: a 4096x4096 frame whose 2x2 blocks share one (U,V) and sweep Y
+    through ColorSpaceConvert(kRGB) alone (planar YV21 so U and V are free planes)."""
+    W = H = 8192
+    yy = np.arange(256, dtype=np.uint8)
+    # chroma plane 4096x4096: block (i,j) -> U = i % 256, V = j % 256 ; luma cycles so every Y meets every (U,V)
+    u = (np.arange(4096) % 256).astype(np.uint8)[:, None].repeat(4096, 1)
+    v = (np.arange(4096) % 256).astype(np.uint8)[None, :].repeat(4096, 0)
+    ci = (np.arange(4096) // 256)[:, None] * 16 + (np.arange(4096) // 256)[None, :]  # 0..255: the Y of this block
+    y = yy[ci].repeat(2, 0).repeat(2, 1)
+    frame = np.concatenate([y.reshape(-1), u.reshape(-1), v.reshape(-1)])
+    ops = [(O.OP_CSC, O.FMT_RGB)]
+    st, want, _ = O.run_op(ops[0], frame, W, H, O.FMT_YV21)
+    assert st == 0
+    st, got, info = gpu_op(ops[0], frame, W, H, O.FMT_YV21, cap=W * H * 3)
+    assert st == 0 and info[:3] == (W, H, O.FMT_RGB)
+    assert_same_bits(got, want, "all YUV triples")
+
+
+@pytest.mark.parametrize("out_dt", [1, 2, 3, 7, 9])
+def test_normalize_dtype_pairs(O, out_dt):
+    """common_operator.cc:42-65: u8 RGB -> every supported output element type (values kept in range so the
+    cast of the difference is defined for unsigned outputs)."""
+    W, H = 37, 23
+    rng = np.random.default_rng(out_dt)
+    fr = rng.integers(100, 200, size=W * H * 3, dtype=np.uint8)
+    ops = [(O.OP_NORMALIZE, 0, 0, 0, 0, 64.0, 2.0)]
+    st, want = oracle_chain(O, ops, fr, W, H, O.FMT_RGB, out_dt, (1, H, W, 3))
+    st2, got = gpu_chain(ops, fr, W, H, O.FMT_RGB, out_dt, (1, H, W, 3))
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, "normalize -> %d" % out_dt)
+
+
+def test_data_type_convert_u8_to_f32(O):
+    ops = [(O.OP_DTC,)]
+    fr = rand_frames(O, 1, 64, 48, O.FMT_RGB, 9)
+    st, want = oracle_chain(O, ops, fr, 64, 48, O.FMT_RGB, O.DT_F32, (1, 48, 64, 3))
+    st2, got = gpu_chain(ops, fr, 64, 48, O.FMT_RGB, O.DT_F32, (1, 48, 64, 3))
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, "DataTypeConvert")
+
+
+@pytest.mark.parametrize("ops", [
+    [(1, 64, 48)],                                   # Resize to identical dims (image_operator.cc:180-184)
+    [(5, 0, 0, 0, 0, 127.5, 127.5)],                 # Normalize on YUV input (common_operator.cc:111-117)
+    [(7,)],                                          # AutoConvert rejects YUV (image_operator.cc:493-501)
+    [(0, 0, 0, 64, 10)],                             # Crop x1 == W out of bounds
+])
+def test_error_statuses_match_oracle(O, ops):
+    fr = rand_frames(O, 1, 64, 48, O.FMT_NV12, 3)
+    fmt = O.FMT_NV12
+    odims = (1, 48, 64, 3)
+    st, _ = O.run_chain(ops, fr[0], 64, 48, fmt, O.DT_U8, odims)
+    assert st != 0
+    st2, out = gpu_chain(ops, fr, 64, 48, fmt, O.DT_U8, odims)
+    assert st2 != 0 and out is None
+
+
+@pytest.mark.parametrize("angle", [0, 90, 180, 270, -90, 450])
+@pytest.mark.parametrize("fmt_name,W,H", [("GRAY", 33, 21), ("RGB", 33, 21), ("RGBA", 20, 31), ("YV12", 35, 21), ("NV12", 34, 22),
+                                          ("NV21", 33, 23)])
+def test_rotate_all_formats(O, angle, fmt_name, W, H):
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, 77)[0]
+    st, want, winfo = O.run_op((O.OP_ROTATE, angle), fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_ROTATE, angle), fr, W, H, fmt)
+    assert st == st2
+    if st == 0:
+        assert info[:3] == tuple(winfo)
+        assert_same_bits(got, want, "rotate %d %s" % (angle, fmt_name))
+
+
+@pytest.mark.parametrize("fmt_name,W,H,box", [("GRAY", 33, 21, (3, 2, 20, 11)), ("RGB", 33, 21, (1, 1, 31, 19)),
+                                              ("RGBA", 20, 31, (5, 7, 9, 30)), ("YV12", 36, 22, (3, 5, 30, 20)),
+                                              ("NV12", 36, 22, (4, 2, 33, 19)), ("NV21", 37, 23, (1, 1, 36, 22))])
+def test_crop_all_formats(O, fmt_name, W, H, box):
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, 78)[0]
+    st, want, winfo = O.run_op((O.OP_CROP,) + box, fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_CROP,) + box, fr, W, H, fmt)
+    assert st == 0 and st2 == 0 and info[:3] == tuple(winfo)
+    assert_same_bits(got, want, "crop %s" % fmt_name)
+
+
+@pytest.mark.parametrize("hv", [(1, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize("fmt_name,W,H", [("GRAY", 33, 21), ("RGB", 33, 21), ("RGBA", 20, 31), ("YV12", 36, 22), ("NV12", 36, 22)])
+def test_flip_all_formats(O, hv, fmt_name, W, H):
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, 79)[0]
+    st, want, winfo = O.run_op((O.OP_FLIP,) + hv, fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_FLIP,) + hv, fr, W, H, fmt)
+    assert st == st2
+    if st == 0:
+        assert info[:3] == tuple(winfo)
+        assert_same_bits(got, want, "flip %s %s" % (hv, fmt_name))

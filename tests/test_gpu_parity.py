@@ -1,0 +1,204 @@
+"""GPU parity tests proper: the CUDA path (through the Band C API / C-ABI) against the CPU oracle on the
+same seeded inputs. Integer stages: bit-exact. Float Normalize: BASELINE.json allows 1e-6 relative;
+the kernels reproduce the IEEE result, so the tests demand identical bits (0 ulp <= 1e-6)."""
+import hashlib
+import importlib.util
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from gpu_util import (assert_same_bits, gpu_chain, gpu_image_chain, gpu_op, oracle_chain, rand_frames)
+
+pytestmark = pytest.mark.gpu
+
+NORM = (5, 0, 0, 0, 0, 127.5, 127.5)
+
+
+def _csc(O, fmt):
+    return (O.OP_CSC, fmt)
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE.json configs at their full sizes, a few frames each
+# ---------------------------------------------------------------------------------------------------
+def test_c1_nv21_640x480_to_224_f32(O):
+    ops = [_csc(O, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
+    fr = rand_frames(O, 1, 640, 480, O.FMT_NV21, 1)
+    st, want = oracle_chain(O, ops, fr, 640, 480, O.FMT_NV21, O.DT_F32, (1, 224, 224, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, 640, 480, O.FMT_NV21, O.DT_F32, (1, 224, 224, 3))
+    assert st == 0
+    assert_same_bits(got, want, "C1")
+    # BASELINE tolerance statement (redundant with the bit check, kept explicit)
+    assert np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-30)) <= 1e-6
+
+
+@pytest.mark.parametrize("resident", [False, True])
+def test_north_star_nv12_1080p_to_224_f32(O, resident):
+    ops = [_csc(O, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
+    fr = rand_frames(O, 5, 1920, 1080, O.FMT_NV12, 2)
+    st, want = oracle_chain(O, ops, fr, 1920, 1080, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, 1920, 1080, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3), device_resident=resident)
+    assert st == 0
+    assert_same_bits(got, want, "north star resident=%s" % resident)
+
+
+@pytest.mark.parametrize("resident", [False, True])
+def test_c2_nv12_1080p_to_300_u8(O, resident):
+    ops = [_csc(O, O.FMT_RGB), (O.OP_RESIZE, 300, 300)]
+    fr = rand_frames(O, 4, 1920, 1080, O.FMT_NV12, 3)
+    st, want = oracle_chain(O, ops, fr, 1920, 1080, O.FMT_NV12, O.DT_U8, (1, 300, 300, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, 1920, 1080, O.FMT_NV12, O.DT_U8, (1, 300, 300, 3), device_resident=resident)
+    assert st == 0
+    assert_same_bits(got, want, "C2")
+
+
+def test_c3_yv12_4k_rotate_crop_to_512_f32(O):
+    ops = [(O.OP_ROTATE, 90), (O.OP_CROP, 0, 840, 2159, 2999), _csc(O, O.FMT_RGB), (O.OP_RESIZE, 512, 512), NORM]
+    fr = rand_frames(O, 2, 3840, 2160, O.FMT_YV12, 4)
+    st, want = oracle_chain(O, ops, fr, 3840, 2160, O.FMT_YV12, O.DT_F32, (1, 512, 512, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, 3840, 2160, O.FMT_YV12, O.DT_F32, (1, 512, 512, 3), device_resident=True)
+    assert st == 0
+    assert_same_bits(got, want, "C3")
+
+
+@pytest.mark.parametrize("target", [(224, 1), (300, 3), (513, 1)])
+def test_c4_nv21_1080p_mixed_targets(O, target):
+    d, dt = target
+    ops = [_csc(O, O.FMT_RGB), (O.OP_RESIZE, d, d)] + ([NORM] if dt == 1 else [])
+    fr = rand_frames(O, 3, 1920, 1080, O.FMT_NV21, 5 + d)
+    st, want = oracle_chain(O, ops, fr, 1920, 1080, O.FMT_NV21, dt, (1, d, d, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, 1920, 1080, O.FMT_NV21, dt, (1, d, d, 3), device_resident=True)
+    assert st == 0
+    assert_same_bits(got, want, "C4 %d" % d)
+
+
+@pytest.mark.parametrize("s,d", [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (64, 128),
+                                 (64, 256), (64, 512), (64, 1024), (64, 2048), (640, 224), (225, 224)])
+def test_c5_rgba_to_rgb_autoconvert(O, s, d):
+    """C5 (i): default AutoConvert into a u8 RGB tensor = CSC(drop alpha) -> ResizeRgb, incl. the
+    Down2 / DownEven box, point-sample and bilinear-up dispatch cases."""
+    ops = [(O.OP_AUTO,)]
+    fr = rand_frames(O, 1, s, s, O.FMT_RGBA, 100 + d)
+    st, want = oracle_chain(O, ops, fr, s, s, O.FMT_RGBA, O.DT_U8, (1, d, d, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, s, s, O.FMT_RGBA, O.DT_U8, (1, d, d, 3))
+    assert st == 0
+    assert_same_bits(got, want, "C5 rgb %d->%d" % (s, d))
+
+
+@pytest.mark.parametrize("s,d", [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (2048, 1536),
+                                 (2048, 768), (64, 128), (64, 256), (64, 100), (64, 2048), (640, 224)])
+def test_c5_rgba_to_gray_resize(O, s, d):
+    """C5 (ii): CSC(Gray) -> Resize through ScalePlane (x86 rounding blender, Down2/Down34/Down38/Up2 cases)."""
+    ops = [_csc(O, O.FMT_GRAY), (O.OP_RESIZE, d, d)]
+    fr = rand_frames(O, 1, s, s, O.FMT_RGBA, 200 + d)[0]
+    cur, w, h, f = fr, s, s, O.FMT_RGBA
+    for op in ops:
+        st, cur, (w, h, f) = O.run_op(op, cur, w, h, f)
+        assert st == 0
+    st, got, info = gpu_image_chain(ops, fr, s, s, O.FMT_RGBA, O.FMT_GRAY, O.DT_U8, d, d)
+    assert st == 0 and info[:3] == (d, d, O.FMT_GRAY)
+    assert_same_bits(got, cur, "C5 gray %d->%d" % (s, d))
+
+
+# ---------------------------------------------------------------------------------------------------
+# committed golden fixtures
+# ---------------------------------------------------------------------------------------------------
+def _make_golden():
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(GOLDEN, "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    return mg
+
+
+def test_frozen_digests_on_gpu(O):
+    """Every case of tests/golden/oracle_frozen.json, computed by the CUDA path, hashes to the frozen digest."""
+    mg = _make_golden()
+    with open(os.path.join(GOLDEN, "oracle_frozen.json")) as f:
+        frozen = json.load(f)
+    for name, ops, W, H, fmt, odt, odims, seed in mg.frozen_cases():
+        rng = np.random.default_rng(seed)
+        frame = rng.integers(0, 256, size=O.frame_bytes(W, H, fmt), dtype=np.uint8)
+        if len(odims) == 2:
+            st, got, _ = gpu_image_chain(ops, frame, W, H, fmt, O.FMT_GRAY, O.DT_U8, odims[1], odims[0])
+        else:
+            st, got = gpu_chain(ops, frame, W, H, fmt, odt, odims)
+            got = got[0] if st == 0 else None
+        assert st == 0, name
+        assert hashlib.sha256(np.ascontiguousarray(got).tobytes()).hexdigest() == frozen[name], name
+
+
+def test_reference_crop_kat(O):
+    """image_operation_test.cc:12-29 on the GPU backing."""
+    st, out, info = gpu_op((O.OP_CROP, 0, 0, 1, 1), np.arange(1, 10, dtype=np.uint8), 3, 3, O.FMT_GRAY)
+    assert st == 0 and info[:3] == (2, 2, O.FMT_GRAY)
+    assert out.tolist() == [1, 2, 4, 5]
+
+
+def test_reference_crop_hippo(O, hippo):
+    """image_operation_test.cc:31-44."""
+    src = hippo["hippo"]
+    H, W = src.shape[:2]
+    st, out, info = gpu_op((O.OP_CROP, 0, 0, 255, 255), src.reshape(-1), W, H, O.FMT_RGB)
+    assert st == 0 and info[:2] == (256, 256)
+    assert np.array_equal(out.reshape(256, 256, 3), hippo["crop_256"])
+
+
+@pytest.mark.parametrize("box", [(0, 0, 600, 400), (255, 0, 0, 255), (0, 255, 255, 0), (-1, -1, 256, 256),
+                                 (0, 0, -1, -1), (-1, -1, -1, -1)])
+def test_reference_crop_failures(O, hippo, box):
+    """image_operation_test.cc:46-75: kInvalidArgument (3)."""
+    src = hippo["hippo"]
+    H, W = src.shape[:2]
+    st, _, _ = gpu_op((O.OP_CROP,) + box, src.reshape(-1), W, H, O.FMT_RGB)
+    assert st == O.INVALID_ARGUMENT
+
+
+@pytest.mark.parametrize("assigned", [True, False])
+def test_reference_convert_gray(O, hippo, assigned):
+    """image_operation_test.cc:77-119 (assigned output / auto-created output)."""
+    src = hippo["hippo"]
+    H, W = src.shape[:2]
+    if assigned:
+        st, out, info = gpu_op((O.OP_CSC, -1), src.reshape(-1), W, H, O.FMT_RGB, assign=(O.FMT_GRAY, O.DT_U8, W, H))
+    else:
+        st, out, info = gpu_op((O.OP_CSC, O.FMT_GRAY), src.reshape(-1), W, H, O.FMT_RGB)
+    assert st == 0 and info[:3] == (W, H, O.FMT_GRAY)
+    want = 0.299 * src[..., 0] + 0.587 * src[..., 1] + 0.114 * src[..., 2]
+    assert np.abs(out.reshape(H, W).astype(np.float64) - want).max() <= 1.0
+    st, ref, _ = O.run_op((O.OP_CSC, O.FMT_GRAY), src.reshape(-1), W, H, O.FMT_RGB)
+    assert_same_bits(out, ref, "gray")
+
+
+def test_reference_rotate_round_trip(O, hippo):
+    """image_operation_test.cc:121-141."""
+    src = hippo["hippo"]
+    H, W = src.shape[:2]
+    st, r90, info = gpu_op((O.OP_ROTATE, 90), src.reshape(-1), W, H, O.FMT_RGB)
+    assert st == 0 and info[:2] == (H, W)
+    assert np.array_equal(r90.reshape(W, H, 3), np.rot90(src, 1))
+    st, back, info2 = gpu_op((O.OP_ROTATE, 270), r90, H, W, O.FMT_RGB)
+    assert st == 0 and info2[:2] == (W, H)
+    assert np.array_equal(back.reshape(H, W, 3), src)
+
+
+def test_reference_resize_hippo(O, hippo):
+    """image_operation_test.cc:143-159 (+-3 on the bytes it compares) and bit-exact vs the oracle."""
+    src = hippo["hippo"]
+    H, W = src.shape[:2]
+    st, out, info = gpu_op((O.OP_RESIZE, 256, 256), src.reshape(-1), W, H, O.FMT_RGB)
+    assert st == 0 and info[:2] == (256, 256)
+    want = hippo["resize_256"].reshape(-1).astype(np.int32)
+    n = 256 * 256
+    assert np.abs(out[:n].astype(np.int32) - want[:n]).max() <= 3
+    assert np.abs(out.astype(np.int32) - want).mean() < 0.25
+    st, ref, _ = O.run_op((O.OP_RESIZE, 256, 256), src.reshape(-1), W, H, O.FMT_RGB)
+    assert_same_bits(out, ref, "hippo resize")
