@@ -36,7 +36,8 @@ EXPORTED = [
     "BandAddOperator", "BandImageProcessorProcess", "BandImageProcessorDelete",
     # additive
     "BandTensorCreate", "BandTensorGetMemorySpace", "BandBufferSetFromDeviceRawData",
-    "BandBufferSetFromDeviceYUVData", "BandImageProcessorProcessBatch", "BandImageProcessorIsFused",
+    "BandBufferSetFromDeviceYUVData", "BandImageProcessorProcessBatch", "BandImageProcessorProcessBatchAsync",
+    "BandImageProcessorSynchronize", "BandImageProcessorGetStream", "BandImageProcessorIsFused",
     "BandCudaGetDeviceCount", "BandCudaSetDevice", "BandHostAlloc", "BandHostFree", "BandDeviceAlloc",
     "BandDeviceFree", "BandCopyToDevice", "BandCopyToHost", "BandCudaLaunchCount", "BandGetLastError",
 ]
@@ -89,6 +90,10 @@ def lib():
     L.BandBufferSetFromDeviceRawData.argtypes = [vp, vp, sz, sz, ci]
     L.BandBufferSetFromDeviceYUVData.argtypes = [vp, vp, vp, vp, sz, sz, sz, sz, sz, ci]
     L.BandImageProcessorProcessBatch.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
+    L.BandImageProcessorProcessBatchAsync.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
+    L.BandImageProcessorSynchronize.argtypes = [vp]
+    L.BandImageProcessorGetStream.argtypes = [vp]
+    L.BandImageProcessorGetStream.restype = vp
     L.BandImageProcessorIsFused.argtypes = [vp]
     L.BandCudaSetDevice.argtypes = [ci]
     L.BandHostAlloc.argtypes = [sz]
@@ -234,6 +239,16 @@ class ImageProcessor:
     def process_batch_handles(self, buffer_array, tensor_array, n):
         """Same call with pre-built ctypes arrays (keeps Python overhead out of timed loops)."""
         return lib().BandImageProcessorProcessBatch(self.handle, buffer_array, tensor_array, n)
+
+    def process_batch_async(self, buffer_array, tensor_array, n):
+        return lib().BandImageProcessorProcessBatchAsync(self.handle, buffer_array, tensor_array, n)
+
+    def synchronize(self):
+        return lib().BandImageProcessorSynchronize(self.handle)
+
+    @property
+    def stream(self):
+        return lib().BandImageProcessorGetStream(self.handle)
 
     @property
     def is_fused(self):

@@ -80,6 +80,19 @@ absl::Status BufferProcessor::ProcessBatch(const Buffer* const* inputs, Buffer* 
   return status;
 }
 
+absl::Status BufferProcessor::ProcessBatchAsync(const Buffer* const* inputs, Buffer* const* outputs, size_t n) {
+  if (n == 0) return absl::OkStatus();
+  if (inputs == nullptr || outputs == nullptr || inputs[0] == nullptr || outputs[0] == nullptr)
+    return absl::InvalidArgumentError("ProcessBatchAsync: null buffer list");
+  RETURN_IF_ERROR(Prepare(*inputs[0], *outputs[0]));
+  absl::Status status = plan_->Run(inputs, outputs, static_cast<int>(n), /*synchronize=*/false);
+  if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::ProcessBatchAsync failed %s", status.ToString().c_str());
+  return status;
+}
+
+absl::Status BufferProcessor::Synchronize() { return plan_ ? plan_->Synchronize() : absl::OkStatus(); }
+void* BufferProcessor::GetComputeStream() const { return plan_ ? plan_->ComputeStream() : nullptr; }
+
 size_t BufferProcessor::GetNumLaunchSegments() const { return plan_ ? plan_->NumSegments() : 0; }
 bool BufferProcessor::IsSingleFastLaunch() const { return plan_ && plan_->IsSingleFastLaunch(); }
 

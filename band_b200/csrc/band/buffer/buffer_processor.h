@@ -51,6 +51,11 @@ class BufferProcessor {
   // Additive: n frames sharing one layout, each written to its own output.
   // Frames may be host or device memory; returns after all results are in place.
   virtual absl::Status ProcessBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n);
+  // Additive: enqueue only; results are complete after Synchronize(). The buffers must stay alive until then.
+  virtual absl::Status ProcessBatchAsync(const Buffer* const* inputs, Buffer* const* outputs, size_t n);
+  absl::Status Synchronize();
+  // CUDA stream the fused launches go to (nullptr before the first Process*); for event timing.
+  void* GetComputeStream() const;
   // Additive introspection for tests / benchmarks.
   size_t GetNumLaunchSegments() const;
   bool IsSingleFastLaunch() const;

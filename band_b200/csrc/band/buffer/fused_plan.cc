@@ -566,6 +566,18 @@ FusedPlan::~FusedPlan() {
     if (st) bandcu_stream_destroy(st);
   for (void* ev : events_)
     if (ev) bandcu_event_destroy(ev);
+  if (fence_a_) bandcu_event_destroy(fence_a_);
+  if (fence_b_) bandcu_event_destroy(fence_b_);
+}
+
+void* FusedPlan::ComputeStream() { return EnsureStreams().ok() ? stream_ : nullptr; }
+
+absl::Status FusedPlan::Synchronize() {
+  if (!stream_) return absl::OkStatus();
+  if (bandcu_stream_sync(stream_) != BANDCU_OK) return CudaError("stream sync");
+  if (bandcu_stream_sync(copy_out_) != BANDCU_OK) return CudaError("stream sync");
+  in_flight_ = false;
+  return absl::OkStatus();
 }
 
 bool FusedPlan::IsSingleFastLaunch() const {
@@ -692,7 +704,7 @@ constexpr int kMaxPassFrames = 2048;
 }  // namespace
 
 absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host,
-                                bool out_host) {
+                                bool out_host, bool synchronize) {
   std::vector<HostRanges> in_r, out_r;
   size_t in_step = 0, out_step = 0;
   bool in_uniform = false, out_uniform = false;
@@ -726,6 +738,15 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   const bool staged = in_host || download;
   const int chunk = staged ? kChunkFrames : m;
   size_t ev = 0;
+  if (staged && in_flight_) {
+    // an earlier asynchronous pass may still use the staging areas: its kernels read in_stage_, its
+    // downloads read out_stage_
+    if (!fence_a_ && bandcu_event_create_sync(&fence_a_) != BANDCU_OK) return CudaError("fence event");
+    if (!fence_b_ && bandcu_event_create_sync(&fence_b_) != BANDCU_OK) return CudaError("fence event");
+    if (bandcu_event_record(fence_a_, stream_) != BANDCU_OK || bandcu_stream_wait_event(copy_in_, fence_a_) != BANDCU_OK ||
+        bandcu_event_record(fence_b_, copy_out_) != BANDCU_OK || bandcu_stream_wait_event(stream_, fence_b_) != BANDCU_OK)
+      return CudaError("fence");
+  }
   for (int a = 0; a < m; a += chunk) {
     const int b = std::min(m, a + chunk);
     if (in_host) {
@@ -783,12 +804,15 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
       }
     }
   }
+  in_flight_ = true;
+  if (!synchronize) return absl::OkStatus();
   if (bandcu_stream_sync(stream_) != BANDCU_OK) return CudaError("stream sync");
   if (download && bandcu_stream_sync(copy_out_) != BANDCU_OK) return CudaError("stream sync");
+  in_flight_ = false;
   return absl::OkStatus();
 }
 
-absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs, int n) {
+absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs, int n, bool synchronize) {
   if (n <= 0) return absl::OkStatus();
   if (inputs == nullptr || (writes_output_ && outputs == nullptr)) return absl::InvalidArgumentError("null frame list");
   const MemorySpace in_space = inputs[0] ? inputs[0]->GetMemorySpace() : MemorySpace::kHost;
@@ -808,7 +832,7 @@ absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs,
   for (int base = 0; base < n; base += kMaxPassFrames) {
     const int m = std::min(kMaxPassFrames, n - base);
     RETURN_IF_ERROR(RunPass(inputs + base, writes_output_ ? outputs + base : nullptr, m,
-                            in_space == MemorySpace::kHost, out_space == MemorySpace::kHost));
+                            in_space == MemorySpace::kHost, out_space == MemorySpace::kHost, synchronize));
   }
   return absl::OkStatus();
 }

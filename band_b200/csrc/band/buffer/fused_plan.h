@@ -72,7 +72,11 @@ class FusedPlan {
   // Runs n frames. inputs/outputs may live in host or device memory (all frames
   // of a call in the same space); host frames are staged through plan-owned
   // device memory. Synchronous: returns after the stream has drained.
-  absl::Status Run(const Buffer* const* inputs, Buffer* const* outputs, int n);
+  absl::Status Run(const Buffer* const* inputs, Buffer* const* outputs, int n, bool synchronize = true);
+  // Waits for everything a Run(..., false) enqueued (compute and copy-out streams).
+  absl::Status Synchronize();
+  // The stream the kernels are launched on (created on first use); for CUDA-event timing by harnesses.
+  void* ComputeStream();
   size_t NumSegments() const { return segments_.size(); }
   bool IsSingleFastLaunch() const;
   const ImageLayout& input_layout() const { return input_; }
@@ -85,7 +89,8 @@ class FusedPlan {
   FusedPlan(const FusedPlan&) = delete;
   absl::Status EnsureStreams();
   absl::Status EnsureCapacity(int frames, size_t in_bytes, size_t out_bytes);
-  absl::Status RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host, bool out_host);
+  absl::Status RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host, bool out_host,
+                       bool synchronize);
   absl::Status RunSegments(int first, int last);
   SlotPointers Resolve(int slot, int frame) const;
   void* Event(size_t index);
@@ -112,6 +117,9 @@ class FusedPlan {
   void* copy_in_ = nullptr;
   void* copy_out_ = nullptr;
   std::vector<void*> events_;
+  void* fence_a_ = nullptr;  // orders a new pass's uploads after the previous pass's kernels
+  void* fence_b_ = nullptr;  // orders a new pass's kernels after the previous pass's downloads
+  bool in_flight_ = false;   // an unsynchronised pass may still be running
 };
 
 // Walks an operator chain and emits segments. Operators call the stage

@@ -170,28 +170,51 @@ BandStatus BandImageProcessorProcess(BandImageProcessor* image_processor, BandBu
   return status.ok() ? kBandOk : kBandErr;
 }
 
-BandStatus BandImageProcessorProcessBatch(BandImageProcessor* image_processor, BandBuffer* const* buffers,
-                                          BandTensor* const* target_tensors, size_t count) {
+static BandStatus ProcessBatchImpl(BandImageProcessor* image_processor, BandBuffer* const* buffers,
+                                   BandTensor* const* target_tensors, size_t count, bool async) {
   if (!image_processor || !buffers || !target_tensors) {
     BAND_LOG(LogSeverity::kError, "BandImageProcessorProcessBatch: null argument");
     return kBandErr;
   }
-  std::vector<const Buffer*> in(count);
-  std::vector<std::unique_ptr<Buffer>> views(count);
-  std::vector<Buffer*> out(count);
+  // per-thread scratch: a harness calls this in a loop with thousands of frames
+  thread_local std::vector<const Buffer*> in;
+  thread_local std::vector<Buffer*> out;
+  in.resize(count);
+  out.resize(count);
   for (size_t i = 0; i < count; ++i) {
     if (!buffers[i] || !buffers[i]->impl || !target_tensors[i]) {
       BAND_LOG(LogSeverity::kError, "BandImageProcessorProcessBatch: entry %d is null", static_cast<int>(i));
       return kBandErr;
     }
     in[i] = buffers[i]->impl.get();
-    views[i].reset(Buffer::CreateFromTensor(target_tensors[i]->impl.get()));
-    if (!views[i]) return kBandErr;
-    out[i] = views[i].get();
+    out[i] = target_tensors[i]->View();
+    if (!out[i]) return kBandErr;
   }
-  absl::Status status = image_processor->impl->ProcessBatch(in.data(), out.data(), count);
+  absl::Status status = async ? image_processor->impl->ProcessBatchAsync(in.data(), out.data(), count)
+                              : image_processor->impl->ProcessBatch(in.data(), out.data(), count);
   if (!status.ok()) g_last_error = status.ToString();
   return status.ok() ? kBandOk : kBandErr;
+}
+
+BandStatus BandImageProcessorProcessBatch(BandImageProcessor* image_processor, BandBuffer* const* buffers,
+                                          BandTensor* const* target_tensors, size_t count) {
+  return ProcessBatchImpl(image_processor, buffers, target_tensors, count, false);
+}
+
+BandStatus BandImageProcessorProcessBatchAsync(BandImageProcessor* image_processor, BandBuffer* const* buffers,
+                                               BandTensor* const* target_tensors, size_t count) {
+  return ProcessBatchImpl(image_processor, buffers, target_tensors, count, true);
+}
+
+BandStatus BandImageProcessorSynchronize(BandImageProcessor* image_processor) {
+  if (!image_processor) return kBandErr;
+  absl::Status status = image_processor->impl->Synchronize();
+  if (!status.ok()) g_last_error = status.ToString();
+  return status.ok() ? kBandOk : kBandErr;
+}
+
+void* BandImageProcessorGetStream(BandImageProcessor* image_processor) {
+  return image_processor ? image_processor->impl->GetComputeStream() : nullptr;
 }
 
 int BandImageProcessorIsFused(BandImageProcessor* image_processor) {

@@ -13,6 +13,13 @@
 struct BandTensor {
   explicit BandTensor(std::unique_ptr<band::Tensor> tensor) : impl(std::move(tensor)) {}
   std::unique_ptr<band::Tensor> impl;
+  // Buffer view over the tensor memory (Buffer::CreateFromTensor), built on first use: a C-API tensor's
+  // type and dims never change after creation, so batch calls do not rebuild it per frame.
+  std::unique_ptr<band::Buffer> view;
+  band::Buffer* View() {
+    if (!view) view.reset(band::Buffer::CreateFromTensor(impl.get()));
+    return view.get();
+  }
 };
 
 struct BandBuffer {

@@ -145,6 +145,16 @@ BAND_CAPI_EXPORT extern BandStatus BandBufferSetFromDeviceYUVData(BandBuffer* bu
 BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatch(BandImageProcessor* image_processor,
                                                                   BandBuffer* const* buffers,
                                                                   BandTensor* const* target_tensors, size_t count);
+/* Enqueue only: results are complete after BandImageProcessorSynchronize. Buffers and tensors must stay alive
+ * (and host memory untouched) until then. */
+BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatchAsync(BandImageProcessor* image_processor,
+                                                                       BandBuffer* const* buffers,
+                                                                       BandTensor* const* target_tensors,
+                                                                       size_t count);
+BAND_CAPI_EXPORT extern BandStatus BandImageProcessorSynchronize(BandImageProcessor* image_processor);
+/* cudaStream_t the processor launches on (NULL before its first Process*); lets a harness bracket the
+ * launches with CUDA events. */
+BAND_CAPI_EXPORT extern void* BandImageProcessorGetStream(BandImageProcessor* image_processor);
 /* 1 when the last Process/ProcessBatch ran as a single staged fast-kernel launch per batch. */
 BAND_CAPI_EXPORT extern int BandImageProcessorIsFused(BandImageProcessor* image_processor);
 BAND_CAPI_EXPORT extern int BandCudaGetDeviceCount();
