@@ -683,7 +683,10 @@ absl::Status FusedPlan::RunSegments(int first, int last) {
 }
 
 namespace {
-// Frames whose single host range advances by a constant step can move as one copy.
+// Frames that sit exactly back to back in PAGEABLE host memory can move as one copy. Pinned memory is
+// never merged across frames: a copy must not span two cudaMallocHost allocations, and neighbouring
+// allocations cannot be told from one big one here. Frames with gaps are not merged either (the gap may
+// be unmapped).
 bool UniformStep(const std::vector<HostRanges>& r, size_t* step) {
   if (r.empty() || r[0].count != 1) return false;
   if (r.size() == 1) {
@@ -691,8 +694,8 @@ bool UniformStep(const std::vector<HostRanges>& r, size_t* step) {
     return true;
   }
   const ptrdiff_t d = r[1].lo[0] - r[0].lo[0];
-  if (d < static_cast<ptrdiff_t>(r[0].bytes[0]) || d > static_cast<ptrdiff_t>(r[0].bytes[0] + 4096) || (d & 15))
-    return false;
+  if (d != static_cast<ptrdiff_t>(r[0].bytes[0]) || (d & 15)) return false;
+  if (bandcu_pointer_kind(r[0].lo[0]) != 0 || bandcu_pointer_kind(r.back().lo[0]) != 0) return false;
   for (size_t f = 1; f < r.size(); ++f)
     if (r[f].count != 1 || r[f].bytes[0] != r[0].bytes[0] || r[f].lo[0] - r[0].lo[0] != d * static_cast<ptrdiff_t>(f))
       return false;

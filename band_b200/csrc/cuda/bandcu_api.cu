@@ -343,6 +343,16 @@ int bandcu_pointer_is_device(const void* ptr) {
   }
   return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? 1 : 0;
 }
+int bandcu_pointer_kind(const void* ptr) {
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, ptr);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return 2;
+  return a.type == cudaMemoryTypeHost ? 1 : 0;
+}
 const char* bandcu_last_error_string(void) { return g_err; }
 
 }  // extern "C"

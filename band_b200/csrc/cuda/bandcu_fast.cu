@@ -11,18 +11,26 @@
 // BASELINE config with a 4:2:0 semi-planar source. Integer results are bit
 // exact; the float stage is a 256-entry table built with IEEE sub/div.
 //
-// Design (sm_100a, HBM-bound):
-//  * persistent CTAs, one work item = R output rows of one frame;
-//  * the 2 luma rows + <=2 chroma rows each output row samples are staged into
-//    shared memory by the TMA engine (cp.async.bulk + mbarrier complete_tx),
-//    double-buffered so the next item's rows stream in while this one computes;
-//    rows the resize never samples are never read from HBM;
-//  * one thread per output column: x-dependent terms (xi, xf, chroma byte
-//    offsets) live in registers across the R rows;
-//  * SWAR arithmetic: R|B share one 32-bit lane pair for the vertical and the
-//    horizontal blend (no cross-lane carry: <= 65408 and <= 32385);
-//  * results go through a shared-memory row stage and leave as 128-bit
-//    coalesced stores (NHWC rows are 16-byte multiples for the named shapes).
+// Design (sm_100a). ncu on the first version showed the kernel is NOT limited by
+// HBM (it never reads the rows the resize skips: 2.06 MB of DRAM traffic per
+// frame against 3.71 MB algorithmic) but by instruction issue and by one block
+// barrier per work item. Hence:
+//  * persistent, warp-specialised CTAs. Warp 0 is the producer: it posts one
+//    cp.async.bulk (TMA engine) per needed source row into an S-deep ring of
+//    shared-memory stages (mbarrier complete_tx). The other warps consume:
+//    wait(full[s]) -> compute -> arrive(empty[s]). No __syncthreads in the loop;
+//    warps drift apart freely and the ring keeps HBM requests in flight;
+//  * one work item = R output rows of one frame; consumer warps are split into
+//    G row groups so one staged item feeds G*ceil(dw/32) warps;
+//  * one thread per output column: the x-dependent terms (byte offsets, packed
+//    7-bit weights) live in registers across rows;
+//  * packed 16-bit arithmetic on the LEFT|RIGHT source pixel pair: BT.601
+//    clamps as one VIADDMNMX.S16x2.RELU (DPX) per channel pair, vertical blend
+//    as two IMADs on both lanes, and the horizontal blend of a pair as ONE
+//    32-bit multiply ((L|R<<16) * (w1|w0<<16) >> 23);
+//  * results leave as direct global stores (a warp writes 384 contiguous bytes
+//    per row); L2 merges them into full sectors.
+#include <cstdlib>
 #include <cstring>
 
 #include "bandcu_device.cuh"
@@ -30,29 +38,33 @@
 
 namespace bandcu {
 
+constexpr int kMaxStages = 4;
+constexpr int kMaxRows = 16;
+
 struct FastParams {
   int W, H;            // source luma dims
   int stride0, stride_uv;
   int x0, y0, dx, dy, max_y, linear;
   int dw, dh;
   int R;               // output rows per work item
+  int G;               // consumer row groups
+  int S;               // ring depth
+  int cols;            // consumer threads per row group (multiple of 32)
+  int passes;          // column passes per row
   int row_pitch;       // bytes per staged source row slot
-  int out_row_bytes;   // dw * 3 * sizeof(OT)
+  int stage_bytes;     // R * 4 * row_pitch
   long long dst_row_stride;
   int groups_per_frame;
   long long n_items;
-  int use_bulk;        // 1: cp.async.bulk staging, 0: cooperative loads
-  int in_stage_bytes, out_stage_bytes;
-  const void* lut;     // 256 x OT (normalize) or nullptr
+  int use_bulk;        // 1: cp.async.bulk staging, 0: producer-warp byte copies
+  const void* lut;     // 256 x float (normalize) or nullptr
   BatchArgs batch;
 };
 
 struct FastPlan {
   void* lut_dev;
-  int lut_dtype;
   int num_sms;
-  int block;
-  int R;
+  int R, G, S;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -62,6 +74,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
@@ -82,7 +97,7 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                : "memory");
 }
 
-// Source rows one output row samples.
+// Source rows one output row samples (ScaleARGBBilinearDown row stepping).
 struct RowSel {
   int yi, yf;      // luma row and 8-bit vertical fraction
   int ct, cb;      // chroma rows for luma rows yi and yi+1
@@ -98,10 +113,20 @@ __device__ __forceinline__ RowSel row_select(const FastParams& P, int oy) {
   return s;
 }
 
-// Stage the source rows of one work item. Slot layout per output row j:
+// Shared-memory map: barriers | per-stage row info | Normalize table | ring of stages.
+constexpr int kOffFull = 0;                              // kMaxStages x u64
+constexpr int kOffEmpty = 8 * kMaxStages;                // kMaxStages x u64
+constexpr int kOffRowInfo = 16 * kMaxStages;             // kMaxStages x kMaxRows x u32
+constexpr int kOffLut = kOffRowInfo + 4 * kMaxStages * kMaxRows;  // 256 x f32
+constexpr int kOffStages = ((kOffLut + 1024 + 127) / 128) * 128;
+
+// Producer (warp 0): stage the source rows of one work item. Slot layout per output row j:
 //   [4j+0] luma yi   [4j+1] luma yi+1 (only if yf)   [4j+2] chroma ct   [4j+3] chroma cb (only if yf && cb != ct)
+// rowinfo[j] = yf | (bottom chroma slot: 2 or 3) << 8.
 template <bool VU>
-__device__ __forceinline__ void stage_item(const FastParams& P, long long item, uint8_t* stage, uint64_t* bar) {
+__device__ __forceinline__ void produce_item(const FastParams& P, long long item, uint8_t* stage, uint32_t* rowinfo,
+                                             uint64_t* full) {
+  const int lane = threadIdx.x;
   const int f = (int)(item / P.groups_per_frame);
   const int g = (int)(item - (long long)f * P.groups_per_frame);
   const FramePtrs fp = frame_ptrs(P.batch, f);
@@ -109,35 +134,36 @@ __device__ __forceinline__ void stage_item(const FastParams& P, long long item, 
   const int oy0 = g * P.R;
   const int nrows = min(P.R, P.dh - oy0);
   const int ybytes = P.W, cbytes = ((P.W + 1) >> 1) << 1;
+  if (lane < nrows) {
+    const RowSel s = row_select(P, oy0 + lane);
+    rowinfo[lane] = (uint32_t)s.yf | ((s.yf && s.cb != s.ct) ? (3u << 8) : (2u << 8));
+  }
+  __syncwarp();
   if (P.use_bulk) {
-    // warp 0: lane 0 posts the byte count, then lanes issue one row copy each
-    if (threadIdx.x < 32) {
-      const int lane = threadIdx.x;
-      if (lane == 0) {
-        uint32_t total = 0;
-        for (int j = 0; j < nrows; ++j) {
-          RowSel s = row_select(P, oy0 + j);
-          total += ybytes + cbytes;
-          if (s.yf) total += ybytes + (s.cb != s.ct ? cbytes : 0);
-        }
-        mbar_expect_tx(bar, total);
+    if (lane == 0) {
+      uint32_t total = 0;
+      for (int j = 0; j < nrows; ++j) {
+        const RowSel s = row_select(P, oy0 + j);
+        total += ybytes + cbytes;
+        if (s.yf) total += ybytes + (s.cb != s.ct ? cbytes : 0);
       }
-      __syncwarp();
-      for (int k = lane; k < nrows * 4; k += 32) {
-        const int j = k >> 2, slot = k & 3;
-        RowSel s = row_select(P, oy0 + j);
-        uint8_t* dst = stage + (size_t)k * P.row_pitch;
-        if (slot == 0) bulk_g2s(dst, fp.p0 + (long long)s.yi * P.stride0, ybytes, bar);
-        else if (slot == 1) { if (s.yf) bulk_g2s(dst, fp.p0 + (long long)(s.yi + 1) * P.stride0, ybytes, bar); }
-        else if (slot == 2) bulk_g2s(dst, uv + (long long)s.ct * P.stride_uv, cbytes, bar);
-        else { if (s.yf && s.cb != s.ct) bulk_g2s(dst, uv + (long long)s.cb * P.stride_uv, cbytes, bar); }
-      }
+      mbar_expect_tx(full, total);
+    }
+    __syncwarp();
+    for (int k = lane; k < nrows * 4; k += 32) {
+      const int j = k >> 2, slot = k & 3;
+      const RowSel s = row_select(P, oy0 + j);
+      uint8_t* dst = stage + (size_t)k * P.row_pitch;
+      if (slot == 0) bulk_g2s(dst, fp.p0 + (long long)s.yi * P.stride0, ybytes, full);
+      else if (slot == 1) { if (s.yf) bulk_g2s(dst, fp.p0 + (long long)(s.yi + 1) * P.stride0, ybytes, full); }
+      else if (slot == 2) bulk_g2s(dst, uv + (long long)s.ct * P.stride_uv, cbytes, full);
+      else { if (s.yf && s.cb != s.ct) bulk_g2s(dst, uv + (long long)s.cb * P.stride_uv, cbytes, full); }
     }
   } else {
-    // cooperative byte-granular staging (any alignment / odd widths)
+    // byte-granular staging by the producer warp (any alignment / odd widths)
     for (int k = 0; k < nrows * 4; ++k) {
       const int j = k >> 2, slot = k & 3;
-      RowSel s = row_select(P, oy0 + j);
+      const RowSel s = row_select(P, oy0 + j);
       const uint8_t* src;
       int nb;
       if (slot == 0) { src = fp.p0 + (long long)s.yi * P.stride0; nb = ybytes; }
@@ -145,145 +171,155 @@ __device__ __forceinline__ void stage_item(const FastParams& P, long long item, 
       else if (slot == 2) { src = uv + (long long)s.ct * P.stride_uv; nb = cbytes; }
       else { if (!s.yf || s.cb == s.ct) continue; src = uv + (long long)s.cb * P.stride_uv; nb = cbytes; }
       uint8_t* dst = stage + (size_t)k * P.row_pitch;
-      for (int i = threadIdx.x; i < nb; i += blockDim.x) dst[i] = src[i];
+      for (int i = lane; i < nb; i += 32) dst[i] = src[i];
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(full);  // release: the warp's stores above are visible to waiters
   }
 }
 
-// Copy `nbytes` from shared (same 16-byte phase as dst) to global.
-__device__ __forceinline__ void copy_out(const uint8_t* s, uint8_t* g, int nbytes) {
-  const int head = min((int)((16 - (reinterpret_cast<uintptr_t>(g) & 15)) & 15), nbytes);
-  const int mid = (nbytes - head) >> 4;
-  const int tail = nbytes - head - (mid << 4);
-  if ((int)threadIdx.x < head) g[threadIdx.x] = s[threadIdx.x];
-  const uint4* s4 = reinterpret_cast<const uint4*>(s + head);
-  uint4* g4 = reinterpret_cast<uint4*>(g + head);
-  for (int i = threadIdx.x; i < mid; i += blockDim.x) g4[i] = s4[i];
-  const int toff = head + (mid << 4);
-  if ((int)threadIdx.x < tail) g[toff + threadIdx.x] = s[toff + threadIdx.x];
+// ---- packed pixel arithmetic ---------------------------------------------------
+// One source row, the LEFT and RIGHT source pixels of an output column, as three
+// registers R2/G2/B2 = value_left | value_right << 16 (8-bit values in 16-bit lanes).
+//
+// libyuv YuvPixel (kYuvI601Constants):  yy = (Y * 0x0101 * 18997) >> 16
+//   R = clamp((yy + 102 V           - 14216) >> 6)
+//   G = clamp((yy - 25 U - 52 V     +  8696) >> 6)
+//   B = clamp((yy + 128 U           - 17544) >> 6)
+// clamp(x >> 6, 0, 255) == clamp(x, 0, 16383) >> 6. R and G sums fit signed 16 bits, so one
+// VIADDMNMX.S16x2.RELU does add + upper clamp + lower clamp for both pixels. The B sum can
+// exceed 32767, so it runs biased by +17544 in unsigned lanes.
+template <bool VU>
+__device__ __forceinline__ void yuv_pair_to_rgb(const uint8_t* __restrict__ yrow, const uint8_t* __restrict__ crow,
+                                                int xi, int cL, int cR, uint32_t& R2, uint32_t& G2, uint32_t& B2) {
+  const uint32_t pL = (uint32_t)yrow[xi] * 4882229u;
+  const uint32_t pR = (uint32_t)yrow[xi + 1] * 4882229u;
+  const uint32_t yy = __byte_perm(pL, pR, 0x7632);  // (pL >> 16) | (pR >> 16) << 16, lanes <= 18997
+  const uint32_t w = __byte_perm((uint32_t) * reinterpret_cast<const uint16_t*>(crow + cL),
+                                 (uint32_t) * reinterpret_cast<const uint16_t*>(crow + cR), 0x5410);
+  const uint32_t u2 = __byte_perm(w, 0u, VU ? 0x4341 : 0x4240);  // U_left | U_right << 16
+  const uint32_t v2 = __byte_perm(w, 0u, VU ? 0x4240 : 0x4341);
+  const uint32_t r = __viaddmin_s16x2_relu(yy, __vadd2(v2 * 102u, 0xC878C878u /* -14216 */), 0x3FFF3FFFu);
+  const uint32_t t = u2 * 25u + v2 * 52u;  // lanes <= 19635
+  const uint32_t g = __viaddmin_s16x2_relu(yy, __vadd2(~t, 0x21F921F9u /* 8696 + 1 */), 0x3FFF3FFFu);
+  uint32_t b = __vmaxu2(__viaddmin_u16x2(yy, u2 << 7, 0x84878487u /* 17544 + 16383 */), 0x44884488u /* 17544 */);
+  b = __vadd2(b, 0xBB78BB78u /* -17544 */);
+  R2 = (r >> 6) & 0x00FF00FFu;
+  G2 = (g >> 6) & 0x00FF00FFu;
+  B2 = (b >> 6) & 0x00FF00FFu;
 }
+// InterpolateRow_C on both lanes: (top*(256-f) + bottom*f + 128) >> 8; f == 0 keeps top whatever bottom holds.
+__device__ __forceinline__ uint32_t vblend2(uint32_t top, uint32_t bot, uint32_t w0, uint32_t w1) {
+  return ((top * w0 + bot * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
+}
+// ScaleARGBFilterCols_C on a packed pair: (L*(0x7f^xf) + R*xf) >> 7, truncating. wp = xf | (0x7f^xf) << 16, so
+// (L | R<<16) * wp = L*xf + (L*(0x7f^xf) + R*xf) << 16 (+ a term beyond bit 31); L*xf < 65536 never carries.
+__device__ __forceinline__ uint32_t hblend_pair(uint32_t v2, uint32_t wp) { return (v2 * wp) >> 23; }
 
 template <typename OT, bool VU>
-__global__ void __launch_bounds__(512) fast_nv_bilinear_down_kernel(const __grid_constant__ FastParams P) {
+__global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(128) uint8_t smem[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);            // 2 barriers
-  OT* lut = reinterpret_cast<OT*>(smem + 16);                     // 256 entries (<= 1024 B)
-  uint8_t* in_stage0 = smem + 16 + 1024;
-  uint8_t* out_stage0 = in_stage0 + 2 * (size_t)P.in_stage_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kOffFull);
+  uint64_t* empty = reinterpret_cast<uint64_t*>(smem + kOffEmpty);
+  uint32_t* rowinfo = reinterpret_cast<uint32_t*>(smem + kOffRowInfo);
+  float* lut = reinterpret_cast<float*>(smem + kOffLut);
+  uint8_t* stages = smem + kOffStages;
+  const int consumer_warps = (P.G * P.cols) >> 5;
 
   if (threadIdx.x == 0) {
-    mbar_init(&bars[0], 1);
-    mbar_init(&bars[1], 1);
+    for (int s = 0; s < P.S; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], consumer_warps);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (P.lut) {
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = reinterpret_cast<const OT*>(P.lut)[i];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = reinterpret_cast<const float*>(P.lut)[i];
   }
   __syncthreads();
 
-  uint32_t phase0 = 0, phase1 = 0;
-  long long item = blockIdx.x;
-  if (item < P.n_items) stage_item<VU>(P, item, in_stage0, &bars[0]);
-
-  for (int it = 0; item < P.n_items; item += gridDim.x, ++it) {
-    const int st = it & 1;
-    uint8_t* in_stage = in_stage0 + (size_t)st * P.in_stage_bytes;
-    uint8_t* out_stage = out_stage0 + (size_t)st * P.out_stage_bytes;
-    const long long next = item + gridDim.x;
-    if (next < P.n_items)
-      stage_item<VU>(P, next, in_stage0 + (size_t)(st ^ 1) * P.in_stage_bytes, &bars[st ^ 1]);
-    if (P.use_bulk) {
-      if (st == 0) { mbar_wait(&bars[0], phase0); phase0 ^= 1; }
-      else { mbar_wait(&bars[1], phase1); phase1 ^= 1; }
-    } else {
-      __syncthreads();
+  if (threadIdx.x < 32) {
+    // ---------------- producer warp ----------------
+    int s = 0;
+    uint32_t wrap = 0;  // how many times the ring has wrapped
+    for (long long item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+      if (wrap) mbar_wait(&empty[s], (wrap - 1) & 1);  // consumers released the previous use of this stage
+      produce_item<VU>(P, item, stages + (size_t)s * P.stage_bytes, rowinfo + s * kMaxRows, &full[s]);
+      if (++s == P.S) { s = 0; ++wrap; }
     }
+    return;
+  }
 
+  // ---------------- consumer warps ----------------
+  const int ct = threadIdx.x - 32;
+  const int jg = ct / P.cols;            // row group of this thread
+  const int col = ct - jg * P.cols;      // column slot within a pass
+  const int lane = threadIdx.x & 31;
+  int s = 0;
+  uint32_t wrap = 0;
+  for (long long item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+    const uint8_t* stage = stages + (size_t)s * P.stage_bytes;
+    const uint32_t* ri = rowinfo + s * kMaxRows;
     const int f = (int)(item / P.groups_per_frame);
     const int g = (int)(item - (long long)f * P.groups_per_frame);
     const int oy0 = g * P.R;
     const int nrows = min(P.R, P.dh - oy0);
-    const FramePtrs fp = frame_ptrs(P.batch, f);
-    uint8_t* gout = fp.out + (long long)oy0 * P.dst_row_stride;
-    const bool contiguous = (P.dst_row_stride == (long long)P.out_row_bytes);
-    const int phase = (int)(reinterpret_cast<uintptr_t>(gout) & 15);
+    uint8_t* gout = frame_ptrs(P.batch, f).out + (long long)oy0 * P.dst_row_stride;
+    mbar_wait(&full[s], wrap & 1);
 
-    for (int ox = threadIdx.x; ox < P.dw; ox += blockDim.x) {
-      const int x = P.x0 + ox * P.dx;
-      const int xi = x >> 16;
-      const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
-      const uint32_t wx0 = 0x7fu ^ xf, wx1 = xf;
-      const int cL = (xi >> 1) << 1, cR = ((xi + 1) >> 1) << 1;
-#pragma unroll 2
-      for (int j = 0; j < nrows; ++j) {
-        const RowSel s = row_select(P, oy0 + j);
-        const uint8_t* Yt = in_stage + (size_t)(4 * j) * P.row_pitch;
-        const uint8_t* Ct = Yt + 2 * (size_t)P.row_pitch;
-        // top row: two luma samples, their (nearest) chroma pairs
-        const int yyL = yuv_luma_term(Yt[xi]), yyR = yuv_luma_term(Yt[xi + 1]);
-        const uint32_t uvL = *reinterpret_cast<const uint16_t*>(Ct + cL);
-        const uint32_t uvR = *reinterpret_cast<const uint16_t*>(Ct + cR);
-        const ChromaTerms tL = VU ? yuv_chroma_terms(uvL >> 8, uvL & 0xFF) : yuv_chroma_terms(uvL & 0xFF, uvL >> 8);
-        const ChromaTerms tR = VU ? yuv_chroma_terms(uvR >> 8, uvR & 0xFF) : yuv_chroma_terms(uvR & 0xFF, uvR >> 8);
-        // packed lanes: rb = R | B<<16 ; gg = G_left | G_right<<16
-        uint32_t rbL = (uint32_t)clamp_shift6(yyL + tL.cr) | ((uint32_t)clamp_shift6(yyL + tL.cb) << 16);
-        uint32_t rbR = (uint32_t)clamp_shift6(yyR + tR.cr) | ((uint32_t)clamp_shift6(yyR + tR.cb) << 16);
-        uint32_t gg = (uint32_t)clamp_shift6(yyL + tL.cg) | ((uint32_t)clamp_shift6(yyR + tR.cg) << 16);
-        if (s.yf) {
-          const uint8_t* Yb = Yt + P.row_pitch;
-          const uint8_t* Cb = (s.cb != s.ct) ? Yt + 3 * (size_t)P.row_pitch : Ct;
-          const int zzL = yuv_luma_term(Yb[xi]), zzR = yuv_luma_term(Yb[xi + 1]);
-          const uint32_t vwL = *reinterpret_cast<const uint16_t*>(Cb + cL);
-          const uint32_t vwR = *reinterpret_cast<const uint16_t*>(Cb + cR);
-          const ChromaTerms bL = VU ? yuv_chroma_terms(vwL >> 8, vwL & 0xFF) : yuv_chroma_terms(vwL & 0xFF, vwL >> 8);
-          const ChromaTerms bR = VU ? yuv_chroma_terms(vwR >> 8, vwR & 0xFF) : yuv_chroma_terms(vwR & 0xFF, vwR >> 8);
-          const uint32_t rbL2 = (uint32_t)clamp_shift6(zzL + bL.cr) | ((uint32_t)clamp_shift6(zzL + bL.cb) << 16);
-          const uint32_t rbR2 = (uint32_t)clamp_shift6(zzR + bR.cr) | ((uint32_t)clamp_shift6(zzR + bR.cb) << 16);
-          const uint32_t gg2 = (uint32_t)clamp_shift6(zzL + bL.cg) | ((uint32_t)clamp_shift6(zzR + bR.cg) << 16);
-          // InterpolateRow_C on two 16-bit lanes at once
-          const uint32_t w1 = (uint32_t)s.yf, w0 = 256u - w1;
-          rbL = ((rbL * w0 + rbL2 * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
-          rbR = ((rbR * w0 + rbR2 * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
-          gg = ((gg * w0 + gg2 * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
-        }
-        // ScaleARGBFilterCols_C: (a*(0x7f^xf) + b*xf) >> 7, truncating
-        const uint32_t rb = rbL * wx0 + rbR * wx1;  // lanes <= 32385
-        const uint32_t r = (rb >> 7) & 0xFFu;
-        const uint32_t b = rb >> 23;
-        const uint32_t gq = ((gg & 0xFFFFu) * wx0 + (gg >> 16) * wx1) >> 7;
-        if (sizeof(OT) == 1) {
-          uint8_t* o = out_stage + phase + (size_t)j * P.out_row_bytes + ox * 3;
-          o[0] = (uint8_t)r; o[1] = (uint8_t)gq; o[2] = (uint8_t)b;
-        } else {
-          OT* o = reinterpret_cast<OT*>(out_stage + phase + (size_t)j * P.out_row_bytes) + ox * 3;
-          o[0] = lut[r]; o[1] = lut[gq]; o[2] = lut[b];
+    for (int pass = 0; pass < P.passes; ++pass) {
+      const int ox = pass * P.cols + col;
+      if (ox < P.dw) {
+        const int x = P.x0 + ox * P.dx;
+        const int xi = x >> 16;
+        const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
+        const uint32_t wp = xf | ((0x7fu ^ xf) << 16);
+        const int cL = (xi >> 1) << 1, cR = ((xi + 1) >> 1) << 1;
+        for (int j = jg; j < nrows; j += P.G) {
+          const uint32_t info = ri[j];
+          const uint32_t w1 = info & 0xFFu, w0 = 256u - w1;
+          const uint8_t* yt = stage + (size_t)(4 * j) * P.row_pitch;
+          const uint8_t* yb = yt + P.row_pitch;
+          const uint8_t* ctop = yt + 2 * (size_t)P.row_pitch;
+          const uint8_t* cbot = yt + (size_t)(info >> 8) * P.row_pitch;
+          uint32_t tr, tg, tb, br, bg, bb;
+          yuv_pair_to_rgb<VU>(yt, ctop, xi, cL, cR, tr, tg, tb);
+          yuv_pair_to_rgb<VU>(yb, cbot, xi, cL, cR, br, bg, bb);
+          const uint32_t r = hblend_pair(vblend2(tr, br, w0, w1), wp);
+          const uint32_t gq = hblend_pair(vblend2(tg, bg, w0, w1), wp);
+          const uint32_t b = hblend_pair(vblend2(tb, bb, w0, w1), wp);
+          uint8_t* orow = gout + (long long)j * P.dst_row_stride;
+          if (sizeof(OT) == 1) {
+            uint8_t* o = orow + ox * 3;
+            o[0] = (uint8_t)r; o[1] = (uint8_t)gq; o[2] = (uint8_t)b;
+          } else {
+            float* o = reinterpret_cast<float*>(orow) + ox * 3;
+            o[0] = lut[r]; o[1] = lut[gq]; o[2] = lut[b];
+          }
         }
       }
     }
-    __syncthreads();  // out_stage complete; every thread is done reading in_stage
-    if (contiguous) {
-      copy_out(out_stage + phase, gout, nrows * P.out_row_bytes);
-    } else {
-      for (int j = 0; j < nrows; ++j) {
-        // per-row phase: rows are staged back to back, so only copy vectorised when phases agree
-        const uint8_t* srow = out_stage + phase + (size_t)j * P.out_row_bytes;
-        uint8_t* grow = gout + (long long)j * P.dst_row_stride;
-        if (((reinterpret_cast<uintptr_t>(srow) ^ reinterpret_cast<uintptr_t>(grow)) & 15) == 0) copy_out(srow, grow, P.out_row_bytes);
-        else for (int i = threadIdx.x; i < P.out_row_bytes; i += blockDim.x) grow[i] = srow[i];
-      }
-    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+    if (++s == P.S) { s = 0; ++wrap; }
   }
 }
 
 // Builds the Normalize table with the same device arithmetic as the generic kernel.
-template <typename OT>
-__global__ void build_lut_kernel(OT* lut, float mean, float sd) {
+__global__ void build_lut_kernel(float* lut, float mean, float sd) {
   int i = threadIdx.x;
-  if (i < 256) lut[i] = normalize_elem<OT>((float)i, mean, sd);
+  if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
 }
 
 static bool is_identity(const BandCuAffine& m) {
   return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
+}
+
+static int env_int(const char* name, int lo, int hi, int dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  const int x = atoi(v);
+  return (x < lo || x > hi) ? dflt : x;
 }
 
 bool fast_plan_supported(const BandCuPlanDesc& d) {
@@ -295,7 +331,7 @@ bool fast_plan_supported(const BandCuPlanDesc& d) {
   if (!is_identity(d.luma_map) || !is_identity(d.pre_map) || !is_identity(d.chroma_map)) return false;
   if (d.normalize ? (d.out_dtype != BANDCU_DT_F32) : false) return false;
   if (d.vw < 2 || d.vw > 8192 || d.dst_width > 4096) return false;
-  // 32-bit x/y stepping inside the kernel
+  // 32-bit x stepping inside the kernel
   if ((long long)d.x0 + (long long)d.dst_width * d.dx > 0x7fffffffLL) return false;
   return true;
 }
@@ -310,19 +346,15 @@ int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out) {
   if (d.normalize) {
     e = cudaMalloc(&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
-    build_lut_kernel<float><<<1, 256>>>((float*)p->lut_dev, d.mean, d.std_);
+    build_lut_kernel<<<1, 256>>>((float*)p->lut_dev, d.mean, d.std_);
     count_launch();
     e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { cudaFree(p->lut_dev); delete p; return (int)e; }
   }
-  // block: smallest multiple of 32 covering dst_width in ceil(dw/512) column passes
-  const int passes = (d.dst_width + 511) / 512;
-  const int per = (d.dst_width + passes - 1) / passes;
-  p->block = ((per + 31) / 32) * 32;
-  if (p->block < 64) p->block = 64;
-  p->R = 4;
-  const char* r = getenv("BANDCU_FAST_ROWS");
-  if (r && atoi(r) > 0 && atoi(r) <= 16) p->R = atoi(r);
+  p->R = env_int("BANDCU_FAST_ROWS", 1, kMaxRows, 4);
+  p->G = env_int("BANDCU_FAST_GROUPS", 1, kMaxRows, 1);
+  p->S = env_int("BANDCU_FAST_STAGES", 2, kMaxStages, 3);
+  if (p->G > p->R) p->G = p->R;
   *out = p;
   return BANDCU_OK;
 }
@@ -334,11 +366,11 @@ void fast_plan_destroy(FastPlan* p) {
 }
 
 template <typename OT>
-static int launch_fast_t(FastPlan* p, FastParams& P, bool vu, int grid, size_t smem, cudaStream_t stream) {
+static int launch_fast_t(FastParams& P, bool vu, int grid, int block, size_t smem, cudaStream_t stream) {
   auto kern = vu ? fast_nv_bilinear_down_kernel<OT, true> : fast_nv_bilinear_down_kernel<OT, false>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kern<<<grid, p->block, smem, stream>>>(P);
+  kern<<<grid, block, smem, stream>>>(P);
   count_launch();
   return (int)cudaGetLastError();
 }
@@ -362,14 +394,22 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.stride0 = d.stride0; P.stride_uv = d.stride_uv;
   P.x0 = d.x0; P.y0 = d.y0; P.dx = d.dx; P.dy = d.dy; P.max_y = d.max_y; P.linear = d.linear;
   P.dw = d.dst_width; P.dh = d.dst_height;
-  P.R = p->R;
-  const int esz = d.normalize ? 4 : 1;
-  P.out_row_bytes = d.dst_width * 3 * esz;
   P.dst_row_stride = d.dst_row_stride;
   const int cbytes = ((d.vw + 1) >> 1) << 1;
   P.row_pitch = ((cbytes + 15) / 16) * 16 + 16;  // +16: xi+1 may touch one byte past the row when xf == 0
-  P.in_stage_bytes = P.R * 4 * P.row_pitch;
-  P.out_stage_bytes = ((P.R * P.out_row_bytes + 15) / 16) * 16 + 32;
+  // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
+  P.R = p->R; P.G = p->G; P.S = p->S;
+  P.passes = (d.dst_width + 511) / 512;
+  P.cols = (((d.dst_width + P.passes - 1) / P.passes) + 31) / 32 * 32;
+  while (P.G > 1 && 32 + P.G * P.cols > 1024) --P.G;
+  const size_t smem_cap = 226 * 1024;
+  while (P.S > 2 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.S;
+  while (P.R > 1 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.R;
+  if (P.G > P.R) P.G = P.R;
+  P.stage_bytes = P.R * 4 * P.row_pitch;
+  const size_t smem = kOffStages + (size_t)P.S * P.stage_bytes;
+  if (smem > smem_cap) return BANDCU_E_UNSUPPORTED;
+  const int block = 32 + P.G * P.cols;
   P.groups_per_frame = (d.dst_height + P.R - 1) / P.R;
   P.n_items = (long long)n * P.groups_per_frame;
   P.lut = p->lut_dev;
@@ -385,19 +425,27 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.use_bulk = aligned ? 1 : 0;
   const char* nb = getenv("BANDCU_FAST_NO_BULK");
   if (nb && nb[0] == '1') P.use_bulk = 0;
-  const size_t smem = 16 + 1024 + 2 * (size_t)P.in_stage_bytes + 2 * (size_t)P.out_stage_bytes;
-  if (smem > 200 * 1024) return BANDCU_E_UNSUPPORTED;
-  // persistent grid: as many CTAs per SM as shared memory / threads allow
-  int per_sm = (int)((220 * 1024) / (smem + 1024));
-  int by_threads = 2048 / p->block;
-  if (per_sm > by_threads) per_sm = by_threads;
-  if (per_sm < 1) per_sm = 1;
-  if (per_sm > 8) per_sm = 8;
+  // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
+  int per_sm = 1;
+  {
+    cudaError_t e;
+    if (d.normalize) {
+      auto kern = vu ? fast_nv_bilinear_down_kernel<float, true> : fast_nv_bilinear_down_kernel<float, false>;
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
+    } else {
+      auto kern = vu ? fast_nv_bilinear_down_kernel<uint8_t, true> : fast_nv_bilinear_down_kernel<uint8_t, false>;
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
+    }
+    if (e != cudaSuccess) return (int)e;
+    if (per_sm < 1) return BANDCU_E_UNSUPPORTED;
+  }
   long long want = (long long)p->num_sms * per_sm;
   int grid = (int)(P.n_items < want ? P.n_items : want);
   if (grid < 1) grid = 1;
-  return d.normalize ? launch_fast_t<float>(p, P, vu, grid, smem, stream)
-                     : launch_fast_t<uint8_t>(p, P, vu, grid, smem, stream);
+  return d.normalize ? launch_fast_t<float>(P, vu, grid, block, smem, stream)
+                     : launch_fast_t<uint8_t>(P, vu, grid, block, smem, stream);
 }
 
 }  // namespace bandcu

@@ -102,6 +102,7 @@ def lib():
     L.bandcu_event_record.argtypes = [vp, vp]
     L.bandcu_event_elapsed_ms.argtypes = [vp, vp, C.POINTER(C.c_float)]
     L.bandcu_pointer_is_device.argtypes = [vp]
+    L.bandcu_pointer_kind.argtypes = [vp]
     L.bandcu_last_error_string.restype = C.c_char_p
     _lib = L
     return L
@@ -118,5 +119,5 @@ EXPORTED = [
     "bandcu_malloc", "bandcu_free", "bandcu_host_alloc", "bandcu_host_free", "bandcu_memcpy_h2d", "bandcu_memcpy_d2h",
     "bandcu_memcpy_d2d", "bandcu_memset", "bandcu_stream_create", "bandcu_stream_destroy", "bandcu_stream_sync",
     "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",
-    "bandcu_pointer_is_device", "bandcu_last_error_string",
+    "bandcu_pointer_is_device", "bandcu_pointer_kind", "bandcu_last_error_string",
 ]

@@ -186,6 +186,8 @@ BANDCU_API int bandcu_event_elapsed_ms(void* start, void* stop, float* ms);
 BANDCU_API int bandcu_stream_wait_event(void* stream, void* ev);
 /* 1 if ptr is device (or managed) memory, 0 if host, <0 on error. */
 BANDCU_API int bandcu_pointer_is_device(const void* ptr);
+/* 0 pageable host memory, 1 pinned / registered host memory, 2 device or managed memory, <0 on error. */
+BANDCU_API int bandcu_pointer_kind(const void* ptr);
 BANDCU_API const char* bandcu_last_error_string(void);
 
 #ifdef __cplusplus

@@ -12,7 +12,7 @@ NORM = (5, 0, 0, 0, 0, 127.5, 127.5)
 
 
 @pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21"])
-@pytest.mark.parametrize("W,H,dw,dh", [(641, 479, 224, 224), (3, 5, 2, 3), (2, 2, 1, 1), (17, 9, 5, 4), (642, 482, 225, 223),
+@pytest.mark.parametrize("W,H,dw,dh", [(641, 479, 224, 224), (3, 5, 2, 3), (2, 2, 3, 2), (17, 9, 5, 4), (642, 482, 225, 223),
                                        (1921, 1081, 300, 300)])
 def test_odd_and_tiny_yuv_frames(O, fmt_name, W, H, dw, dh):
     fmt = getattr(O, "FMT_" + fmt_name)
