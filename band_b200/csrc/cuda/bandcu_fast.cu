@@ -353,7 +353,7 @@ int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out) {
   }
   p->R = env_int("BANDCU_FAST_ROWS", 1, kMaxRows, 4);
   p->G = env_int("BANDCU_FAST_GROUPS", 1, kMaxRows, 1);
-  p->S = env_int("BANDCU_FAST_STAGES", 2, kMaxStages, 3);
+  p->S = env_int("BANDCU_FAST_STAGES", 2, kMaxStages, 2);
   if (p->G > p->R) p->G = p->R;
   *out = p;
   return BANDCU_OK;

@@ -37,6 +37,10 @@ OUT_BYTES = DW * DH * 3 * 4                                    # 602 112
 ALG_BYTES = FRAME_BYTES + OUT_BYTES                            # 3 712 512 (SURVEY 8d / DESIGN.md)
 WORKLOAD = "1080p NV12 -> ColorSpaceConvert(RGB) -> Resize(224,224) -> Normalize(127.5,127.5) f32 [1,224,224,3]"
 METRIC = "frames/s (1080p NV12->224x224 RGB f32)"
+# dram__bytes_read.sum + dram__bytes_write.sum of the fused kernel per frame, from the committed ncu --set full
+# capture (profiles/r01_ncu_full_fast_v2_R4G1S3.txt: 770.742 MB + 280.732 MB over a 512-frame launch). Below the
+# algorithmic figure because the down-scaler never reads the source rows it does not sample.
+NCU_TRAFFIC_PER_FRAME = (770.742016e6 + 280.731904e6) / 512
 
 
 def measured_peak():
@@ -301,7 +305,9 @@ def run_ours(args):
                 "gpu_launches": e2e_launches},
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": args.traffic, "peak_source": peak_src, "kernel": "fast_nv_bilinear_down_kernel<float,false>",
+                     "traffic": args.traffic if args.traffic is not None else NCU_TRAFFIC_PER_FRAME * F,
+                     "traffic_source": "ncu --set full, profiles/r01_ncu_full_fast_v2_R4G1S3.txt, scaled per frame",
+                     "peak_source": peak_src, "kernel": "fast_nv_bilinear_down_kernel<float,false>",
                      "kernel_ms": kernel_ms, "bytes_per_launch_algorithmic": ALG_BYTES * F},
         "clocks": clocks, "parity": parity,
     }
