@@ -145,27 +145,16 @@ def host_threads():
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
 def dist_setup(n_gpus):
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    import torch
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    return rank, local, world, dist
+    """One process per GPU (torchrun env); NCCL carries the barrier and the timing reduction only."""
+    from band_b200 import shard
+    rank, local, world = shard.env_rank()
+    return rank, local, world, shard.init_dist("nccl")
 
 
 def barrier_max(dist, local, value_ms):
     """max over ranks of a device-measured duration (no data-path collective: timing only)."""
-    if dist is None:
-        return value_ms
-    import torch
-    t = torch.tensor([value_ms], dtype=torch.float64, device="cuda:%d" % local)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    from band_b200 import shard
+    return shard.max_over_ranks(dist, value_ms, device="cuda:%d" % local)
 
 
 def sync_all(dist, local):
