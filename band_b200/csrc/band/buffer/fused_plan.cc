@@ -2,6 +2,7 @@
 #include "band/buffer/fused_plan.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "absl/strings/str_format.h"
@@ -708,10 +709,20 @@ constexpr int kMaxPassFrames = 2048;
 
 absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host,
                                 bool out_host, bool synchronize) {
+  // Zero-copy input: a chain that lowers to the single staged launch reads every needed source row exactly
+  // once, through the TMA engine. When the frames sit in PINNED host memory (mapped into the device address
+  // space under UVA) the kernel pulls those rows straight over PCIe: rows the resize never samples never
+  // cross the bus and there is no staging copy at all. Pageable frames are staged through HBM as before.
+  bool zero_copy = in_host && !writes_input_ && IsSingleFastLaunch() && getenv("BAND_NO_ZERO_COPY") == nullptr;
+  for (int f = 0; zero_copy && f < m; ++f) {
+    for (int k = 0; k < input_.num_planes; ++k)
+      if (bandcu_pointer_kind((*inputs[f])[k].data) != 1) { zero_copy = false; break; }
+  }
+  const bool in_staged = in_host && !zero_copy;
   std::vector<HostRanges> in_r, out_r;
   size_t in_step = 0, out_step = 0;
   bool in_uniform = false, out_uniform = false;
-  if (in_host) {
+  if (in_staged) {
     in_r.reserve(m);
     for (int f = 0; f < m; ++f) in_r.push_back(RangesOf(*inputs[f], input_));
     in_uniform = UniformStep(in_r, &in_step);
@@ -731,15 +742,16 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   in_ptrs_.resize(m);
   out_ptrs_.assign(m, SlotPointers());
   for (int f = 0; f < m; ++f) {
-    in_ptrs_[f] = in_host ? StagedPointers(*inputs[f], input_, in_r[f], in_stage_ + in_step * f)
+    in_ptrs_[f] = in_staged ? StagedPointers(*inputs[f], input_, in_r[f], in_stage_ + in_step * f)
                           : BufferPointers(*inputs[f]);
     if (writes_output_)
       out_ptrs_[f] = out_host ? StagedPointers(*outputs[f], output_, out_r[f], out_stage_ + out_step * f)
                               : BufferPointers(*outputs[f]);
   }
-  const bool download = (out_host && writes_output_) || (in_host && writes_input_);
-  const bool staged = in_host || download;
-  const int chunk = staged ? kChunkFrames : m;
+  const bool download = (out_host && writes_output_) || (in_staged && writes_input_);
+  const bool staged = in_staged || download;
+  int chunk = staged ? kChunkFrames : m;
+  if (const char* c = getenv("BAND_CHUNK_FRAMES")) { if (staged && atoi(c) > 0) chunk = atoi(c); }
   size_t ev = 0;
   if (staged && in_flight_) {
     // an earlier asynchronous pass may still use the staging areas: its kernels read in_stage_, its
@@ -752,7 +764,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   }
   for (int a = 0; a < m; a += chunk) {
     const int b = std::min(m, a + chunk);
-    if (in_host) {
+    if (in_staged) {
       if (in_uniform) {
         const size_t bytes = in_step * (b - a - 1) + in_r[a].bytes[0];
         if (bandcu_memcpy_h2d(in_stage_ + in_step * a, in_r[a].lo[0], bytes, copy_in_) != BANDCU_OK)
@@ -794,7 +806,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
           }
         }
       }
-      if (in_host && writes_input_) {  // an in-place stage changed the (staged) chain input: copy it back
+      if (in_staged && writes_input_) {  // an in-place stage changed the (staged) chain input: copy it back
         for (int f = a; f < b; ++f) {
           size_t off = 0;
           for (int i = 0; i < in_r[f].count; ++i) {

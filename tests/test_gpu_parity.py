@@ -202,3 +202,42 @@ def test_reference_resize_hippo(O, hippo):
     assert np.abs(out.astype(np.int32) - want).mean() < 0.25
     st, ref, _ = O.run_op((O.OP_RESIZE, 256, 256), src.reshape(-1), W, H, O.FMT_RGB)
     assert_same_bits(out, ref, "hippo resize")
+
+
+@pytest.mark.parametrize("fmt_name,W,H,d,f32", [("NV12", 1920, 1080, 224, True), ("NV21", 1920, 1080, 300, False),
+                                                ("NV21", 640, 480, 224, True)])
+def test_pinned_host_frames_zero_copy(O, fmt_name, W, H, d, f32):
+    """Frames in PINNED host memory (BandHostAlloc): the staged kernel pulls the rows it samples straight over
+    PCIe (no staging copy). Same bits as the oracle."""
+    import ctypes as C
+    from band_b200 import band_c as B
+    fmt = getattr(O, "FMT_" + fmt_name)
+    n = 40  # more than one 32-frame chunk
+    fr = rand_frames(O, 4, W, H, fmt, 4242)
+    fb = fr.shape[1]
+    L = B.lib()
+    host = L.BandHostAlloc(n * fb)
+    assert host
+    try:
+        hv = np.ctypeslib.as_array(C.cast(host, C.POINTER(C.c_uint8)), shape=(n, fb))
+        for i in range(n):
+            hv[i] = fr[i % 4]
+        ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, d, d)] + ([NORM] if f32 else [])
+        dt = O.DT_F32 if f32 else O.DT_U8
+        st, want = oracle_chain(O, ops, fr, W, H, fmt, dt, (1, d, d, 3))
+        assert st == 0
+        from gpu_util import to_capi_ops, NP_OF_ORC
+        proc = B.ImageProcessor(to_capi_ops(ops))
+        tens = [B.Tensor(NP_OF_ORC[dt], (1, d, d, 3), device=False) for _ in range(n)]
+        bufs = [B.Buffer().set_raw(host + i * fb, W, H, B.FORMATS[fmt_name]) for i in range(n)]
+        assert proc.process_batch(bufs, tens) == B.kBandOk, B.last_error()
+        assert proc.is_fused
+        for i in range(n):
+            assert_same_bits(tens[i].numpy(), want[i % 4], "pinned frame %d" % i)
+        for b in bufs:
+            b.close()
+        for t in tens:
+            t.close()
+        proc.close()
+    finally:
+        L.BandHostFree(host)
