@@ -210,6 +210,54 @@ absl::Status ChainLowering::EmitInto(int dst_slot, const ImageLayout& dst) {
     plan_->segments_.push_back(seg);
     return absl::OkStatus();
   }
+  if (v.IsYuv() && v.scaled) {  // Resize in the YUV domain: every plane through its own libyuv scaler
+    if (dst.num_planes != 3) return absl::InvalidArgumentError("YUV output buffer needs three planes");
+    const bool nv = v.format == BufferFormat::kNV12 || v.format == BufferFormat::kNV21;
+    const size_t want_ps = nv ? 2 : 1;
+    if (v.src.pixel_stride[1] != want_ps || dst.pixel_stride[1] != want_ps || v.src.pixel_stride[2] != want_ps ||
+        dst.pixel_stride[2] != want_ps)
+      return absl::UnimplementedError("Resize of a 4:2:0 buffer with non-native chroma pixel strides is not supported");
+    seg.kind = Segment::Kind::kYuvScale;
+    seg.interleaved_uv = nv;
+    auto plane_desc = [&](int src_kind, int channels, const ScaleSpec& spec, int sw, int sh, int dw, int dh,
+                          size_t src_stride, size_t dst_stride) {
+      BandCuPlanDesc d{};
+      d.src_kind = src_kind;
+      d.stride0 = static_cast<int>(src_stride);
+      d.vw = sw;
+      d.vh = sh;
+      d.luma_map = d.pre_map = d.chroma_map = kIdentity;
+      d.cvt = BANDCU_CVT_NONE;
+      d.flavor = spec.flavor;
+      d.scale_mode = spec.mode;
+      d.linear = spec.linear;
+      d.x0 = spec.x0; d.y0 = spec.y0; d.dx = spec.dx; d.dy = spec.dy; d.max_y = spec.max_y;
+      d.dst_width = dw;
+      d.dst_height = dh;
+      d.channels = channels;
+      d.out_dtype = BANDCU_DT_U8;
+      d.dst_row_stride = static_cast<long long>(dst_stride);
+      return d;
+    };
+    const int sw = v.pre_w, sh = v.pre_h, dw = v.w, dh = v.h;
+    const int shw = (sw + 1) / 2, shh = (sh + 1) / 2, dhw = (dw + 1) / 2, dhh = (dh + 1) / 2;
+    BandCuPlanDesc dy = plane_desc(BANDCU_SRC_GRAY, 1, DispatchPlaneScale(sw, sh, dw, dh), sw, sh, dw, dh,
+                                   v.src.row_stride[0], dst.row_stride[0]);
+    if (bandcu_plan_create(&dy, &seg.plane_plan[0]) != BANDCU_OK) return CudaError("bandcu_plan_create");
+    if (nv) {
+      BandCuPlanDesc duv = plane_desc(BANDCU_SRC_UV, 2, DispatchUvScale(shw, shh, dhw, dhh), shw, shh, dhw, dhh,
+                                      v.src.row_stride[1], dst.row_stride[1]);
+      if (bandcu_plan_create(&duv, &seg.plane_plan[1]) != BANDCU_OK) return CudaError("bandcu_plan_create");
+    } else {
+      for (int k = 1; k <= 2; ++k) {
+        BandCuPlanDesc dc = plane_desc(BANDCU_SRC_GRAY, 1, DispatchPlaneScale(shw, shh, dhw, dhh), shw, shh, dhw, dhh,
+                                       v.src.row_stride[k], dst.row_stride[k]);
+        if (bandcu_plan_create(&dc, &seg.plane_plan[k]) != BANDCU_OK) return CudaError("bandcu_plan_create");
+      }
+    }
+    plan_->segments_.push_back(seg);
+    return absl::OkStatus();
+  }
   if (v.IsYuv()) {  // 4:2:0 in, 4:2:0 out: pure permutation of luma and chroma samples
     if (dst.num_planes != 3) return absl::InvalidArgumentError("YUV output buffer needs three planes");
     seg.kind = Segment::Kind::kYuvMap;
@@ -382,9 +430,20 @@ absl::Status ChainLowering::ConvertColor(BufferFormat to) {
 absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
   if (view_->dtype != DataType::kUInt8)
     return absl::UnimplementedError("Resize on non-uint8 pixels is not supported");
-  if (view_->IsYuv())
-    return absl::UnimplementedError("Resize of a 4:2:0 buffer (NV12Scale / I420Scale) has no CUDA kernel yet");
   if (dst_width <= 0 || dst_height <= 0) return absl::InvalidArgumentError("Resize: non-positive output dimension");
+  if (view_->IsYuv()) {
+    // ResizeYv / ResizeNv (libyuv_image_operator.cc:376-435): the planes of a MATERIALISED 4:2:0 image go through
+    // ScalePlane (Y, planar U and V) or UVScale (interleaved chroma); pending index maps / repacks are closed first
+    if (!view_->Untouched() || view_->format != view_->src.format) RETURN_IF_ERROR(Flush());
+    View& y = *view_;
+    terminal_noop_ = false;
+    y.scaled = true;
+    y.pre_w = y.w;
+    y.pre_h = y.h;
+    y.w = dst_width;
+    y.h = dst_height;
+    return absl::OkStatus();
+  }
   if (view_->scaled || view_->normalized) RETURN_IF_ERROR(Flush());
   View& v = *view_;
   terminal_noop_ = false;
@@ -557,8 +616,11 @@ SlotPointers StagedPointers(const Buffer& b, const ImageLayout& l, const HostRan
 }  // namespace
 
 FusedPlan::~FusedPlan() {
-  for (Segment& s : segments_)
+  for (Segment& s : segments_) {
     if (s.plan) bandcu_plan_destroy(s.plan);
+    for (BandCuPlan* p : s.plane_plan)
+      if (p) bandcu_plan_destroy(p);
+  }
   for (unsigned char* p : scratch_mem_)
     if (p) bandcu_free(p);
   if (in_stage_) bandcu_free(in_stage_);
@@ -658,6 +720,21 @@ absl::Status FusedPlan::RunSegments(int first, int last) {
           const SlotPointers s = Resolve(seg.src_slot, f), d = Resolve(seg.dst_slot, f);
           const BandCuYuvPtrs p = {s.y, s.u, s.v, d.y, d.u, d.v};
           if (bandcu_yuv_map(&seg.yuv, &p, stream_) != BANDCU_OK) return CudaError("bandcu_yuv_map");
+        }
+        break;
+      }
+      case Segment::Kind::kYuvScale: {
+        frames_.resize(m);
+        for (int k = 0; k < 3; ++k) {
+          if (!seg.plane_plan[k]) continue;
+          for (int f = 0; f < m; ++f) {
+            const SlotPointers s = Resolve(seg.src_slot, first + f), d = Resolve(seg.dst_slot, first + f);
+            const unsigned char* sp = k == 0 ? s.y : (seg.interleaved_uv ? std::min(s.u, s.v) : (k == 1 ? s.u : s.v));
+            unsigned char* dp = k == 0 ? d.y : (seg.interleaved_uv ? std::min(d.u, d.v) : (k == 1 ? d.u : d.v));
+            frames_[f] = BandCuFrame{sp, nullptr, nullptr, dp};
+          }
+          if (bandcu_plan_run(seg.plane_plan[k], frames_.data(), m, stream_) != BANDCU_OK)
+            return CudaError("bandcu_plan_run");
         }
         break;
       }

@@ -44,7 +44,7 @@ struct ImageLayout {
 enum : int { kSlotInput = -1, kSlotOutput = -2 };  // otherwise: index into FusedPlan::scratch
 
 struct Segment {
-  enum class Kind { kPixel, kYuvMap, kElementwise };
+  enum class Kind { kPixel, kYuvMap, kYuvScale, kElementwise };
   Kind kind = Kind::kPixel;
   int src_slot = kSlotInput;
   int dst_slot = kSlotOutput;
@@ -53,6 +53,10 @@ struct Segment {
   BandCuPlan* plan = nullptr;
   // kYuvMap
   BandCuYuvMapDesc yuv{};
+  // kYuvScale (Resize of a 4:2:0 buffer: I420Scale / NV12Scale, libyuv_image_operator.cc:376-435): one plan per
+  // plane -- [0] luma, [1] U (or the interleaved UV plane), [2] V (planar only)
+  BandCuPlan* plane_plan[3] = {nullptr, nullptr, nullptr};
+  bool interleaved_uv = false;
   // kElementwise (Normalize / DataTypeConvert on an already materialised buffer)
   int in_dtype = 0, out_dtype = 0;
   long long count = 0;

@@ -82,7 +82,9 @@ int FixedDiv1(int num, int div) {
   return static_cast<int>(((static_cast<int64_t>(num) << 16) - 0x00010001) / (div - 1));
 }
 
-ScaleSpec DispatchArgbScale(int sw, int sh, int dw, int dh) {
+namespace {
+// Shared by ScaleARGB (4 bytes per pixel) and ScaleUV (2 bytes per pixel).
+ScaleSpec DispatchPacked(int sw, int sh, int dw, int dh, bool uv) {
   const int kF = BANDCU_FLAVOR_ARGB;
   Filter f = ReduceBilinear(sw, sh, dw, dh);
   const Slope s = ComputeSlope(sw, sh, dw, dh, f);
@@ -97,10 +99,25 @@ ScaleSpec DispatchArgbScale(int sw, int sh, int dw, int dh) {
   // unit horizontal step starting on a pixel: rows are blended whole
   if (s.dx == 0x10000 && (s.x & 0xffff) == 0)
     return Make(kF, BANDCU_SCALE_VERTICAL, s, f == kNone ? 1 : 0, VerticalMaxY(sh));
+  if (uv) {  // scale_uv.cc only: exact 2x up-samplers
+    if ((dw + 1) / 2 == sw && f == kLinear) {
+      Slope u;
+      u.dy = dh > 1 ? FixedDiv(sh - 1, dh - 1) : 0;
+      return Make(kF, BANDCU_SCALE_UP2_LINEAR, u, 1, max_y);
+    }
+    if ((dh + 1) / 2 == sh && (dw + 1) / 2 == sw && f == kBilinear) {
+      Slope u;
+      return Make(kF, BANDCU_SCALE_UP2_BILINEAR, u, 0, max_y);
+    }
+  }
   if (f != kNone && s.dy < 65536) return Make(kF, BANDCU_SCALE_BILINEAR_UP, s, f == kLinear ? 1 : 0, max_y);
   if (f != kNone) return Make(kF, BANDCU_SCALE_BILINEAR_DOWN, s, f == kLinear ? 1 : 0, max_y);
   return Make(kF, BANDCU_SCALE_POINT, s, 1, max_y);
 }
+}  // namespace
+
+ScaleSpec DispatchArgbScale(int sw, int sh, int dw, int dh) { return DispatchPacked(sw, sh, dw, dh, false); }
+ScaleSpec DispatchUvScale(int sw, int sh, int dw, int dh) { return DispatchPacked(sw, sh, dw, dh, true); }
 
 ScaleSpec DispatchPlaneScale(int sw, int sh, int dw, int dh) {
   const int kF = BANDCU_FLAVOR_PLANE;

@@ -29,6 +29,9 @@ int FixedDiv1(int num, int div);
 // ARGBScale(..., kFilterBilinear) on a src_w x src_h image of 4-byte (or, for
 // RGB, 3 used bytes of 4) pixels -> dst_w x dst_h.
 ScaleSpec DispatchArgbScale(int src_w, int src_h, int dst_w, int dst_h);
+// UVScale(..., kFilterBilinear) on an interleaved 2-channel chroma plane (inside NV12Scale,
+// libyuv_image_operator.cc:422): ScaleARGB's rules plus the exact-2x up-samplers of scale_uv.cc.
+ScaleSpec DispatchUvScale(int src_w, int src_h, int dst_w, int dst_h);
 // ScalePlane(..., kFilterBilinear) on an 8-bit plane.
 ScaleSpec DispatchPlaneScale(int src_w, int src_h, int dst_w, int dst_h);
 

@@ -51,11 +51,13 @@ struct BandCuPlan {
 
 static int validate_desc(const BandCuPlanDesc* d) {
   if (!d) return BANDCU_E_INVALID;
-  if (d->src_kind < BANDCU_SRC_GRAY || d->src_kind > BANDCU_SRC_YUV420) return BANDCU_E_INVALID;
+  if (d->src_kind < BANDCU_SRC_GRAY || d->src_kind > BANDCU_SRC_UV) return BANDCU_E_INVALID;
   if (d->vw <= 0 || d->vh <= 0 || d->dst_width <= 0 || d->dst_height <= 0) return BANDCU_E_INVALID;
-  if (d->channels != 1 && d->channels != 3 && d->channels != 4) return BANDCU_E_INVALID;
+  if (d->channels < 1 || d->channels > 4) return BANDCU_E_INVALID;
   if (d->scale_mode < BANDCU_SCALE_COPY || d->scale_mode > BANDCU_SCALE_UP2_BILINEAR) return BANDCU_E_INVALID;
-  if (d->scale_mode >= BANDCU_SCALE_DOWN34 && (d->flavor != BANDCU_FLAVOR_PLANE || d->channels != 1))
+  const bool up2 = d->scale_mode == BANDCU_SCALE_UP2_LINEAR || d->scale_mode == BANDCU_SCALE_UP2_BILINEAR;
+  if (d->scale_mode >= BANDCU_SCALE_DOWN34 && !(up2 && d->src_kind == BANDCU_SRC_UV) &&
+      (d->flavor != BANDCU_FLAVOR_PLANE || d->channels != 1))
     return BANDCU_E_UNSUPPORTED;
   if (d->flavor == BANDCU_FLAVOR_PLANE && d->channels != 1) return BANDCU_E_UNSUPPORTED;
   if (d->normalize) {
@@ -68,7 +70,8 @@ static int validate_desc(const BandCuPlanDesc* d) {
   int ch;
   switch (d->cvt) {
     case BANDCU_CVT_NONE:
-      ch = d->src_kind == BANDCU_SRC_GRAY ? 1 : d->src_kind == BANDCU_SRC_RGB ? 3 : d->src_kind == BANDCU_SRC_RGBA ? 4 : -1;
+      ch = d->src_kind == BANDCU_SRC_GRAY ? 1 : d->src_kind == BANDCU_SRC_RGB ? 3 : d->src_kind == BANDCU_SRC_RGBA ? 4
+           : d->src_kind == BANDCU_SRC_UV ? 2 : -1;
       break;
     case BANDCU_CVT_YUV2RGB: ch = d->src_kind == BANDCU_SRC_YUV420 ? 3 : -1; break;
     case BANDCU_CVT_YUV2RGBA: ch = d->src_kind == BANDCU_SRC_YUV420 ? 4 : -1; break;

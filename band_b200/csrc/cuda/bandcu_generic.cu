@@ -34,6 +34,10 @@ __device__ __forceinline__ uint32_t fetch_px(const BandCuPlanDesc& d, const Fram
   switch (d.src_kind) {
     case BANDCU_SRC_GRAY:
       return p[col];
+    case BANDCU_SRC_UV: {
+      const uint8_t* q = p + col * 2;
+      return (uint32_t)q[0] | ((uint32_t)q[1] << 8);
+    }
     case BANDCU_SRC_RGB: {
       const uint8_t* q = p + col * 3;
       uint32_t R = q[0], G = q[1], B = q[2];
@@ -155,26 +159,36 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       return (uint32_t)((sum * mul) >> 16) & 0xFFu;
     }
     case BANDCU_SCALE_UP2_LINEAR:
-    case BANDCU_SCALE_UP2_BILINEAR: {  // ScalePlaneUp2_{Linear,Bilinear} + *_Any_C edges
+    case BANDCU_SCALE_UP2_BILINEAR: {  // Scale{Plane,UV}Up2_{Linear,Bilinear} + *_Any_C edges, per channel
       const int dw = d.dst_width, dh = d.dst_height, sh = d.vh;
       int cn, cf;  // near / far source column
       if (ox == 0) { cn = cf = 0; }
       else if (ox == dw - 1) { cn = cf = (dw - 1) / 2; }
       else { const int xx = (ox - 1) >> 1; if (ox & 1) { cn = xx; cf = xx + 1; } else { cn = xx + 1; cf = xx; } }
+      uint32_t out = 0;
       if (d.scale_mode == BANDCU_SCALE_UP2_LINEAR) {
         int row;
         if (dh == 1) row = (sh - 1) / 2;
         else row = (int)(((long long)32767 + (long long)oy * d.dy) >> 16);  // d.dy = FixedDiv(sh-1, dh-1)
-        const int n = (int)fetch_px(d, f, row, cn), fr = (int)fetch_px(d, f, row, cf);
-        return (uint32_t)((3 * n + fr + 2) >> 2);
+        const uint32_t pn = fetch_px(d, f, row, cn), pf = fetch_px(d, f, row, cf);
+        for (int k = 0; k < d.channels; ++k) {
+          const int n = (pn >> (8 * k)) & 0xFF, fr = (pf >> (8 * k)) & 0xFF;
+          out |= (uint32_t)((3 * n + fr + 2) >> 2) << (8 * k);
+        }
+        return out;
       }
       int rn, rf;  // near / far source row
       if (oy == 0) { rn = rf = 0; }
       else if (oy == dh - 1 && !(dh & 1)) { rn = rf = sh - 1; }
       else { const int yy = (oy - 1) >> 1; if (oy & 1) { rn = yy; rf = yy + 1; } else { rn = yy + 1; rf = yy; } }
-      const int A = (int)fetch_px(d, f, rn, cn), B = (int)fetch_px(d, f, rn, cf);
-      const int C = (int)fetch_px(d, f, rf, cn), D = (int)fetch_px(d, f, rf, cf);
-      return (uint32_t)((9 * A + 3 * B + 3 * C + D + 8) >> 4);
+      const uint32_t pa = fetch_px(d, f, rn, cn), pb = fetch_px(d, f, rn, cf);
+      const uint32_t pc = fetch_px(d, f, rf, cn), pd = fetch_px(d, f, rf, cf);
+      for (int k = 0; k < d.channels; ++k) {
+        const int A = (pa >> (8 * k)) & 0xFF, B = (pb >> (8 * k)) & 0xFF;
+        const int Cc = (pc >> (8 * k)) & 0xFF, D = (pd >> (8 * k)) & 0xFF;
+        out |= (uint32_t)((9 * A + 3 * B + 3 * Cc + D + 8) >> 4) << (8 * k);
+      }
+      return out;
     }
     default:
       return 0;

@@ -10,7 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libbandcu.so")
 
-SRC_GRAY, SRC_RGB, SRC_RGBA, SRC_YUV420 = 0, 1, 2, 3
+SRC_GRAY, SRC_RGB, SRC_RGBA, SRC_YUV420, SRC_UV = 0, 1, 2, 3, 4
 CVT_NONE, CVT_YUV2RGB, CVT_YUV2RGBA, CVT_YUV2GRAY, CVT_RGB2GRAY, CVT_RGBA2GRAY, CVT_RGBA2RGB = range(7)
 FLAVOR_ARGB, FLAVOR_PLANE = 0, 1
 (SCALE_COPY, SCALE_POINT, SCALE_BILINEAR_DOWN, SCALE_BILINEAR_UP, SCALE_BOX2, SCALE_VERTICAL, SCALE_DOWN34,

@@ -37,7 +37,13 @@ enum {
  * U and V base pointers plus a chroma pixel stride (2 = interleaved, 1 =
  * planar), exactly how GetYuvDataFromBuffer (libyuv_image_operator.cc:51-88)
  * describes them. */
-enum { BANDCU_SRC_GRAY = 0, BANDCU_SRC_RGB = 1, BANDCU_SRC_RGBA = 2, BANDCU_SRC_YUV420 = 3 };
+enum {
+  BANDCU_SRC_GRAY = 0,
+  BANDCU_SRC_RGB = 1,
+  BANDCU_SRC_RGBA = 2,
+  BANDCU_SRC_YUV420 = 3,
+  BANDCU_SRC_UV = 4, /* one interleaved chroma plane as a 2-channel image (UVScale inside NV12Scale, :422) */
+};
 
 /* Per-pixel conversion applied when a source pixel is fetched. */
 enum {
@@ -67,8 +73,8 @@ enum {
   BANDCU_SCALE_VERTICAL = 5,      /* ScalePlaneVertical */
   BANDCU_SCALE_DOWN34 = 6,        /* ScalePlaneDown34 (plane only) */
   BANDCU_SCALE_DOWN38 = 7,        /* ScalePlaneDown38 (plane only) */
-  BANDCU_SCALE_UP2_LINEAR = 8,    /* ScalePlaneUp2_Linear (plane only) */
-  BANDCU_SCALE_UP2_BILINEAR = 9,  /* ScalePlaneUp2_Bilinear (plane only) */
+  BANDCU_SCALE_UP2_LINEAR = 8,    /* ScalePlaneUp2_Linear / ScaleUVLinearUp2 (plane and UV only) */
+  BANDCU_SCALE_UP2_BILINEAR = 9,  /* ScalePlaneUp2_Bilinear / ScaleUVBilinearUp2 (plane and UV only) */
 };
 
 /* Output element types (Normalize / DataTypeConvert targets,
@@ -112,7 +118,7 @@ typedef struct BandCuPlanDesc {
   int max_y;          /* clamp for y (mode dependent) */
   int dst_width, dst_height;
   /* output */
-  int channels;       /* 1, 3 or 4 channels per output pixel */
+  int channels;       /* 1, 2 (UV), 3 or 4 channels per output pixel */
   int out_dtype;      /* BANDCU_DT_* */
   int normalize;      /* 0: store u8 results; 1: out = (T)((T)(v - mean) / std) */
   float mean, std_;

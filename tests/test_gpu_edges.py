@@ -137,3 +137,33 @@ def test_flip_all_formats(O, hv, fmt_name, W, H):
     if st == 0:
         assert info[:3] == tuple(winfo)
         assert_same_bits(got, want, "flip %s %s" % (hv, fmt_name))
+
+
+@pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21"])
+@pytest.mark.parametrize("W,H,dw,dh", [(64, 48, 22, 18), (64, 48, 32, 24), (64, 48, 48, 36), (64, 48, 24, 18),
+                                       (32, 24, 64, 48), (33, 25, 66, 50), (32, 24, 64, 24), (32, 24, 80, 70),
+                                       (65, 47, 23, 21), (64, 48, 64, 20), (64, 48, 16, 12), (66, 54, 22, 18),
+                                       (1920, 1080, 640, 360), (640, 480, 300, 300)])
+def test_resize_in_yuv_domain(O, fmt_name, W, H, dw, dh):
+    """ResizeYv / ResizeNv (libyuv_image_operator.cc:376-435): I420Scale = ScalePlane per plane, NV12Scale =
+    ScalePlane(Y) + UVScale(interleaved chroma) incl. their Down2/Down34/Down38/Up2/vertical special cases."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, W + 3 * dw)[0]
+    st, want, winfo = O.run_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt, cap=max(1 << 16, dw * dh * 4))
+    assert st == 0 and st2 == 0, (st, st2)
+    assert info[:3] == tuple(winfo)
+    assert_same_bits(got, want, "yuv resize %s %dx%d->%dx%d" % (fmt_name, W, H, dw, dh))
+
+
+@pytest.mark.parametrize("fmt_name", ["NV21", "YV12"])
+def test_resize_yuv_then_convert_chain(O, fmt_name):
+    """Chain order matters: Resize in the YUV domain THEN ColorSpaceConvert uses the plane blenders, not the ARGB one."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    W, H, d = 640, 480, 224
+    ops = [(O.OP_RESIZE, d, d), (O.OP_CSC, O.FMT_RGB), NORM]
+    fr = rand_frames(O, 2, W, H, fmt, 31)
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, O.DT_F32, (1, d, d, 3))
+    st2, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, d, d, 3))
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, "resize(yuv)->csc " + fmt_name)
