@@ -14,6 +14,8 @@ namespace cuda {
 namespace {
 
 constexpr BandCuAffine kIdentity = {0, 1, 0, 0, 0, 1};
+// host-only marker in View::cvt: the packed source becomes a 4:2:0 image (own kernel, not a per-fetch conversion)
+constexpr int kCvtRgbToYuv = 1000;
 
 bool IsIdentity(const BandCuAffine& m) {
   return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
@@ -210,6 +212,23 @@ absl::Status ChainLowering::EmitInto(int dst_slot, const ImageLayout& dst) {
     plan_->segments_.push_back(seg);
     return absl::OkStatus();
   }
+  if (v.cvt == kCvtRgbToYuv) {  // packed RGB / RGBA source -> 4:2:0 image
+    if (dst.num_planes != 3) return absl::InvalidArgumentError("YUV output buffer needs three planes");
+    if (v.src.dtype != DataType::kUInt8)
+      return absl::UnimplementedError("image stages on non-uint8 pixels are not supported");
+    seg.kind = Segment::Kind::kRgbToYuv;
+    BandCuRgbToYuvDesc& d = seg.rgb2yuv;
+    d.src_channels = Channels(v.src.format);
+    d.src_stride = static_cast<int>(v.src.row_stride[0]);
+    d.src_map = v.luma;
+    d.width = v.w;
+    d.height = v.h;
+    d.dst_stride_y = static_cast<int>(dst.row_stride[0]);
+    d.dst_stride_uv = static_cast<int>(dst.row_stride[1]);
+    d.dst_pixel_stride_uv = static_cast<int>(dst.pixel_stride[1]);
+    plan_->segments_.push_back(seg);
+    return absl::OkStatus();
+  }
   if (v.IsYuv() && v.scaled) {  // Resize in the YUV domain: every plane through its own libyuv scaler
     if (dst.num_planes != 3) return absl::InvalidArgumentError("YUV output buffer needs three planes");
     const bool nv = v.format == BufferFormat::kNV12 || v.format == BufferFormat::kNV21;
@@ -326,7 +345,7 @@ absl::Status ChainLowering::ApplyIndexMap(const BandCuAffine& luma, const BandCu
                                           int new_h) {
   if (view_->dtype != DataType::kUInt8)
     return absl::UnimplementedError("Crop/Rotate/Flip on non-uint8 pixels are not supported");
-  if (view_->scaled || view_->normalized) RETURN_IF_ERROR(Flush());
+  if (view_->scaled || view_->normalized || view_->cvt == kCvtRgbToYuv) RETURN_IF_ERROR(Flush());
   View& v = *view_;
   terminal_noop_ = false;
   v.luma = Compose(v.luma, luma);
@@ -416,8 +435,9 @@ absl::Status ChainLowering::ConvertColor(BufferFormat to) {
   } else if (from == BufferFormat::kRGBA && to == BufferFormat::kGrayScale) {
     v.cvt = BANDCU_CVT_RGBA2GRAY;
   } else if ((from == BufferFormat::kRGB || from == BufferFormat::kRGBA) && Buffer::IsYUV(to)) {
-    return absl::UnimplementedError(absl::StrFormat("ColorSpaceConvert %s -> %s has no CUDA kernel yet",
-                                                    ToString(from), ToString(to)));
+    // RAWToI420 / ABGRTo{NV12,NV21,I420}: every target layout receives the same Y/U/V samples (the reference's
+    // RGB -> NV route goes through a temporary I420 image and a sample-preserving repack, :536-583)
+    v.cvt = kCvtRgbToYuv;
   } else {
     return absl::InternalError(absl::StrFormat("Format %s -> %s is not supported.", ToString(from), ToString(to)));
   }
@@ -720,6 +740,14 @@ absl::Status FusedPlan::RunSegments(int first, int last) {
           const SlotPointers s = Resolve(seg.src_slot, f), d = Resolve(seg.dst_slot, f);
           const BandCuYuvPtrs p = {s.y, s.u, s.v, d.y, d.u, d.v};
           if (bandcu_yuv_map(&seg.yuv, &p, stream_) != BANDCU_OK) return CudaError("bandcu_yuv_map");
+        }
+        break;
+      }
+      case Segment::Kind::kRgbToYuv: {
+        for (int f = first; f < last; ++f) {
+          const SlotPointers s = Resolve(seg.src_slot, f), d = Resolve(seg.dst_slot, f);
+          const BandCuRgbToYuvPtrs p = {s.y, d.y, d.u, d.v};
+          if (bandcu_rgb_to_yuv420(&seg.rgb2yuv, &p, stream_) != BANDCU_OK) return CudaError("bandcu_rgb_to_yuv420");
         }
         break;
       }

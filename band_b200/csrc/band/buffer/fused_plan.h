@@ -44,7 +44,7 @@ struct ImageLayout {
 enum : int { kSlotInput = -1, kSlotOutput = -2 };  // otherwise: index into FusedPlan::scratch
 
 struct Segment {
-  enum class Kind { kPixel, kYuvMap, kYuvScale, kElementwise };
+  enum class Kind { kPixel, kYuvMap, kYuvScale, kRgbToYuv, kElementwise };
   Kind kind = Kind::kPixel;
   int src_slot = kSlotInput;
   int dst_slot = kSlotOutput;
@@ -53,6 +53,8 @@ struct Segment {
   BandCuPlan* plan = nullptr;
   // kYuvMap
   BandCuYuvMapDesc yuv{};
+  // kRgbToYuv (ColorSpaceConvert RGB/RGBA -> NV12/NV21/YV12/YV21, libyuv_image_operator.cc:523-587,621-674)
+  BandCuRgbToYuvDesc rgb2yuv{};
   // kYuvScale (Resize of a 4:2:0 buffer: I420Scale / NV12Scale, libyuv_image_operator.cc:376-435): one plan per
   // plane -- [0] luma, [1] U (or the interleaved UV plane), [2] V (planar only)
   BandCuPlan* plane_plan[3] = {nullptr, nullptr, nullptr};

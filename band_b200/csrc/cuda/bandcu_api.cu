@@ -237,6 +237,16 @@ int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void
   return BANDCU_OK;
 }
 
+int bandcu_rgb_to_yuv420(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtrs* ptrs, void* stream) {
+  if (!desc || !ptrs || !ptrs->src || !ptrs->dy || !ptrs->du || !ptrs->dv)
+    return fail(BANDCU_E_INVALID, "rgb_to_yuv420: null argument");
+  if (desc->width <= 0 || desc->height <= 0 || (desc->src_channels != 3 && desc->src_channels != 4))
+    return fail(BANDCU_E_INVALID, "rgb_to_yuv420: bad descriptor");
+  int e = launch_rgb_to_yuv(*desc, *ptrs, (cudaStream_t)stream);
+  if (e != 0) return fail(e, "rgb_to_yuv420: launch");
+  return BANDCU_OK;
+}
+
 int bandcu_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean, float std_,
                      void* stream) {
   if (!in || !out || n < 0) return fail(BANDCU_E_INVALID, "normalize: bad arguments");

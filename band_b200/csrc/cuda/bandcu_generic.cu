@@ -297,6 +297,55 @@ int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream
 }
 
 // ---------------------------------------------------------------------------
+// RGB / RGBA -> 4:2:0: RAWToI420 / ABGRToI420 / ABGRToNV12 / ABGRToNV21
+// (libyuv_image_operator.cc:570,:626,:643,:661). libyuv row_common.cc, default C build:
+//   Y = (66 R + 129 G + 25 B + 0x1080) >> 8
+//   per 2x2 block (edge samples repeated): aX = (sum of the four X + 1) >> 1   ("2x" average)
+//   U = (56 aB - 37 aG - 19 aR + 0x8080) >> 8 ;  V = (56 aR - 47 aG - 9 aB + 0x8080) >> 8
+// One thread per chroma sample: it also writes the block's (up to) four luma samples.
+// ---------------------------------------------------------------------------
+struct RgbToYuvParams {
+  BandCuRgbToYuvDesc d;
+  BandCuRgbToYuvPtrs p;
+};
+__global__ void __launch_bounds__(256) rgb_to_yuv420_kernel(const __grid_constant__ RgbToYuvParams P) {
+  const BandCuRgbToYuvDesc& d = P.d;
+  const int cx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int cy = blockIdx.y * blockDim.y + threadIdx.y;
+  const int cw = (d.width + 1) >> 1, chh = (d.height + 1) >> 1;
+  if (cx >= cw || cy >= chh) return;
+  const uint8_t* src = (const uint8_t*)P.p.src;
+  uint8_t* dy = (uint8_t*)P.p.dy;
+  const int x0 = 2 * cx, y0 = 2 * cy;
+  const int x1 = min(x0 + 1, d.width - 1), y1 = min(y0 + 1, d.height - 1);
+  int sr = 0, sg = 0, sb = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = (k & 2) ? y1 : y0, c = (k & 1) ? x1 : x0;
+    const uint8_t* q = src + (long long)map_row(d.src_map, r, c) * d.src_stride +
+                       (long long)map_col(d.src_map, r, c) * d.src_channels;
+    const int R = q[0], G = q[1], B = q[2];
+    sr += R; sg += G; sb += B;
+    const bool fresh = !((k & 1) && x1 == x0) && !((k & 2) && y1 == y0);  // a repeated edge sample is not a pixel
+    if (fresh) dy[(long long)r * d.dst_stride_y + c] = (uint8_t)((66 * R + 129 * G + 25 * B + 0x1080) >> 8);
+  }
+  const int ar = (sr + 1) >> 1, ag = (sg + 1) >> 1, ab = (sb + 1) >> 1;
+  const long long o = (long long)cy * d.dst_stride_uv + (long long)cx * d.dst_pixel_stride_uv;
+  ((uint8_t*)P.p.du)[o] = (uint8_t)((56 * ab - 37 * ag - 19 * ar + 0x8080) >> 8);
+  ((uint8_t*)P.p.dv)[o] = (uint8_t)((56 * ar - 47 * ag - 9 * ab + 0x8080) >> 8);
+}
+int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, cudaStream_t stream) {
+  RgbToYuvParams P;
+  P.d = d;
+  P.p = p;
+  dim3 block(32, 8, 1);
+  dim3 grid(((d.width + 1) / 2 + 31) / 32, ((d.height + 1) / 2 + 7) / 8, 1);
+  rgb_to_yuv420_kernel<<<grid, block, 0, stream>>>(P);
+  count_launch();
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // Element-wise Normalize / DataTypeConvert over any dtype pair
 // (common_operator.cc:24-65): out[i] = static_cast<Out>((in[i] - mean)) / std.
 // The difference is computed in float for integer/float inputs and in double for

@@ -59,6 +59,16 @@ class YuvPtrs(C.Structure):
                 ("dv", C.c_void_p)]
 
 
+class RgbToYuvDesc(C.Structure):
+    _fields_ = [("src_channels", C.c_int), ("src_stride", C.c_int), ("src_map", Affine), ("width", C.c_int),
+                ("height", C.c_int), ("dst_stride_y", C.c_int), ("dst_stride_uv", C.c_int),
+                ("dst_pixel_stride_uv", C.c_int)]
+
+
+class RgbToYuvPtrs(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dy", C.c_void_p), ("du", C.c_void_p), ("dv", C.c_void_p)]
+
+
 class BandCuError(RuntimeError):
     pass
 
@@ -82,6 +92,7 @@ def lib():
     L.bandcu_plan_run.argtypes = [vp, C.POINTER(Frame), ci, vp]
     L.bandcu_launch_count.restype = ll
     L.bandcu_yuv_map.argtypes = [C.POINTER(YuvMapDesc), C.POINTER(YuvPtrs), vp]
+    L.bandcu_rgb_to_yuv420.argtypes = [C.POINTER(RgbToYuvDesc), C.POINTER(RgbToYuvPtrs), vp]
     L.bandcu_normalize.argtypes = [vp, ci, vp, ci, ll, C.c_float, C.c_float, vp]
     L.bandcu_device_count.argtypes = [C.POINTER(ci)]
     L.bandcu_set_device.argtypes = [ci]
@@ -115,7 +126,7 @@ def check(code, what=""):
 
 EXPORTED = [
     "bandcu_plan_create", "bandcu_plan_destroy", "bandcu_plan_is_fast", "bandcu_plan_run_strided", "bandcu_plan_run",
-    "bandcu_launch_count", "bandcu_yuv_map", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
+    "bandcu_launch_count", "bandcu_yuv_map", "bandcu_rgb_to_yuv420", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
     "bandcu_malloc", "bandcu_free", "bandcu_host_alloc", "bandcu_host_free", "bandcu_memcpy_h2d", "bandcu_memcpy_d2h",
     "bandcu_memcpy_d2d", "bandcu_memset", "bandcu_stream_create", "bandcu_stream_destroy", "bandcu_stream_sync",
     "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",

@@ -165,6 +165,22 @@ typedef struct BandCuYuvPtrs {
 } BandCuYuvPtrs;
 BANDCU_API int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void* stream);
 
+/* ---- RGB / RGBA -> 4:2:0 (ColorSpaceConvert to NV12/NV21/YV12/YV21: RAWToI420 :570, ABGRToNV12 :626,
+ * ABGRToNV21 :643, ABGRToI420 :661; libyuv's default C rows RGBToY / RGB2xToU / RGB2xToV with the 2x2
+ * chroma average). One launch per frame; a pending Crop/Rotate/Flip of the packed source folds into src_map. */
+typedef struct BandCuRgbToYuvDesc {
+  int src_channels;            /* 3 (RGB) or 4 (RGBA: bytes R,G,B,A) */
+  int src_stride;              /* bytes between source rows */
+  BandCuAffine src_map;        /* converted-image (r,c) -> source (row, col) */
+  int width, height;           /* dims of the converted image */
+  int dst_stride_y, dst_stride_uv, dst_pixel_stride_uv;
+} BandCuRgbToYuvDesc;
+typedef struct BandCuRgbToYuvPtrs {
+  const void* src;
+  void *dy, *du, *dv;
+} BandCuRgbToYuvPtrs;
+BANDCU_API int bandcu_rgb_to_yuv420(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtrs* ptrs, void* stream);
+
 /* ---- element-wise Normalize / DataTypeConvert on an arbitrary dtype pair
  * (common_operator.cc:24-65); n elements, contiguous. ----------------------- */
 BANDCU_API int bandcu_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean,

@@ -167,3 +167,49 @@ def test_resize_yuv_then_convert_chain(O, fmt_name):
     st2, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, d, d, 3))
     assert st == 0 and st2 == 0
     assert_same_bits(got, want, "resize(yuv)->csc " + fmt_name)
+
+
+@pytest.mark.parametrize("dst_name", ["NV12", "NV21", "YV12", "YV21"])
+@pytest.mark.parametrize("src_name,W,H", [("RGB", 64, 48), ("RGBA", 64, 48), ("RGB", 65, 47), ("RGBA", 33, 21), ("RGB", 2, 2),
+                                          ("RGBA", 1, 1), ("RGB", 1920, 1080)])
+def test_rgb_to_yuv_conversions(O, src_name, dst_name, W, H):
+    """ConvertFromRgb / ConvertFromRgba -> 4:2:0 (libyuv_image_operator.cc:523-587,621-674): RAWToI420, ABGRToNV12,
+    ABGRToNV21, ABGRToI420 with libyuv's default C rows (parity unpinned: no reference test covers them)."""
+    sf, df = getattr(O, "FMT_" + src_name), getattr(O, "FMT_" + dst_name)
+    fr = rand_frames(O, 1, W, H, sf, 5 * W + H)[0]
+    st, want, winfo = O.run_op((O.OP_CSC, df), fr, W, H, sf)
+    st2, got, info = gpu_op((O.OP_CSC, df), fr, W, H, sf)
+    assert st == 0 and st2 == 0, (st, st2)
+    assert info[:3] == tuple(winfo)
+    assert_same_bits(got, want, "%s->%s %dx%d" % (src_name, dst_name, W, H))
+
+
+@pytest.mark.parametrize("src_name", ["NV12", "NV21", "YV12", "YV21"])
+@pytest.mark.parametrize("dst_name", ["NV12", "NV21", "YV12", "YV21", "RGBA", "GRAY"])
+def test_yuv_repacks_and_other_targets(O, src_name, dst_name):
+    """YUV <-> YUV repacks (:125-162,:213-250,:302-367), YUV -> RGBA (..ToABGR) and YUV -> gray (Y-plane copy)."""
+    if src_name == dst_name:
+        pytest.skip("same format is an error in both implementations (checked elsewhere)")
+    sf, df = getattr(O, "FMT_" + src_name), getattr(O, "FMT_" + dst_name)
+    W, H = 37, 23
+    fr = rand_frames(O, 1, W, H, sf, 99)[0]
+    st, want, winfo = O.run_op((O.OP_CSC, df), fr, W, H, sf)
+    st2, got, info = gpu_op((O.OP_CSC, df), fr, W, H, sf)
+    assert st == st2
+    if st == 0:
+        assert info[:3] == tuple(winfo)
+        assert_same_bits(got, want, "%s->%s" % (src_name, dst_name))
+
+
+def test_crop_then_rgb_to_yuv_chain(O):
+    """A pending index map on the packed source folds into the RGB -> YUV launch."""
+    W, H = 70, 50
+    fr = rand_frames(O, 1, W, H, O.FMT_RGB, 5)[0]
+    ops = [(O.OP_ROTATE, 90), (O.OP_CROP, 3, 5, 40, 60), (O.OP_CSC, O.FMT_NV21)]
+    cur, w, h, f = fr, W, H, O.FMT_RGB
+    for op in ops:
+        st, cur, (w, h, f) = O.run_op(op, cur, w, h, f)
+        assert st == 0
+    st, got, info = gpu_image_chain(ops, fr, W, H, O.FMT_RGB, O.FMT_NV21, O.DT_U8, w, h)
+    assert st == 0 and info[:3] == (w, h, O.FMT_NV21)
+    assert_same_bits(got, cur, "rotate+crop+rgb->nv21")
