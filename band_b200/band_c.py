@@ -37,7 +37,7 @@ EXPORTED = [
     # additive
     "BandTensorCreate", "BandTensorGetMemorySpace", "BandBufferSetFromDeviceRawData",
     "BandBufferSetFromDeviceYUVData", "BandImageProcessorProcessBatch", "BandImageProcessorProcessBatchAsync",
-    "BandImageProcessorSynchronize", "BandImageProcessorGetStream", "BandImageProcessorIsFused",
+    "BandImageProcessorSynchronize", "BandImageProcessorProcessBuffers", "BandImageProcessorGetStream", "BandImageProcessorIsFused",
     "BandCudaGetDeviceCount", "BandCudaSetDevice", "BandHostAlloc", "BandHostFree", "BandDeviceAlloc",
     "BandDeviceFree", "BandCopyToDevice", "BandCopyToHost", "BandCudaLaunchCount", "BandGetLastError",
 ]
@@ -92,6 +92,7 @@ def lib():
     L.BandImageProcessorProcessBatch.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
     L.BandImageProcessorProcessBatchAsync.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
     L.BandImageProcessorSynchronize.argtypes = [vp]
+    L.BandImageProcessorProcessBuffers.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz, ci]
     L.BandImageProcessorGetStream.argtypes = [vp]
     L.BandImageProcessorGetStream.restype = vp
     L.BandImageProcessorIsFused.argtypes = [vp]

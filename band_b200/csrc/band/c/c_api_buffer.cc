@@ -206,6 +206,24 @@ BandStatus BandImageProcessorProcessBatchAsync(BandImageProcessor* image_process
   return ProcessBatchImpl(image_processor, buffers, target_tensors, count, true);
 }
 
+BandStatus BandImageProcessorProcessBuffers(BandImageProcessor* image_processor, BandBuffer* const* inputs,
+                                            BandBuffer* const* outputs, size_t count, int async) {
+  if (!image_processor || !inputs || !outputs) return kBandErr;
+  thread_local std::vector<const Buffer*> in;
+  thread_local std::vector<Buffer*> out;
+  in.resize(count);
+  out.resize(count);
+  for (size_t i = 0; i < count; ++i) {
+    if (!inputs[i] || !inputs[i]->impl || !outputs[i] || !outputs[i]->impl) return kBandErr;
+    in[i] = inputs[i]->impl.get();
+    out[i] = outputs[i]->impl.get();
+  }
+  absl::Status status = async ? image_processor->impl->ProcessBatchAsync(in.data(), out.data(), count)
+                              : image_processor->impl->ProcessBatch(in.data(), out.data(), count);
+  if (!status.ok()) g_last_error = status.ToString();
+  return status.ok() ? kBandOk : kBandErr;
+}
+
 BandStatus BandImageProcessorSynchronize(BandImageProcessor* image_processor) {
   if (!image_processor) return kBandErr;
   absl::Status status = image_processor->impl->Synchronize();

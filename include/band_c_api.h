@@ -152,6 +152,13 @@ BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatchAsync(BandImage
                                                                        BandTensor* const* target_tensors,
                                                                        size_t count);
 BAND_CAPI_EXPORT extern BandStatus BandImageProcessorSynchronize(BandImageProcessor* image_processor);
+/* n frames -> n IMAGE buffers (any BandBufferFormat, e.g. gray or NV12 outputs that a tensor cannot describe):
+ * the C++ BufferProcessor::Process(input, output) of the reference, which its C API does not expose. Enqueue only
+ * when `async` is non-zero. */
+BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBuffers(BandImageProcessor* image_processor,
+                                                                    BandBuffer* const* inputs,
+                                                                    BandBuffer* const* outputs, size_t count,
+                                                                    int async);
 /* cudaStream_t the processor launches on (NULL before its first Process*); lets a harness bracket the
  * launches with CUDA events. */
 BAND_CAPI_EXPORT extern void* BandImageProcessorGetStream(BandImageProcessor* image_processor);

@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""Secondary measurements: every BASELINE.json config (C1..C5) on one GPU, device-resident, through the Band C API.
+
+  python scripts/bench_configs.py [--configs c1,c2,c3,c4,c5] [--steps K] [--cpu] > profiles/rNN_configs.jsonl
+
+One JSON line per case: frames/s (CUDA events on the processor's launch stream), algorithmic bytes per frame
+(input frame once in full + output), achieved GB/s and fraction of the measured HBM copy bandwidth,
+kernel launches per step, and (with --cpu) the oracle port on ONE host thread for the same chain. bench.py stays the
+driver-facing headline (north star); this script is the evidence for the other rows of DESIGN.md's table.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from band_b200 import band_c as B          # noqa: E402
+from band_b200 import cuda_shim as S       # noqa: E402
+from band_b200 import hotpath              # noqa: E402
+
+
+def peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        return 6650.0
+
+
+def event():
+    e = C.c_void_p()
+    S.check(S.lib().bandcu_event_create(C.byref(e)), "event")
+    return e
+
+
+def elapsed(a, b):
+    ms = C.c_float()
+    S.check(S.lib().bandcu_event_elapsed_ms(a, b, C.byref(ms)), "elapsed")
+    return float(ms.value)
+
+
+class ImageBatch:
+    """n device frames -> n device IMAGE buffers (for outputs a tensor cannot describe: gray, YUV)."""
+
+    def __init__(self, ops, n, W, H, fmt, out_fmt, out_w, out_h):
+        L = B.lib()
+        self.n = n
+        self.proc = B.ImageProcessor(ops)
+        self.fb = B.frame_bytes(W, H, fmt)
+        self.pitch = (self.fb + 255) // 256 * 256
+        self.ob = B.frame_bytes(out_w, out_h, out_fmt)
+        self.opitch = (self.ob + 255) // 256 * 256
+        self.din = L.BandDeviceAlloc(self.pitch * n)
+        self.dout = L.BandDeviceAlloc(self.opitch * n)
+        assert self.din and self.dout
+        self.inb = [B.Buffer().set_raw(self.din + i * self.pitch, W, H, fmt, device=True) for i in range(n)]
+        self.outb = [B.Buffer().set_raw(self.dout + i * self.opitch, out_w, out_h, out_fmt, device=True) for i in range(n)]
+        self._ia = (C.c_void_p * n)(*[b.handle for b in self.inb])
+        self._oa = (C.c_void_p * n)(*[b.handle for b in self.outb])
+
+    def fill(self, uniq):
+        L = B.lib()
+        for i in range(self.n):
+            assert L.BandCopyToDevice(self.din + i * self.pitch, uniq[i % len(uniq)].ctypes.data, self.fb) == B.kBandOk
+
+    def step(self, async_=True):
+        st = B.lib().BandImageProcessorProcessBuffers(self.proc.handle, self._ia, self._oa, self.n, 1 if async_ else 0)
+        assert st == B.kBandOk, B.last_error()
+
+    def close(self):
+        for b in self.inb + self.outb:
+            b.close()
+        self.proc.close()
+        B.lib().BandDeviceFree(self.din)
+        B.lib().BandDeviceFree(self.dout)
+
+
+def time_steps(step_async, sync, stream_of, steps, warmup=3):
+    for _ in range(warmup):
+        step_async()
+    sync()
+    stream = stream_of()
+    e0, e1 = event(), event()
+    L = S.lib()
+    n0 = hotpath.launch_count()
+    S.check(L.bandcu_event_record(e0, stream), "rec")
+    for _ in range(steps):
+        step_async()
+    S.check(L.bandcu_event_record(e1, stream), "rec")
+    sync()
+    return elapsed(e0, e1) / steps, (hotpath.launch_count() - n0) / steps
+
+
+def cpu_fps(ops_oracle, W, H, fmt_o, out_dt, out_dims, seconds=2.0):
+    """Oracle port, ONE host thread, bounded sample."""
+    from oracle import oracle as O
+    rng = np.random.default_rng(1)
+    frame = rng.integers(0, 256, size=O.frame_bytes(W, H, fmt_o), dtype=np.uint8)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        if out_dims is None:
+            cur, w, h, f = frame, W, H, fmt_o
+            for op in ops_oracle:
+                st, cur, (w, h, f) = O.run_op(op, cur, w, h, f)
+                assert st == 0
+        else:
+            st, _ = O.run_chain(ops_oracle, frame, W, H, fmt_o, out_dt, out_dims)
+            assert st == 0, st
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > seconds and n >= 2:
+            return n / dt
+
+
+NORM_O = (5, 0, 0, 0, 0, 127.5, 127.5)
+
+
+def tensor_case(name, W, H, fmt, dw, dh, f32, n, steps, cpu, pre_ops=(), pre_ops_o=()):
+    """chain [pre_ops] -> CSC(RGB) -> Resize -> [Normalize] into device tensors."""
+    ops = list(pre_ops) + hotpath.chain_ops(dw, dh, f32)
+    dt = np.float32 if f32 else np.uint8
+    rb = hotpath.ResidentBatch(ops, n, W, H, fmt, dt, (1, dh, dw, 3))
+    rng = np.random.default_rng(3)
+    uniq = rng.integers(0, 256, size=(4, rb.frame_bytes), dtype=np.uint8)
+    L = B.lib()
+    for i in range(n):
+        assert L.BandCopyToDevice(rb.dev_frames + i * rb.frame_pitch, uniq[i % 4].ctypes.data, rb.frame_bytes) == B.kBandOk
+    rb.step()
+    ms, launches = time_steps(lambda: rb.proc.process_batch_async(rb._ba, rb._ta, n), rb.proc.synchronize,
+                              lambda: rb.proc.stream, steps)
+    alg = rb.frame_bytes + rb.out_bytes
+    fps = n / (ms * 1e-3)
+    line = {"case": name, "frames_per_s": fps, "ms_per_step": ms, "frames_per_step": n, "launches_per_step": launches,
+            "fused_single_launch": rb.is_fused, "alg_bytes_per_frame": alg, "achieved_GBps": fps * alg / 1e9,
+            "frac_of_measured_hbm": fps * alg / 1e9 / peak()}
+    if cpu:
+        from oracle import oracle as O
+        o_ops = list(pre_ops_o) + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh)] + ([NORM_O] if f32 else [])
+        line["cpu_oracle_1thread_fps"] = cpu_fps(o_ops, W, H, getattr(O, "FMT_" + fmt), O.DT_F32 if f32 else O.DT_U8,
+                                                 (1, dh, dw, 3))
+    rb.close()
+    return line
+
+
+def c1_latency(steps):
+    """Single 640x480 NV21 frame -> 224x224 f32: latency of one synchronous BandImageProcessorProcess call."""
+    W, H = 640, 480
+    ops = hotpath.chain_ops(224, 224, True)
+    out = []
+    for resident in (True, False):
+        proc = B.ImageProcessor(ops)
+        t = B.Tensor(np.float32, (1, 224, 224, 3), device=resident)
+        fb = B.frame_bytes(W, H, B.kBandNV21)
+        rng = np.random.default_rng(5)
+        frame = rng.integers(0, 256, size=fb, dtype=np.uint8)
+        L = B.lib()
+        if resident:
+            dev = L.BandDeviceAlloc(fb)
+            L.BandCopyToDevice(dev, frame.ctypes.data, fb)
+            buf = B.Buffer().set_raw(dev, W, H, B.kBandNV21, device=True)
+        else:
+            host = L.BandHostAlloc(fb)
+            C.memmove(host, frame.ctypes.data, fb)
+            buf = B.Buffer().set_raw(host, W, H, B.kBandNV21)
+        for _ in range(20):
+            assert proc.process(buf, t) == B.kBandOk
+        ts = []
+        for _ in range(max(steps, 200)):
+            t0 = time.perf_counter()
+            proc.process(buf, t)
+            ts.append((time.perf_counter() - t0) * 1e6)
+        ts = np.array(ts)
+        out.append({"case": "c1_single_640x480_nv21_to_224_f32_" + ("resident" if resident else "pinned_host"),
+                    "latency_us_median": float(np.median(ts)), "latency_us_p10": float(np.percentile(ts, 10)),
+                    "latency_us_p90": float(np.percentile(ts, 90)), "note": "host clock around the synchronous call"})
+        buf.close(); t.close(); proc.close()
+    return out
+
+
+def c5_cases(steps, cpu):
+    lines = []
+    from oracle import oracle as O
+    for S_, D_ in [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (64, 128), (64, 256), (64, 512),
+                   (64, 1024), (64, 2048)]:
+        n = int(max(8, min(2048, 1.0e9 // (4 * S_ * S_ + 3 * D_ * D_))))
+        # (i) AutoConvert (empty builder) into a u8 RGB tensor
+        rb = hotpath.ResidentBatch([], n, S_, S_, "RGBA", np.uint8, (1, D_, D_, 3))
+        rng = np.random.default_rng(7)
+        uniq = rng.integers(0, 256, size=(2, rb.frame_bytes), dtype=np.uint8)
+        for i in range(n):
+            B.lib().BandCopyToDevice(rb.dev_frames + i * rb.frame_pitch, uniq[i % 2].ctypes.data, rb.frame_bytes)
+        rb.step()
+        ms, launches = time_steps(lambda: rb.proc.process_batch_async(rb._ba, rb._ta, n), rb.proc.synchronize,
+                                  lambda: rb.proc.stream, steps)
+        alg = 4 * S_ * S_ + 3 * D_ * D_
+        fps = n / (ms * 1e-3)
+        line = {"case": "c5_rgba_%d_to_rgb_%d" % (S_, D_), "frames_per_s": fps, "ms_per_step": ms, "frames_per_step": n,
+                "launches_per_step": launches, "alg_bytes_per_frame": alg, "achieved_GBps": fps * alg / 1e9,
+                "frac_of_measured_hbm": fps * alg / 1e9 / peak()}
+        if cpu:
+            line["cpu_oracle_1thread_fps"] = cpu_fps([(O.OP_AUTO,)], S_, S_, O.FMT_RGBA, O.DT_U8, (1, D_, D_, 3), 1.0)
+        lines.append(line)
+        rb.close()
+        # (ii) CSC(Gray) -> Resize into a gray image buffer
+        ops = [(B.BAND_COLOR_SPACE_CONVERT, B.kBandGrayScale), (B.BAND_RESIZE, D_, D_)]
+        ib = ImageBatch(ops, n, S_, S_, B.kBandRGBA, B.kBandGrayScale, D_, D_)
+        ib.fill(uniq)
+        ib.step(False)
+        ms, launches = time_steps(ib.step, ib.proc.synchronize, lambda: ib.proc.stream, steps)
+        alg = 4 * S_ * S_ + D_ * D_
+        fps = n / (ms * 1e-3)
+        line = {"case": "c5_rgba_%d_to_gray_%d" % (S_, D_), "frames_per_s": fps, "ms_per_step": ms, "frames_per_step": n,
+                "launches_per_step": launches, "alg_bytes_per_frame": alg, "achieved_GBps": fps * alg / 1e9,
+                "frac_of_measured_hbm": fps * alg / 1e9 / peak()}
+        if cpu:
+            line["cpu_oracle_1thread_fps"] = cpu_fps([(O.OP_CSC, O.FMT_GRAY), (O.OP_RESIZE, D_, D_)], S_, S_, O.FMT_RGBA,
+                                                     None, None, 1.0)
+        lines.append(line)
+        ib.close()
+    return lines
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="c1,c2,c3,c4,c5")
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--device", type=int, default=0)
+    a = ap.parse_args()
+    hotpath.set_device(a.device)
+    want = set(a.configs.split(","))
+    out = []
+    if "ns" in want or "c4" in want:
+        out.append(tensor_case("north_star_1080p_nv12_to_224_f32", 1920, 1080, "NV12", 224, 224, True, 1024, a.steps, a.cpu))
+    if "c1" in want:
+        out += c1_latency(a.steps)
+        out.append(tensor_case("c1_batch_640x480_nv21_to_224_f32", 640, 480, "NV21", 224, 224, True, 4096, a.steps, a.cpu))
+    if "c2" in want:
+        out.append(tensor_case("c2_1080p_nv12_to_300_u8", 1920, 1080, "NV12", 300, 300, False, 1024, a.steps, a.cpu))
+    if "c3" in want:
+        from oracle import oracle as O
+        out.append(tensor_case("c3_4k_yv12_rot90_crop_to_512_f32", 3840, 2160, "YV12", 512, 512, True, 128, a.steps, a.cpu,
+                               pre_ops=[(B.BAND_ROTATE, 90), (B.BAND_CROP, 0, 840, 2159, 2999)],
+                               pre_ops_o=[(O.OP_ROTATE, 90), (O.OP_CROP, 0, 840, 2159, 2999)]))
+    if "c4" in want:
+        parts = [tensor_case("c4_1080p_nv21_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 683, a.steps, a.cpu),
+                 tensor_case("c4_1080p_nv21_to_300_u8", 1920, 1080, "NV21", 300, 300, False, 683, a.steps, a.cpu),
+                 tensor_case("c4_1080p_nv21_to_513_f32", 1920, 1080, "NV21", 513, 513, True, 682, a.steps, a.cpu)]
+        out += parts
+        tot_frames = sum(p["frames_per_step"] for p in parts)
+        tot_ms = sum(p["ms_per_step"] for p in parts)
+        tot_bytes = sum(p["frames_per_step"] * p["alg_bytes_per_frame"] for p in parts)
+        out.append({"case": "c4_mixed_2048_frames_per_gpu (224 f32 / 300 u8 / 513 f32 round-robin, three launches)",
+                    "frames_per_s": tot_frames / (tot_ms * 1e-3), "ms_per_step": tot_ms, "frames_per_step": tot_frames,
+                    "achieved_GBps": tot_bytes / (tot_ms * 1e-3) / 1e9,
+                    "frac_of_measured_hbm": tot_bytes / (tot_ms * 1e-3) / 1e9 / peak()})
+    if "c5" in want:
+        out += c5_cases(a.steps, a.cpu)
+    for line in out:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
