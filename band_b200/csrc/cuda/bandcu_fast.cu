@@ -47,7 +47,6 @@ struct FastParams {
   int x0, y0, dx, dy, max_y, linear;
   int dw, dh;
   int R;               // output rows per work item
-  int G;               // consumer row groups
   int S;               // ring depth
   int cols;            // consumer threads per row group (multiple of 32)
   int passes;          // column passes per row
@@ -64,7 +63,7 @@ struct FastParams {
 struct FastPlan {
   void* lut_dev;
   int num_sms;
-  int R, G, S;
+  int R, S;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -117,12 +116,13 @@ __device__ __forceinline__ RowSel row_select(const FastParams& P, int oy) {
 constexpr int kOffFull = 0;                              // kMaxStages x u64
 constexpr int kOffEmpty = 8 * kMaxStages;                // kMaxStages x u64
 constexpr int kOffRowInfo = 16 * kMaxStages;             // kMaxStages x kMaxRows x u32
-constexpr int kOffLut = kOffRowInfo + 4 * kMaxStages * kMaxRows;  // 256 x f32
-constexpr int kOffStages = ((kOffLut + 1024 + 127) / 128) * 128;
+constexpr int kOffLut = kOffRowInfo + 4 * kMaxStages * kMaxRows;  // replicated 256 x f32 table
+constexpr int kLutBytes = 256 * 4 * 8;  // 256 entries x kLutCopies
+constexpr int kOffStages = ((kOffLut + kLutBytes + 127) / 128) * 128;
 
 // Producer (warp 0): stage the source rows of one work item. Slot layout per output row j:
 //   [4j+0] luma yi   [4j+1] luma yi+1 (only if yf)   [4j+2] chroma ct   [4j+3] chroma cb (only if yf && cb != ct)
-// rowinfo[j] = yf | (bottom chroma slot: 2 or 3) << 8.
+// rowinfo[j] = yf | 0x100 when the bottom luma row has its own chroma row (slot 3).
 template <bool VU>
 __device__ __forceinline__ void produce_item(const FastParams& P, long long item, uint8_t* stage, uint32_t* rowinfo,
                                              uint64_t* full) {
@@ -136,7 +136,7 @@ __device__ __forceinline__ void produce_item(const FastParams& P, long long item
   const int ybytes = P.W, cbytes = ((P.W + 1) >> 1) << 1;
   if (lane < nrows) {
     const RowSel s = row_select(P, oy0 + lane);
-    rowinfo[lane] = (uint32_t)s.yf | ((s.yf && s.cb != s.ct) ? (3u << 8) : (2u << 8));
+    rowinfo[lane] = (uint32_t)s.yf | ((s.yf && s.cb != s.ct) ? 0x100u : 0u);
   }
   __syncwarp();
   if (P.use_bulk) {
@@ -179,30 +179,64 @@ __device__ __forceinline__ void produce_item(const FastParams& P, long long item
 }
 
 // ---- packed pixel arithmetic ---------------------------------------------------
-// One source row, the LEFT and RIGHT source pixels of an output column, as three
-// registers R2/G2/B2 = value_left | value_right << 16 (8-bit values in 16-bit lanes).
+// Everything below works on the LEFT and RIGHT source pixels of an output column at once: a register holds
+// value_left | value_right << 16 (8-bit values or 16-bit terms in 16-bit lanes).
 //
 // libyuv YuvPixel (kYuvI601Constants):  yy = (Y * 0x0101 * 18997) >> 16
 //   R = clamp((yy + 102 V           - 14216) >> 6)
 //   G = clamp((yy - 25 U - 52 V     +  8696) >> 6)
 //   B = clamp((yy + 128 U           - 17544) >> 6)
-// clamp(x >> 6, 0, 255) == clamp(x, 0, 16383) >> 6. R and G sums fit signed 16 bits, so one
-// VIADDMNMX.S16x2.RELU does add + upper clamp + lower clamp for both pixels. The B sum can
-// exceed 32767, so it runs biased by +17544 in unsigned lanes.
+// clamp(x >> 6, 0, 255) == clamp(x, 0, 16383) >> 6. The R and G sums fit signed 16 bits, so one
+// VIADDMNMX.S16x2.RELU does add + upper clamp + lower clamp for both pixels. The B sum can exceed 32767, so it
+// runs biased by +17544 in unsigned lanes.
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+// Chroma-only terms of the pixel pair; shared by the top and the bottom luma row when both use one chroma row.
+struct ChromaPair {
+  uint32_t kr;  // 102 V - 14216            (s16 lanes)
+  uint32_t kg;  // 8696 - 25 U - 52 V       (s16 lanes)
+  uint32_t kb;  // 128 U                    (u16 lanes)
+};
 template <bool VU>
-__device__ __forceinline__ void yuv_pair_to_rgb(const uint8_t* __restrict__ yrow, const uint8_t* __restrict__ crow,
-                                                int xi, int cL, int cR, uint32_t& R2, uint32_t& G2, uint32_t& B2) {
-  const uint32_t pL = (uint32_t)yrow[xi] * 4882229u;
-  const uint32_t pR = (uint32_t)yrow[xi + 1] * 4882229u;
-  const uint32_t yy = __byte_perm(pL, pR, 0x7632);  // (pL >> 16) | (pR >> 16) << 16, lanes <= 18997
-  const uint32_t w = __byte_perm((uint32_t) * reinterpret_cast<const uint16_t*>(crow + cL),
-                                 (uint32_t) * reinterpret_cast<const uint16_t*>(crow + cR), 0x5410);
+__device__ __forceinline__ ChromaPair chroma_pair(uint32_t a_left, uint32_t a_right) {
+  const uint32_t w = __byte_perm(lds_u16(a_left), lds_u16(a_right), 0x5410);
   const uint32_t u2 = __byte_perm(w, 0u, VU ? 0x4341 : 0x4240);  // U_left | U_right << 16
   const uint32_t v2 = __byte_perm(w, 0u, VU ? 0x4240 : 0x4341);
-  const uint32_t r = __viaddmin_s16x2_relu(yy, __vadd2(v2 * 102u, 0xC878C878u /* -14216 */), 0x3FFF3FFFu);
+  ChromaPair c;
+  c.kr = __vadd2(v2 * 102u, 0xC878C878u /* -14216 */);
   const uint32_t t = u2 * 25u + v2 * 52u;  // lanes <= 19635
-  const uint32_t g = __viaddmin_s16x2_relu(yy, __vadd2(~t, 0x21F921F9u /* 8696 + 1 */), 0x3FFF3FFFu);
-  uint32_t b = __vmaxu2(__viaddmin_u16x2(yy, u2 << 7, 0x84878487u /* 17544 + 16383 */), 0x44884488u /* 17544 */);
+  c.kg = __vadd2(~t, 0x21F921F9u /* 8696 + 1: ~t == -t - 1 per lane */);
+  c.kb = u2 << 7;
+  return c;
+}
+// luma pair at byte address a (left pixel) and a + 1 (right pixel) -> 8-bit R, G, B pairs
+__device__ __forceinline__ void luma_pair_to_rgb(uint32_t a, const ChromaPair& c, uint32_t& R2, uint32_t& G2,
+                                                 uint32_t& B2) {
+  const uint32_t pL = lds_u8(a) * 4882229u;
+  const uint32_t pR = lds_u8(a + 1) * 4882229u;
+  const uint32_t yy = __byte_perm(pL, pR, 0x7632);  // (pL >> 16) | (pR >> 16) << 16, lanes <= 18997
+  const uint32_t r = __viaddmin_s16x2_relu(yy, c.kr, 0x3FFF3FFFu);
+  const uint32_t g = __viaddmin_s16x2_relu(yy, c.kg, 0x3FFF3FFFu);
+  uint32_t b = __vmaxu2(__viaddmin_u16x2(yy, c.kb, 0x84878487u /* 17544 + 16383 */), 0x44884488u /* 17544 */);
   b = __vadd2(b, 0xBB78BB78u /* -17544 */);
   R2 = (r >> 6) & 0x00FF00FFu;
   G2 = (g >> 6) & 0x00FF00FFu;
@@ -214,7 +248,10 @@ __device__ __forceinline__ uint32_t vblend2(uint32_t top, uint32_t bot, uint32_t
 }
 // ScaleARGBFilterCols_C on a packed pair: (L*(0x7f^xf) + R*xf) >> 7, truncating. wp = xf | (0x7f^xf) << 16, so
 // (L | R<<16) * wp = L*xf + (L*(0x7f^xf) + R*xf) << 16 (+ a term beyond bit 31); L*xf < 65536 never carries.
-__device__ __forceinline__ uint32_t hblend_pair(uint32_t v2, uint32_t wp) { return (v2 * wp) >> 23; }
+// Returns the product: the 8-bit result sits in bits 23..30.
+__device__ __forceinline__ uint32_t hblend_pair_raw(uint32_t v2, uint32_t wp) { return v2 * wp; }
+
+constexpr int kLutCopies = 8;  // the Normalize table is replicated so that lanes l and l' (l != l' mod 8) never collide
 
 template <typename OT, bool VU>
 __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __grid_constant__ FastParams P) {
@@ -224,7 +261,7 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
   uint32_t* rowinfo = reinterpret_cast<uint32_t*>(smem + kOffRowInfo);
   float* lut = reinterpret_cast<float*>(smem + kOffLut);
   uint8_t* stages = smem + kOffStages;
-  const int consumer_warps = (P.G * P.cols) >> 5;
+  const int consumer_warps = P.cols >> 5;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < P.S; ++s) {
@@ -233,8 +270,9 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (P.lut) {
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = reinterpret_cast<const float*>(P.lut)[i];
+  if (P.lut) {  // lut[v * kLutCopies + k] = table[v]
+    for (int i = threadIdx.x; i < 256 * kLutCopies; i += blockDim.x)
+      lut[i] = reinterpret_cast<const float*>(P.lut)[i / kLutCopies];
   }
   __syncthreads();
 
@@ -250,16 +288,17 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
     return;
   }
 
-  // ---------------- consumer warps ----------------
-  const int ct = threadIdx.x - 32;
-  const int jg = ct / P.cols;            // row group of this thread
-  const int col = ct - jg * P.cols;      // column slot within a pass
+  // ---------------- consumer warps: one thread per output column ----------------
+  const int col = threadIdx.x - 32;
   const int lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t lut_lane = sbase + kOffLut + (uint32_t)(lane & (kLutCopies - 1)) * 4u;
+  const uint32_t pitch = (uint32_t)P.row_pitch;
   int s = 0;
   uint32_t wrap = 0;
   for (long long item = blockIdx.x; item < P.n_items; item += gridDim.x) {
-    const uint8_t* stage = stages + (size_t)s * P.stage_bytes;
-    const uint32_t* ri = rowinfo + s * kMaxRows;
+    const uint32_t stage = sbase + kOffStages + (uint32_t)s * (uint32_t)P.stage_bytes;
+    const uint32_t ri = sbase + kOffRowInfo + (uint32_t)s * (kMaxRows * 4u);
     const int f = (int)(item / P.groups_per_frame);
     const int g = (int)(item - (long long)f * P.groups_per_frame);
     const int oy0 = g * P.R;
@@ -271,30 +310,34 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
       const int ox = pass * P.cols + col;
       if (ox < P.dw) {
         const int x = P.x0 + ox * P.dx;
-        const int xi = x >> 16;
+        const uint32_t xi = (uint32_t)(x >> 16);
         const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
         const uint32_t wp = xf | ((0x7fu ^ xf) << 16);
-        const int cL = (xi >> 1) << 1, cR = ((xi + 1) >> 1) << 1;
-        for (int j = jg; j < nrows; j += P.G) {
-          const uint32_t info = ri[j];
+        // byte offsets inside one staged row group: luma pair, left / right chroma pair (slot 2 = top chroma row)
+        const uint32_t cL = 2u * pitch + ((xi >> 1) << 1), cR = 2u * pitch + (((xi + 1u) >> 1) << 1);
+        uint32_t row = stage;                                   // slot 0 of output row j
+        uint8_t* o = gout + (size_t)ox * (3 * sizeof(OT));      // output pixel of row j
+#pragma unroll 2
+        for (int j = 0; j < nrows; ++j, row += 4u * pitch, o += P.dst_row_stride) {
+          const uint32_t info = lds_u32(ri + 4u * (uint32_t)j);
           const uint32_t w1 = info & 0xFFu, w0 = 256u - w1;
-          const uint8_t* yt = stage + (size_t)(4 * j) * P.row_pitch;
-          const uint8_t* yb = yt + P.row_pitch;
-          const uint8_t* ctop = yt + 2 * (size_t)P.row_pitch;
-          const uint8_t* cbot = yt + (size_t)(info >> 8) * P.row_pitch;
+          const ChromaPair ctop = chroma_pair<VU>(row + cL, row + cR);
+          ChromaPair cbot = ctop;
+          if (info & 0x100u) cbot = chroma_pair<VU>(row + cL + pitch, row + cR + pitch);  // slot 3: warp-uniform
           uint32_t tr, tg, tb, br, bg, bb;
-          yuv_pair_to_rgb<VU>(yt, ctop, xi, cL, cR, tr, tg, tb);
-          yuv_pair_to_rgb<VU>(yb, cbot, xi, cL, cR, br, bg, bb);
-          const uint32_t r = hblend_pair(vblend2(tr, br, w0, w1), wp);
-          const uint32_t gq = hblend_pair(vblend2(tg, bg, w0, w1), wp);
-          const uint32_t b = hblend_pair(vblend2(tb, bb, w0, w1), wp);
-          uint8_t* orow = gout + (long long)j * P.dst_row_stride;
+          luma_pair_to_rgb(row + xi, ctop, tr, tg, tb);
+          luma_pair_to_rgb(row + xi + pitch, cbot, br, bg, bb);
+          const uint32_t r = hblend_pair_raw(vblend2(tr, br, w0, w1), wp);
+          const uint32_t gq = hblend_pair_raw(vblend2(tg, bg, w0, w1), wp);
+          const uint32_t b = hblend_pair_raw(vblend2(tb, bb, w0, w1), wp);
           if (sizeof(OT) == 1) {
-            uint8_t* o = orow + ox * 3;
-            o[0] = (uint8_t)r; o[1] = (uint8_t)gq; o[2] = (uint8_t)b;
+            o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(gq >> 23); o[2] = (uint8_t)(b >> 23);
           } else {
-            float* o = reinterpret_cast<float*>(orow) + ox * 3;
-            o[0] = lut[r]; o[1] = lut[gq]; o[2] = lut[b];
+            // table index v = raw >> 23; byte offset v * 4 * kLutCopies = (raw >> 18) & 0x1FE0
+            float* of = reinterpret_cast<float*>(o);
+            of[0] = lds_f32(lut_lane + ((r >> 18) & 0x1FE0u));
+            of[1] = lds_f32(lut_lane + ((gq >> 18) & 0x1FE0u));
+            of[2] = lds_f32(lut_lane + ((b >> 18) & 0x1FE0u));
           }
         }
       }
@@ -352,9 +395,7 @@ int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out) {
     if (e != cudaSuccess) { cudaFree(p->lut_dev); delete p; return (int)e; }
   }
   p->R = env_int("BANDCU_FAST_ROWS", 1, kMaxRows, 4);
-  p->G = env_int("BANDCU_FAST_GROUPS", 1, kMaxRows, 1);
   p->S = env_int("BANDCU_FAST_STAGES", 2, kMaxStages, 2);
-  if (p->G > p->R) p->G = p->R;
   *out = p;
   return BANDCU_OK;
 }
@@ -398,18 +439,16 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   const int cbytes = ((d.vw + 1) >> 1) << 1;
   P.row_pitch = ((cbytes + 15) / 16) * 16 + 16;  // +16: xi+1 may touch one byte past the row when xf == 0
   // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
-  P.R = p->R; P.G = p->G; P.S = p->S;
+  P.R = p->R; P.S = p->S;
   P.passes = (d.dst_width + 511) / 512;
   P.cols = (((d.dst_width + P.passes - 1) / P.passes) + 31) / 32 * 32;
-  while (P.G > 1 && 32 + P.G * P.cols > 1024) --P.G;
   const size_t smem_cap = 226 * 1024;
   while (P.S > 2 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.S;
   while (P.R > 1 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.R;
-  if (P.G > P.R) P.G = P.R;
   P.stage_bytes = P.R * 4 * P.row_pitch;
   const size_t smem = kOffStages + (size_t)P.S * P.stage_bytes;
   if (smem > smem_cap) return BANDCU_E_UNSUPPORTED;
-  const int block = 32 + P.G * P.cols;
+  const int block = 32 + P.cols;
   P.groups_per_frame = (d.dst_height + P.R - 1) / P.R;
   P.n_items = (long long)n * P.groups_per_frame;
   P.lut = p->lut_dev;
