@@ -39,6 +39,7 @@ using namespace bandcu;
 struct BandCuPlan {
   BandCuPlanDesc d;
   FastPlan* fast;
+  PackedPlan* packed;
   // pointer-table staging for bandcu_plan_run()
   BandCuFrame* table_dev;
   BandCuFrame* table_host;  // pinned
@@ -103,6 +104,13 @@ int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan) {
       return fail(e, "plan_create: fast plan setup");
     }
   }
+  if (!p->fast && packed_plan_supported(p->d)) {
+    int e = packed_plan_create(p->d, &p->packed);
+    if (e != BANDCU_OK) {
+      delete p;
+      return fail(e, "plan_create: packed plan setup");
+    }
+  }
   *plan = p;
   return BANDCU_OK;
 }
@@ -114,6 +122,7 @@ int bandcu_plan_destroy(BandCuPlan* plan) {
   if (plan->table_dev) (void)cudaFree(plan->table_dev);
   if (plan->table_host) (void)cudaFreeHost(plan->table_host);
   if (plan->fast) fast_plan_destroy(plan->fast);
+  if (plan->packed) packed_plan_destroy(plan->packed);
   delete plan;
   return BANDCU_OK;
 }
@@ -127,6 +136,11 @@ static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hin
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: fast kernel launch");
     // this batch's pointers/strides do not meet the staged kernel's alignment
     // rules: the generic kernel computes the identical result.
+  }
+  if (plan->packed) {
+    int e = launch_packed(plan->packed, plan->d, b, hints, n, s);
+    if (e == BANDCU_OK) return BANDCU_OK;
+    if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: packed kernel launch");
   }
   int e = launch_generic(plan->d, b, n, s);
   if (e != 0) return fail(e, "plan_run: generic kernel launch");
@@ -174,6 +188,11 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
   hints.valid = true;
   hints.semi_planar = frames[0].pu && frames[0].pv;
   hints.aligned16 = true;
+  hints.out_aligned16 = true;
+  for (int i = 0; i < n; ++i) {
+    if (reinterpret_cast<uintptr_t>(frames[i].p0) & 15) hints.aligned16 = false;
+    if (reinterpret_cast<uintptr_t>(frames[i].out) & 15) hints.out_aligned16 = false;
+  }
   if (hints.semi_planar) {
     const long long d0 = (const char*)frames[0].pv - (const char*)frames[0].pu;
     hints.semi_planar = (d0 == 1 || d0 == -1);

@@ -18,6 +18,8 @@ namespace bandcu {
 struct GenericParams {
   BandCuPlanDesc d;
   BatchArgs batch;
+  int transposed;  // 1: threadIdx.x walks output ROWS (the index map swaps axes: consecutive output rows are
+                   // consecutive source columns, so this keeps the warp's source reads inside a few sectors)
 };
 
 __device__ __forceinline__ int map_row(const BandCuAffine& m, int r, int c) { return m.r0 + m.rr * r + m.rc * c; }
@@ -25,13 +27,18 @@ __device__ __forceinline__ int map_col(const BandCuAffine& m, int r, int c) { re
 
 // Fetch one pixel of the virtual image (after index maps and colour
 // conversion) as packed channels c0 | c1<<8 | c2<<16 | c3<<24.
+// SRC / CVT: compile-time source kind and conversion (-1 = read them from the descriptor); IDENT = 1 when all
+// three index maps are the identity. launch_generic() picks the instantiation; the arithmetic is the same.
+template <int SRC, int CVT, int IDENT>
 __device__ __forceinline__ uint32_t fetch_px(const BandCuPlanDesc& d, const FramePtrs& f, int r, int c) {
   r = min(max(r, 0), d.vh - 1);
   c = min(max(c, 0), d.vw - 1);
-  const int row = map_row(d.luma_map, r, c);
-  const int col = map_col(d.luma_map, r, c);
+  const int row = IDENT ? r : map_row(d.luma_map, r, c);
+  const int col = IDENT ? c : map_col(d.luma_map, r, c);
   const uint8_t* p = f.p0 + (long long)row * d.stride0;
-  switch (d.src_kind) {
+  const int src_kind = SRC < 0 ? d.src_kind : SRC;
+  const int cvt = CVT < 0 ? d.cvt : CVT;
+  switch (src_kind) {
     case BANDCU_SRC_GRAY:
       return p[col];
     case BANDCU_SRC_UV: {
@@ -41,42 +48,51 @@ __device__ __forceinline__ uint32_t fetch_px(const BandCuPlanDesc& d, const Fram
     case BANDCU_SRC_RGB: {
       const uint8_t* q = p + col * 3;
       uint32_t R = q[0], G = q[1], B = q[2];
-      if (d.cvt == BANDCU_CVT_RGB2GRAY) return rgb_to_yj(R, G, B);
+      if (cvt == BANDCU_CVT_RGB2GRAY) return rgb_to_yj(R, G, B);
       return R | (G << 8) | (B << 16);
     }
     case BANDCU_SRC_RGBA: {
       const uint8_t* q = p + col * 4;
-      uint32_t R = q[0], G = q[1], B = q[2], A = q[3];
-      if (d.cvt == BANDCU_CVT_RGBA2GRAY) return rgb_to_yj(R, G, B);
-      if (d.cvt == BANDCU_CVT_RGBA2RGB) return R | (G << 8) | (B << 16);
+      uint32_t R, G, B, A;
+      if ((reinterpret_cast<uintptr_t>(q) & 3) == 0) {  // one 32-bit load (always, for 4-byte aligned frames)
+        const uint32_t w = *reinterpret_cast<const uint32_t*>(q);
+        if (cvt == BANDCU_CVT_NONE) return w;
+        if (cvt == BANDCU_CVT_RGBA2RGB) return w & 0x00FFFFFFu;
+        R = w & 0xFF; G = (w >> 8) & 0xFF; B = (w >> 16) & 0xFF; A = w >> 24;
+      } else {
+        R = q[0]; G = q[1]; B = q[2]; A = q[3];
+      }
+      if (cvt == BANDCU_CVT_RGBA2GRAY) return rgb_to_yj(R, G, B);
+      if (cvt == BANDCU_CVT_RGBA2RGB) return R | (G << 8) | (B << 16);
       return R | (G << 8) | (B << 16) | (A << 24);
     }
     default: {  // BANDCU_SRC_YUV420
       const int Y = p[col];
-      if (d.cvt == BANDCU_CVT_YUV2GRAY) return (uint32_t)Y;
+      if (cvt == BANDCU_CVT_YUV2GRAY) return (uint32_t)Y;
       // chroma is NEAREST: sample (r1>>1, c1>>1) of the image the conversion ran on
-      const int r1 = map_row(d.pre_map, r, c), c1 = map_col(d.pre_map, r, c);
-      const int cr = map_row(d.chroma_map, r1 >> 1, c1 >> 1);
-      const int cc = map_col(d.chroma_map, r1 >> 1, c1 >> 1);
+      const int r1 = IDENT ? r : map_row(d.pre_map, r, c), c1 = IDENT ? c : map_col(d.pre_map, r, c);
+      const int cr = IDENT ? (r1 >> 1) : map_row(d.chroma_map, r1 >> 1, c1 >> 1);
+      const int cc = IDENT ? (c1 >> 1) : map_col(d.chroma_map, r1 >> 1, c1 >> 1);
       const long long off = (long long)cr * d.stride_uv + (long long)cc * d.pixel_stride_uv;
       const int U = f.pu[off], V = f.pv[off];
       uint32_t rgb = yuv_to_rgb_packed(yuv_luma_term(Y), yuv_chroma_terms(U, V));
-      if (d.cvt == BANDCU_CVT_YUV2RGBA) rgb |= 0xFF000000u;
+      if (cvt == BANDCU_CVT_YUV2RGBA) rgb |= 0xFF000000u;
       return rgb;
     }
   }
 }
 
 // One output pixel of the Resize stage (packed channels).
-__device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy, int ox) {
+template <int SRC, int CVT, int IDENT>
+__device__ __forceinline__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy, int ox) {
   const bool plane = (d.flavor == BANDCU_FLAVOR_PLANE);
   switch (d.scale_mode) {
     case BANDCU_SCALE_COPY:
-      return fetch_px(d, f, oy, ox);
+      return fetch_px<SRC, CVT, IDENT>(d, f, oy, ox);
     case BANDCU_SCALE_POINT: {  // ScaleARGBSimple / ScalePlaneSimple
       long long y = (long long)d.y0 + (long long)oy * d.dy;
       long long x = (long long)d.x0 + (long long)ox * d.dx;
-      return fetch_px(d, f, (int)(y >> 16), (int)(x >> 16));
+      return fetch_px<SRC, CVT, IDENT>(d, f, (int)(y >> 16), (int)(x >> 16));
     }
     case BANDCU_SCALE_BILINEAR_DOWN: {  // ScaleARGBBilinearDown / ScalePlaneBilinearDown
       long long y = (long long)d.y0 + (long long)oy * d.dy;
@@ -85,11 +101,11 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       const int yf = d.linear ? 0 : (int)((y >> 8) & 255);
       const long long x = (long long)d.x0 + (long long)ox * d.dx;
       const int xi = (int)(x >> 16);
-      uint32_t a = fetch_px(d, f, yi, xi);
-      uint32_t b = fetch_px(d, f, yi, xi + 1);
+      uint32_t a = fetch_px<SRC, CVT, IDENT>(d, f, yi, xi);
+      uint32_t b = fetch_px<SRC, CVT, IDENT>(d, f, yi, xi + 1);
       if (yf) {
-        a = interp_rows4(a, fetch_px(d, f, yi + 1, xi), yf);
-        b = interp_rows4(b, fetch_px(d, f, yi + 1, xi + 1), yf);
+        a = interp_rows4(a, fetch_px<SRC, CVT, IDENT>(d, f, yi + 1, xi), yf);
+        b = interp_rows4(b, fetch_px<SRC, CVT, IDENT>(d, f, yi + 1, xi + 1), yf);
       }
       if (plane) return blend_cols1_round7(a, b, (int)(x & 0xffff));
       return blend_cols4_trunc7(a, b, (int)((x >> 9) & 0x7f));
@@ -102,18 +118,18 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       const long long x = (long long)d.x0 + (long long)ox * d.dx;
       const int xi = (int)(x >> 16);
       const int xf7 = (int)((x >> 9) & 0x7f), xf16 = (int)(x & 0xffff);
-      uint32_t a0 = fetch_px(d, f, yi, xi), b0 = fetch_px(d, f, yi, xi + 1);
+      uint32_t a0 = fetch_px<SRC, CVT, IDENT>(d, f, yi, xi), b0 = fetch_px<SRC, CVT, IDENT>(d, f, yi, xi + 1);
       uint32_t top = plane ? blend_cols1_round7(a0, b0, xf16) : blend_cols4_trunc7(a0, b0, xf7);
       if (!yf) return top;
-      uint32_t a1 = fetch_px(d, f, yi + 1, xi), b1 = fetch_px(d, f, yi + 1, xi + 1);
+      uint32_t a1 = fetch_px<SRC, CVT, IDENT>(d, f, yi + 1, xi), b1 = fetch_px<SRC, CVT, IDENT>(d, f, yi + 1, xi + 1);
       uint32_t bot = plane ? blend_cols1_round7(a1, b1, xf16) : blend_cols4_trunc7(a1, b1, xf7);
       return interp_rows4(top, bot, yf);
     }
     case BANDCU_SCALE_BOX2: {  // 2x2 box at (y0>>16 + oy*(dy>>16), x0>>16 + ox*(dx>>16))
       const int r = (d.y0 >> 16) + oy * (d.dy >> 16);
       const int c = (d.x0 >> 16) + ox * (d.dx >> 16);
-      return box2x2_4(fetch_px(d, f, r, c), fetch_px(d, f, r, c + 1), fetch_px(d, f, r + 1, c),
-                      fetch_px(d, f, r + 1, c + 1));
+      return box2x2_4(fetch_px<SRC, CVT, IDENT>(d, f, r, c), fetch_px<SRC, CVT, IDENT>(d, f, r, c + 1), fetch_px<SRC, CVT, IDENT>(d, f, r + 1, c),
+                      fetch_px<SRC, CVT, IDENT>(d, f, r + 1, c + 1));
     }
     case BANDCU_SCALE_VERTICAL: {  // ScalePlaneVertical (its own max_y, passed in d.max_y)
       long long y = (long long)d.y0 + (long long)oy * d.dy;
@@ -121,9 +137,9 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       const int yi = (int)(y >> 16);
       const int yf = d.linear ? 0 : (int)((y >> 8) & 255);  // d.linear here = "filtering == None"
       const int c = ox + (d.x0 >> 16);
-      uint32_t a = fetch_px(d, f, yi, c);
+      uint32_t a = fetch_px<SRC, CVT, IDENT>(d, f, yi, c);
       if (!yf) return a;
-      return interp_rows4(a, fetch_px(d, f, yi + 1, c), yf);
+      return interp_rows4(a, fetch_px<SRC, CVT, IDENT>(d, f, yi + 1, c), yf);
     }
     case BANDCU_SCALE_DOWN34: {  // ScalePlaneDown34 with ScaleRowDown34_{0,1}_Box_C
       const int g = oy / 3, k = oy - 3 * g;
@@ -135,14 +151,14 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       int hs, ht;
       const int c = 4 * m;
       if (j == 0) {
-        hs = ((int)fetch_px(d, f, rs, c) * 3 + (int)fetch_px(d, f, rs, c + 1) + 2) >> 2;
-        ht = ((int)fetch_px(d, f, rt, c) * 3 + (int)fetch_px(d, f, rt, c + 1) + 2) >> 2;
+        hs = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c) * 3 + (int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c + 1) + 2) >> 2;
+        ht = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c) * 3 + (int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c + 1) + 2) >> 2;
       } else if (j == 1) {
-        hs = ((int)fetch_px(d, f, rs, c + 1) + (int)fetch_px(d, f, rs, c + 2) + 1) >> 1;
-        ht = ((int)fetch_px(d, f, rt, c + 1) + (int)fetch_px(d, f, rt, c + 2) + 1) >> 1;
+        hs = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c + 1) + (int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c + 2) + 1) >> 1;
+        ht = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c + 1) + (int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c + 2) + 1) >> 1;
       } else {
-        hs = ((int)fetch_px(d, f, rs, c + 2) + (int)fetch_px(d, f, rs, c + 3) * 3 + 2) >> 2;
-        ht = ((int)fetch_px(d, f, rt, c + 2) + (int)fetch_px(d, f, rt, c + 3) * 3 + 2) >> 2;
+        hs = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c + 2) + (int)fetch_px<SRC, CVT, IDENT>(d, f, rs, c + 3) * 3 + 2) >> 2;
+        ht = ((int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c + 2) + (int)fetch_px<SRC, CVT, IDENT>(d, f, rt, c + 3) * 3 + 2) >> 2;
       }
       return (k == 1) ? (uint32_t)((hs + ht + 1) >> 1) : (uint32_t)((hs * 3 + ht + 2) >> 2);
     }
@@ -153,7 +169,7 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       const int c0 = 8 * m + 3 * j, nc = (j == 2) ? 2 : 3;
       int sum = 0;
       for (int rr = 0; rr < nr; ++rr)
-        for (int cc = 0; cc < nc; ++cc) sum += (int)fetch_px(d, f, r0 + rr, c0 + cc);
+        for (int cc = 0; cc < nc; ++cc) sum += (int)fetch_px<SRC, CVT, IDENT>(d, f, r0 + rr, c0 + cc);
       const int n = nr * nc;
       const int mul = (n == 9) ? (65536 / 9) : (n == 6) ? (65536 / 6) : (65536 / 4);
       return (uint32_t)((sum * mul) >> 16) & 0xFFu;
@@ -170,7 +186,7 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
         int row;
         if (dh == 1) row = (sh - 1) / 2;
         else row = (int)(((long long)32767 + (long long)oy * d.dy) >> 16);  // d.dy = FixedDiv(sh-1, dh-1)
-        const uint32_t pn = fetch_px(d, f, row, cn), pf = fetch_px(d, f, row, cf);
+        const uint32_t pn = fetch_px<SRC, CVT, IDENT>(d, f, row, cn), pf = fetch_px<SRC, CVT, IDENT>(d, f, row, cf);
         for (int k = 0; k < d.channels; ++k) {
           const int n = (pn >> (8 * k)) & 0xFF, fr = (pf >> (8 * k)) & 0xFF;
           out |= (uint32_t)((3 * n + fr + 2) >> 2) << (8 * k);
@@ -181,8 +197,8 @@ __device__ uint32_t scale_px(const BandCuPlanDesc& d, const FramePtrs& f, int oy
       if (oy == 0) { rn = rf = 0; }
       else if (oy == dh - 1 && !(dh & 1)) { rn = rf = sh - 1; }
       else { const int yy = (oy - 1) >> 1; if (oy & 1) { rn = yy; rf = yy + 1; } else { rn = yy + 1; rf = yy; } }
-      const uint32_t pa = fetch_px(d, f, rn, cn), pb = fetch_px(d, f, rn, cf);
-      const uint32_t pc = fetch_px(d, f, rf, cn), pd = fetch_px(d, f, rf, cf);
+      const uint32_t pa = fetch_px<SRC, CVT, IDENT>(d, f, rn, cn), pb = fetch_px<SRC, CVT, IDENT>(d, f, rn, cf);
+      const uint32_t pc = fetch_px<SRC, CVT, IDENT>(d, f, rf, cn), pd = fetch_px<SRC, CVT, IDENT>(d, f, rf, cf);
       for (int k = 0; k < d.channels; ++k) {
         const int A = (pa >> (8 * k)) & 0xFF, B = (pb >> (8 * k)) & 0xFF;
         const int Cc = (pc >> (8 * k)) & 0xFF, D = (pd >> (8 * k)) & 0xFF;
@@ -201,13 +217,16 @@ __device__ __forceinline__ void store_norm(uint8_t* out_row, int ox, int ch, uin
   for (int k = 0; k < ch; ++k) o[k] = normalize_elem<OT>((float)((px >> (8 * k)) & 0xFFu), mean, sd);
 }
 
+template <int SRC, int CVT, int IDENT>
 __global__ void __launch_bounds__(256) fused_generic_kernel(const __grid_constant__ GenericParams P) {
   const BandCuPlanDesc& d = P.d;
-  const int ox = blockIdx.x * blockDim.x + threadIdx.x;
-  const int oy = blockIdx.y * blockDim.y + threadIdx.y;
+  const int ta = blockIdx.x * blockDim.x + threadIdx.x;
+  const int tb = blockIdx.y * blockDim.y + threadIdx.y;
+  const int ox = P.transposed ? tb : ta;
+  const int oy = P.transposed ? ta : tb;
   if (ox >= d.dst_width || oy >= d.dst_height) return;
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
-  const uint32_t px = scale_px(d, f, oy, ox);
+  const uint32_t px = scale_px<SRC, CVT, IDENT>(d, f, oy, ox);
   uint8_t* out_row = f.out + (long long)oy * d.dst_row_stride;
   const int ch = d.channels;
   if (!d.normalize) {
@@ -230,12 +249,39 @@ __global__ void __launch_bounds__(256) fused_generic_kernel(const __grid_constan
   }
 }
 
+static bool is_identity_map(const BandCuAffine& m) {
+  return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
+}
+typedef void (*GenericKernel)(GenericParams);
+// Specialised instantiations for every (source kind, conversion) pair the plan compiler emits, with and without
+// index maps; anything else runs the fully run-time variant.
+static GenericKernel pick_generic(int src, int cvt, bool ident) {
+#define BANDCU_PAIR(S, C)                                                                                   \
+  if (src == (S) && cvt == (C)) return ident ? fused_generic_kernel<(S), (C), 1> : fused_generic_kernel<(S), (C), 0>;
+  BANDCU_PAIR(BANDCU_SRC_GRAY, BANDCU_CVT_NONE)
+  BANDCU_PAIR(BANDCU_SRC_UV, BANDCU_CVT_NONE)
+  BANDCU_PAIR(BANDCU_SRC_RGB, BANDCU_CVT_NONE)
+  BANDCU_PAIR(BANDCU_SRC_RGB, BANDCU_CVT_RGB2GRAY)
+  BANDCU_PAIR(BANDCU_SRC_RGBA, BANDCU_CVT_NONE)
+  BANDCU_PAIR(BANDCU_SRC_RGBA, BANDCU_CVT_RGBA2GRAY)
+  BANDCU_PAIR(BANDCU_SRC_RGBA, BANDCU_CVT_RGBA2RGB)
+  BANDCU_PAIR(BANDCU_SRC_YUV420, BANDCU_CVT_YUV2RGB)
+  BANDCU_PAIR(BANDCU_SRC_YUV420, BANDCU_CVT_YUV2RGBA)
+  BANDCU_PAIR(BANDCU_SRC_YUV420, BANDCU_CVT_YUV2GRAY)
+#undef BANDCU_PAIR
+  return fused_generic_kernel<-1, -1, 0>;
+}
+
 int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream) {
   GenericParams P;
   P.d = d;
   P.batch = batch;
+  P.transposed = (d.luma_map.rc != 0 && d.luma_map.rr == 0) ? 1 : 0;
   dim3 block(32, 8, 1);
   dim3 grid((d.dst_width + 31) / 32, (d.dst_height + 7) / 8, 1);
+  if (P.transposed) grid = dim3((d.dst_height + 31) / 32, (d.dst_width + 7) / 8, 1);
+  const bool ident = is_identity_map(d.luma_map) && is_identity_map(d.pre_map) && is_identity_map(d.chroma_map);
+  void (*kern)(GenericParams) = pick_generic(d.src_kind, d.cvt, ident);
   // gridDim.z is limited to 65535: chunk very large batches
   for (int done = 0; done < n;) {
     int chunk = n - done > 65535 ? 65535 : n - done;
@@ -250,7 +296,7 @@ int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaS
       Q.batch.first.out += (long long)done * Q.batch.out_stride;
     }
     grid.z = chunk;
-    fused_generic_kernel<<<grid, block, 0, stream>>>(Q);
+    kern<<<grid, block, 0, stream>>>(Q);
     count_launch();
     done += chunk;
   }

@@ -26,8 +26,16 @@ struct TableHints {
   bool semi_planar = false;  // every frame has |pu - pv| == 1 with the same order
   bool vu = false;       // V first (NV21)
   bool aligned16 = false;  // every luma / chroma base pointer is 16-byte aligned
+  bool out_aligned16 = false;  // every output pointer is 16-byte aligned
 };
 // returns BANDCU_E_UNSUPPORTED if this particular batch (layout) cannot use it
 int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
                 cudaStream_t stream);
+// Packed (gray / RGB / RGBA) bilinear Resize without index maps: four output pixels per thread.
+struct PackedPlan;
+bool packed_plan_supported(const BandCuPlanDesc& d);
+int packed_plan_create(const BandCuPlanDesc& d, PackedPlan** out);
+void packed_plan_destroy(PackedPlan* p);
+int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
+                  cudaStream_t stream);
 }  // namespace bandcu

@@ -1,0 +1,254 @@
+// band_b200/csrc/cuda/bandcu_packed.cu
+//
+// Bilinear Resize of PACKED sources (gray / RGB / RGBA) without index maps, optionally behind a per-fetch
+// ColorSpaceConvert (RGBA -> RGB, RGB -> gray, RGBA -> gray) and in front of Normalize: the C5 sweep of
+// BASELINE.json (AutoConvert = CSC -> Resize -> DataTypeConvert, image_operator.cc:465-491) and every
+// ResizeRgb / ResizeRgba / ResizeGray call (libyuv_image_operator.cc:1146-1229,1367-1380) that takes libyuv's
+// general bilinear paths:
+//   ScaleARGBBilinearDown / ScalePlaneBilinearDown : rows blended first, then columns
+//   ScaleARGBBilinearUp   / ScalePlaneBilinearUp   : columns first, then rows
+// with the ARGB column filter ((a*(0x7f^f) + b*f) >> 7, truncating) for 3/4-channel images and the x86 plane
+// filter (a + (((f>>9)*(b-a) + 0x40) >> 7)) for gray. Same arithmetic as fused_generic_kernel (the parity tests run
+// both); what differs is the cost per pixel: ncu showed the generic kernel issue-bound at ~240 instructions per
+// output pixel on the 64^2 -> 2048^2 case. Here one thread produces FOUR adjacent output pixels of a row: the row
+// terms are shared, all index arithmetic is 32-bit, sources are read through the read-only path, and the four
+// results leave as 32/128-bit stores.
+#include <cstring>
+
+#include "bandcu_device.cuh"
+#include "bandcu_internal.h"
+
+namespace bandcu {
+
+struct PackedParams {
+  int sw, sh, stride0;
+  int dw, dh;
+  int x0, y0, dx, dy, max_y, linear;
+  long long dst_row_stride;
+  int vec_ok;          // outputs are aligned for 32/128-bit stores
+  const float* lut;    // Normalize table (f32 outputs) or nullptr
+  BatchArgs batch;
+};
+
+// One source pixel after the per-fetch conversion, channels packed c0 | c1<<8 | c2<<16 | c3<<24.
+template <int SRCCH, int CVT>
+__device__ __forceinline__ uint32_t packed_fetch(const uint8_t* __restrict__ row, int c) {
+  if (SRCCH == 1) return __ldg(row + c);
+  if (SRCCH == 4) {
+    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(row) + c);  // frames are 4-byte aligned (checked on the host)
+    if (CVT == BANDCU_CVT_RGBA2GRAY) return rgb_to_yj(w & 0xFF, (w >> 8) & 0xFF, (w >> 16) & 0xFF);
+    if (CVT == BANDCU_CVT_RGBA2RGB) return w & 0x00FFFFFFu;
+    return w;
+  }
+  const uint8_t* q = row + c * 3;
+  const uint32_t R = __ldg(q), G = __ldg(q + 1), B = __ldg(q + 2);
+  if (CVT == BANDCU_CVT_RGB2GRAY) return rgb_to_yj(R, G, B);
+  return R | (G << 8) | (B << 16);
+}
+
+template <bool PLANE>
+__device__ __forceinline__ uint32_t packed_hblend(uint32_t a, uint32_t b, int x) {
+  if (PLANE) return blend_cols1_round7(a, b, x & 0xffff);
+  return blend_cols4_trunc7(a, b, (x >> 9) & 0x7f);
+}
+
+enum { kPackedDown = 0, kPackedUp = 1, kPackedBox2 = 2 };
+
+template <int SRCCH, int CVT, int OUTCH, int MODE, typename OT>
+__global__ void __launch_bounds__(256) packed_bilinear_kernel(const __grid_constant__ PackedParams P) {
+  constexpr bool UP = (MODE == kPackedUp);
+  constexpr bool PLANE = (OUTCH == 1);
+  __shared__ float lut[256];
+  if (sizeof(OT) == 4) {
+    const int t = threadIdx.y * blockDim.x + threadIdx.x;
+    if (t < 256) lut[t] = P.lut[t];
+    __syncthreads();
+  }
+  const int ox0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int oy = blockIdx.y * blockDim.y + threadIdx.y;
+  if (ox0 >= P.dw || oy >= P.dh) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+
+  int y = P.y0 + oy * P.dy;
+  if (MODE != kPackedBox2 && y > P.max_y) y = P.max_y;
+  // Box2 (ScaleARGBRowDown2Box / DownEvenBox / ScaleRowDown2Box): 2x2 average at (y0>>16 + oy*(dy>>16), ...)
+  const int yi = MODE == kPackedBox2 ? (P.y0 >> 16) + oy * (P.dy >> 16) : (y >> 16);
+  const int yf = (MODE == kPackedBox2 || P.linear) ? 0 : ((y >> 8) & 255);
+  const int r0 = min(max(yi, 0), P.sh - 1), r1 = min(max(yi + 1, 0), P.sh - 1);
+  const uint8_t* row0 = f.p0 + (size_t)r0 * P.stride0;
+  const uint8_t* row1 = f.p0 + (size_t)r1 * P.stride0;
+
+  uint32_t px[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int x = P.x0 + (ox0 + k) * P.dx;
+    const int xi = MODE == kPackedBox2 ? (P.x0 >> 16) + (ox0 + k) * (P.dx >> 16) : (x >> 16);
+    const int c0 = min(max(xi, 0), P.sw - 1), c1 = min(max(xi + 1, 0), P.sw - 1);
+    uint32_t a = packed_fetch<SRCCH, CVT>(row0, c0), b = packed_fetch<SRCCH, CVT>(row0, c1);
+    if (MODE == kPackedBox2) {
+      px[k] = box2x2_4(a, b, packed_fetch<SRCCH, CVT>(row1, c0), packed_fetch<SRCCH, CVT>(row1, c1));
+    } else if (UP) {  // columns, then rows
+      uint32_t top = packed_hblend<PLANE>(a, b, x);
+      if (yf) {
+        const uint32_t a1 = packed_fetch<SRCCH, CVT>(row1, c0), b1 = packed_fetch<SRCCH, CVT>(row1, c1);
+        top = interp_rows4(top, packed_hblend<PLANE>(a1, b1, x), yf);
+      }
+      px[k] = top;
+    } else {   // rows, then columns
+      if (yf) {
+        a = interp_rows4(a, packed_fetch<SRCCH, CVT>(row1, c0), yf);
+        b = interp_rows4(b, packed_fetch<SRCCH, CVT>(row1, c1), yf);
+      }
+      px[k] = packed_hblend<PLANE>(a, b, x);
+    }
+  }
+
+  uint8_t* orow = f.out + (long long)oy * P.dst_row_stride;
+  const bool full4 = (ox0 + 4 <= P.dw) && P.vec_ok;
+  if (sizeof(OT) == 1) {
+    uint8_t* o = orow + (size_t)ox0 * OUTCH;
+    if (full4) {
+      if (OUTCH == 1) {
+        *reinterpret_cast<uint32_t*>(o) = (px[0] & 0xFF) | ((px[1] & 0xFF) << 8) | ((px[2] & 0xFF) << 16) | (px[3] << 24);
+      } else if (OUTCH == 3) {  // 12 bytes: R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+        uint32_t* o4 = reinterpret_cast<uint32_t*>(o);
+        o4[0] = (px[0] & 0x00FFFFFFu) | (px[1] << 24);
+        o4[1] = ((px[1] >> 8) & 0x0000FFFFu) | (px[2] << 16);
+        o4[2] = ((px[2] >> 16) & 0x000000FFu) | (px[3] << 8);
+      } else {
+        *reinterpret_cast<uint4*>(o) = make_uint4(px[0], px[1], px[2], px[3]);
+      }
+    } else {
+      for (int k = 0; k < 4 && ox0 + k < P.dw; ++k)
+        for (int c = 0; c < OUTCH; ++c) o[k * OUTCH + c] = (uint8_t)((px[k] >> (8 * c)) & 0xFF);
+    }
+  } else {
+    float* o = reinterpret_cast<float*>(orow) + (size_t)ox0 * OUTCH;
+    if (full4) {
+      float v[4 * OUTCH];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int c = 0; c < OUTCH; ++c) v[k * OUTCH + c] = lut[(px[k] >> (8 * c)) & 0xFF];
+#pragma unroll
+      for (int q = 0; q < OUTCH; ++q)
+        reinterpret_cast<float4*>(o)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+    } else {
+      for (int k = 0; k < 4 && ox0 + k < P.dw; ++k)
+        for (int c = 0; c < OUTCH; ++c) o[k * OUTCH + c] = lut[(px[k] >> (8 * c)) & 0xFF];
+    }
+  }
+}
+
+struct PackedPlan {
+  float* lut_dev;
+};
+
+__global__ void packed_build_lut_kernel(float* lut, float mean, float sd) {
+  const int i = threadIdx.x;
+  if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
+}
+
+static bool packed_is_identity(const BandCuAffine& m) {
+  return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
+}
+
+bool packed_plan_supported(const BandCuPlanDesc& d) {
+  const char* off = getenv("BANDCU_DISABLE_PACKED");
+  if (off && off[0] == '1') return false;
+  if (d.src_kind != BANDCU_SRC_GRAY && d.src_kind != BANDCU_SRC_RGB && d.src_kind != BANDCU_SRC_RGBA) return false;
+  if (!packed_is_identity(d.luma_map)) return false;
+  // four ADJACENT output pixels per thread only pays while a warp's source footprint stays compact: up-scaling,
+  // down-scaling by at most 2, and the exact 2x box; larger ratios stay on the one-pixel-per-thread kernel
+  if (d.scale_mode == BANDCU_SCALE_BILINEAR_DOWN) { if (d.dx > 0x20000) return false; }
+  else if (d.scale_mode == BANDCU_SCALE_BOX2) { if (d.dx != 0x20000) return false; }
+  else if (d.scale_mode != BANDCU_SCALE_BILINEAR_UP) return false;
+  if ((d.channels == 1) != (d.flavor == BANDCU_FLAVOR_PLANE)) return false;
+  if (d.normalize ? d.out_dtype != BANDCU_DT_F32 : d.out_dtype != BANDCU_DT_U8) return false;
+  if ((long long)d.x0 + (long long)(d.dst_width + 4) * d.dx > 0x7fffffffLL) return false;
+  if ((long long)d.y0 + (long long)(d.dst_height + 1) * d.dy > 0x7fffffffLL) return false;
+  return true;
+}
+
+int packed_plan_create(const BandCuPlanDesc& d, PackedPlan** out) {
+  PackedPlan* p = new PackedPlan();
+  p->lut_dev = nullptr;
+  if (d.normalize) {
+    cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
+    if (e != cudaSuccess) { delete p; return (int)e; }
+    packed_build_lut_kernel<<<1, 256>>>(p->lut_dev, d.mean, d.std_);
+    count_launch();
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { cudaFree(p->lut_dev); delete p; return (int)e; }
+  }
+  *out = p;
+  return BANDCU_OK;
+}
+
+void packed_plan_destroy(PackedPlan* p) {
+  if (!p) return;
+  if (p->lut_dev) (void)cudaFree(p->lut_dev);
+  delete p;
+}
+
+typedef void (*PackedKernel)(PackedParams);
+template <int SRCCH, int CVT, int OUTCH>
+static PackedKernel packed_pick2(int mode, bool f32) {
+  if (mode == kPackedUp) return f32 ? packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedUp, float> : packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedUp, uint8_t>;
+  if (mode == kPackedBox2) return f32 ? packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedBox2, float> : packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedBox2, uint8_t>;
+  return f32 ? packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedDown, float> : packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedDown, uint8_t>;
+}
+static PackedKernel packed_pick(const BandCuPlanDesc& d) {
+  const int up = d.scale_mode == BANDCU_SCALE_BILINEAR_UP ? kPackedUp : d.scale_mode == BANDCU_SCALE_BOX2 ? kPackedBox2 : kPackedDown;
+  const bool f32 = d.normalize != 0;
+  if (d.src_kind == BANDCU_SRC_GRAY && d.cvt == BANDCU_CVT_NONE) return packed_pick2<1, BANDCU_CVT_NONE, 1>(up, f32);
+  if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_NONE) return packed_pick2<3, BANDCU_CVT_NONE, 3>(up, f32);
+  if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_RGB2GRAY) return packed_pick2<3, BANDCU_CVT_RGB2GRAY, 1>(up, f32);
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_NONE) return packed_pick2<4, BANDCU_CVT_NONE, 4>(up, f32);
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2GRAY) return packed_pick2<4, BANDCU_CVT_RGBA2GRAY, 1>(up, f32);
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2RGB) return packed_pick2<4, BANDCU_CVT_RGBA2RGB, 3>(up, f32);
+  return nullptr;
+}
+
+int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
+                  cudaStream_t stream) {
+  PackedKernel kern = packed_pick(d);
+  if (!kern) return BANDCU_E_UNSUPPORTED;
+  bool in4, out16;
+  if (batch.table) {
+    if (!hints.valid) return BANDCU_E_UNSUPPORTED;
+    in4 = hints.aligned16;
+    out16 = hints.out_aligned16;
+  } else {
+    in4 = (reinterpret_cast<uintptr_t>(batch.first.p0) & 3) == 0 && (n == 1 || batch.in_stride % 4 == 0);
+    out16 = (reinterpret_cast<uintptr_t>(batch.first.out) & 15) == 0 && (n == 1 || batch.out_stride % 16 == 0);
+  }
+  if (d.src_kind == BANDCU_SRC_RGBA && !(in4 && d.stride0 % 4 == 0)) return BANDCU_E_UNSUPPORTED;  // 32-bit pixel loads
+  PackedParams P;
+  memset(&P, 0, sizeof(P));
+  P.sw = d.vw; P.sh = d.vh; P.stride0 = d.stride0;
+  P.dw = d.dst_width; P.dh = d.dst_height;
+  P.x0 = d.x0; P.y0 = d.y0; P.dx = d.dx; P.dy = d.dy; P.max_y = d.max_y; P.linear = d.linear;
+  P.dst_row_stride = d.dst_row_stride;
+  P.vec_ok = (out16 && d.dst_row_stride % 16 == 0) ? 1 : 0;
+  P.lut = p->lut_dev;
+  dim3 block(32, 8, 1);
+  dim3 grid((d.dst_width + 127) / 128, (d.dst_height + 7) / 8, 1);
+  for (int done = 0; done < n;) {
+    const int chunk = n - done > 65535 ? 65535 : n - done;
+    P.batch = batch;
+    if (P.batch.table) {
+      P.batch.table += done;
+    } else {
+      P.batch.first.p0 += (long long)done * batch.in_stride;
+      P.batch.first.out += (long long)done * batch.out_stride;
+    }
+    grid.z = chunk;
+    kern<<<grid, block, 0, stream>>>(P);
+    count_launch();
+    done += chunk;
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace bandcu

@@ -182,11 +182,14 @@ def c1_latency(steps):
     return out
 
 
-def c5_cases(steps, cpu):
+C5_PAIRS = [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (64, 128), (64, 256), (64, 512),
+            (64, 1024), (64, 2048)]
+
+
+def c5_cases(steps, cpu, pairs=None):
     lines = []
     from oracle import oracle as O
-    for S_, D_ in [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (64, 128), (64, 256), (64, 512),
-                   (64, 1024), (64, 2048)]:
+    for S_, D_ in (pairs or C5_PAIRS):
         n = int(max(8, min(2048, 1.0e9 // (4 * S_ * S_ + 3 * D_ * D_))))
         # (i) AutoConvert (empty builder) into a u8 RGB tensor
         rb = hotpath.ResidentBatch([], n, S_, S_, "RGBA", np.uint8, (1, D_, D_, 3))
@@ -231,6 +234,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--cpu", action="store_true")
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--c5-pairs", default="", help="e.g. 64:2048,2048:1024 (default: the full sweep)")
     a = ap.parse_args()
     hotpath.set_device(a.device)
     want = set(a.configs.split(","))
@@ -260,7 +264,8 @@ def main():
                     "achieved_GBps": tot_bytes / (tot_ms * 1e-3) / 1e9,
                     "frac_of_measured_hbm": tot_bytes / (tot_ms * 1e-3) / 1e9 / peak()})
     if "c5" in want:
-        out += c5_cases(a.steps, a.cpu)
+        pairs = [tuple(int(v) for v in p.split(":")) for p in a.c5_pairs.split(",") if p] or None
+        out += c5_cases(a.steps, a.cpu, pairs)
     for line in out:
         print(json.dumps(line), flush=True)
 
