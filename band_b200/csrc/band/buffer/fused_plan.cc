@@ -824,6 +824,20 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
       if (bandcu_pointer_kind((*inputs[f])[k].data) != 1) { zero_copy = false; break; }
   }
   const bool in_staged = in_host && !zero_copy;
+  // Zero-copy output: the staged kernel assembles rows in shared memory and pushes them into PINNED host tensors
+  // with bulk stores, so results cross PCIe while the next source rows are being pulled (both directions of the
+  // link busy at once) and neither a staging buffer nor a D2H copy exists. Needs 16-byte granularity.
+  bool zc_out = out_host && writes_output_ && IsSingleFastLaunch() && getenv("BAND_NO_ZERO_COPY") == nullptr &&
+                output_.num_planes == 1 && output_.row_stride[0] % 16 == 0 &&
+                (static_cast<size_t>(segments_[0].pixel.dst_width) * segments_[0].pixel.channels *
+                 GetDataTypeBytes(output_.dtype)) % 16 == 0;
+  for (int f = 0; zc_out && f < m; ++f) {
+    const unsigned char* p = (*outputs[f])[0].data;
+    if ((reinterpret_cast<uintptr_t>(p) & 15) != 0 || bandcu_pointer_kind(p) != 1) zc_out = false;
+  }
+  if (IsSingleFastLaunch() && bandcu_plan_set_host_output(segments_[0].plan, zc_out ? 1 : 0) != BANDCU_OK)
+    return CudaError("bandcu_plan_set_host_output");
+  if (zc_out) out_host = false;  // from here on the tensors are addressed like device memory
   std::vector<HostRanges> in_r, out_r;
   size_t in_step = 0, out_step = 0;
   bool in_uniform = false, out_uniform = false;

@@ -129,6 +129,12 @@ int bandcu_plan_destroy(BandCuPlan* plan) {
 
 int bandcu_plan_is_fast(const BandCuPlan* plan) { return plan && plan->fast ? 1 : 0; }
 
+int bandcu_plan_set_host_output(BandCuPlan* plan, int on) {
+  if (!plan) return fail(BANDCU_E_INVALID, "plan_set_host_output: null plan");
+  if (plan->fast) fast_plan_set_bulk_store(plan->fast, on);
+  return BANDCU_OK;
+}
+
 static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hints, int n, cudaStream_t s) {
   if (plan->fast) {
     int e = launch_fast(plan->fast, plan->d, b, hints, n, s);

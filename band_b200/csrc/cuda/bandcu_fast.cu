@@ -56,6 +56,9 @@ struct FastParams {
   int groups_per_frame;
   long long n_items;
   int use_bulk;        // 1: cp.async.bulk staging, 0: producer-warp byte copies
+  int out_row_bytes;   // dw * 3 * sizeof(OT)
+  int out_buf_bytes;   // BULKOUT: R * out_row_bytes (one of two output staging buffers)
+  int off_out;         // BULKOUT: byte offset of the output staging buffers in shared memory
   const void* lut;     // 256 x float (normalize) or nullptr
   BatchArgs batch;
 };
@@ -64,6 +67,7 @@ struct FastPlan {
   void* lut_dev;
   int num_sms;
   int R, S;
+  int bulk_store;  // results leave through shared memory + cp.async.bulk stores (outputs in pinned host memory)
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -94,6 +98,13 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                    smem_u32(smem_dst)),
                "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
+}
+
+__device__ __forceinline__ void bulk_s2g(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 // Source rows one output row samples (ScaleARGBBilinearDown row stepping).
@@ -253,7 +264,12 @@ __device__ __forceinline__ uint32_t hblend_pair_raw(uint32_t v2, uint32_t wp) { 
 
 constexpr int kLutCopies = 8;  // the Normalize table is replicated so that lanes l and l' (l != l' mod 8) never collide
 
-template <typename OT, bool VU>
+// BULKOUT: the tensors live in PINNED HOST memory. Direct 12-byte stores would cross PCIe as 32-byte write
+// TLPs (measured: 5x slower than a copy); instead an item's rows are assembled in one of two shared-memory
+// output buffers and leave as cp.async.bulk stores (whole rows, maximum-payload TLPs), which overlap the
+// producer's bulk loads of the next items on the other direction of the link (scripts/pcie_tma_probe.cu:
+// 49 GB/s in + 26 GB/s out at once, against 52 GB/s total when a copy engine drains a staging buffer).
+template <typename OT, bool VU, bool BULKOUT>
 __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kOffFull);
@@ -296,6 +312,8 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
   const uint32_t pitch = (uint32_t)P.row_pitch;
   int s = 0;
   uint32_t wrap = 0;
+  uint32_t ob = 0;  // BULKOUT: which output buffer this item fills
+  const long long orow_stride = BULKOUT ? (long long)P.out_row_bytes : P.dst_row_stride;
   for (long long item = blockIdx.x; item < P.n_items; item += gridDim.x) {
     const uint32_t stage = sbase + kOffStages + (uint32_t)s * (uint32_t)P.stage_bytes;
     const uint32_t ri = sbase + kOffRowInfo + (uint32_t)s * (kMaxRows * 4u);
@@ -303,7 +321,14 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
     const int g = (int)(item - (long long)f * P.groups_per_frame);
     const int oy0 = g * P.R;
     const int nrows = min(P.R, P.dh - oy0);
-    uint8_t* gout = frame_ptrs(P.batch, f).out + (long long)oy0 * P.dst_row_stride;
+    uint8_t* const gdst = frame_ptrs(P.batch, f).out + (long long)oy0 * P.dst_row_stride;
+    uint8_t* gout = gdst;
+    if (BULKOUT) {
+      // the bulk store issued two items ago has finished READING this buffer
+      if (col == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      named_bar_sync(1, P.cols);
+      gout = smem + P.off_out + ob * (uint32_t)P.out_buf_bytes;
+    }
     mbar_wait(&full[s], wrap & 1);
 
     for (int pass = 0; pass < P.passes; ++pass) {
@@ -318,7 +343,7 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
         uint32_t row = stage;                                   // slot 0 of output row j
         uint8_t* o = gout + (size_t)ox * (3 * sizeof(OT));      // output pixel of row j
 #pragma unroll 2
-        for (int j = 0; j < nrows; ++j, row += 4u * pitch, o += P.dst_row_stride) {
+        for (int j = 0; j < nrows; ++j, row += 4u * pitch, o += orow_stride) {
           const uint32_t info = lds_u32(ri + 4u * (uint32_t)j);
           const uint32_t w1 = info & 0xFFu, w0 = 256u - w1;
           const ChromaPair ctop = chroma_pair<VU>(row + cL, row + cR);
@@ -345,7 +370,23 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
     if (++s == P.S) { s = 0; ++wrap; }
+    if (BULKOUT) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk engine
+      named_bar_sync(1, P.cols);
+      if (col == 0) {
+        const uint32_t src = sbase + (uint32_t)P.off_out + ob * (uint32_t)P.out_buf_bytes;
+        if (P.dst_row_stride == (long long)P.out_row_bytes) {
+          bulk_s2g(gdst, src, (uint32_t)(nrows * P.out_row_bytes));
+        } else {
+          for (int j = 0; j < nrows; ++j)
+            bulk_s2g(gdst + (long long)j * P.dst_row_stride, src + (uint32_t)(j * P.out_row_bytes), (uint32_t)P.out_row_bytes);
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      ob ^= 1u;
+    }
   }
+  if (BULKOUT && col == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores complete before the CTA retires
 }
 
 // Builds the Normalize table with the same device arithmetic as the generic kernel.
@@ -406,14 +447,15 @@ void fast_plan_destroy(FastPlan* p) {
   delete p;
 }
 
+typedef void (*FastKernel)(const FastParams);
 template <typename OT>
-static int launch_fast_t(FastParams& P, bool vu, int grid, int block, size_t smem, cudaStream_t stream) {
-  auto kern = vu ? fast_nv_bilinear_down_kernel<OT, true> : fast_nv_bilinear_down_kernel<OT, false>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return (int)e;
-  kern<<<grid, block, smem, stream>>>(P);
-  count_launch();
-  return (int)cudaGetLastError();
+static FastKernel pick_kernel(bool vu, bool bulk_out) {
+  if (bulk_out) return vu ? fast_nv_bilinear_down_kernel<OT, true, true> : fast_nv_bilinear_down_kernel<OT, false, true>;
+  return vu ? fast_nv_bilinear_down_kernel<OT, true, false> : fast_nv_bilinear_down_kernel<OT, false, false>;
+}
+
+void fast_plan_set_bulk_store(FastPlan* p, int on) {
+  if (p) p->bulk_store = on ? 1 : 0;
 }
 
 int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
@@ -442,11 +484,25 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.R = p->R; P.S = p->S;
   P.passes = (d.dst_width + 511) / 512;
   P.cols = (((d.dst_width + P.passes - 1) / P.passes) + 31) / 32 * 32;
+  const int esize = d.normalize ? 4 : 1;
+  P.out_row_bytes = d.dst_width * 3 * esize;
+  // bulk stores need 16-byte granularity everywhere (row length, row stride, every output pointer)
+  bool out_aligned;
+  if (batch.table) out_aligned = hints.valid && hints.out_aligned16;
+  else out_aligned = ((reinterpret_cast<uintptr_t>(batch.first.out) & 15) == 0) && (n == 1 || batch.out_stride % 16 == 0);
+  const bool bulk_out = p->bulk_store && out_aligned && (P.out_row_bytes % 16 == 0) && (d.dst_row_stride % 16 == 0);
   const size_t smem_cap = 226 * 1024;
-  while (P.S > 2 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.S;
-  while (P.R > 1 && kOffStages + (size_t)P.S * P.R * 4 * P.row_pitch > smem_cap) --P.R;
+  auto need = [&](int S, int R) {
+    size_t b = kOffStages + (size_t)S * R * 4 * P.row_pitch;
+    if (bulk_out) b = ((b + 127) / 128) * 128 + 2 * (size_t)R * P.out_row_bytes;
+    return b;
+  };
+  while (P.S > 2 && need(P.S, P.R) > smem_cap) --P.S;
+  while (P.R > 1 && need(P.S, P.R) > smem_cap) --P.R;
   P.stage_bytes = P.R * 4 * P.row_pitch;
-  const size_t smem = kOffStages + (size_t)P.S * P.stage_bytes;
+  P.out_buf_bytes = P.R * P.out_row_bytes;
+  P.off_out = (int)(((kOffStages + (size_t)P.S * P.stage_bytes + 127) / 128) * 128);
+  const size_t smem = need(P.S, P.R);
   if (smem > smem_cap) return BANDCU_E_UNSUPPORTED;
   const int block = 32 + P.cols;
   P.groups_per_frame = (d.dst_height + P.R - 1) / P.R;
@@ -465,26 +521,18 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   const char* nb = getenv("BANDCU_FAST_NO_BULK");
   if (nb && nb[0] == '1') P.use_bulk = 0;
   // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
+  FastKernel kern = d.normalize ? pick_kernel<float>(vu, bulk_out) : pick_kernel<uint8_t>(vu, bulk_out);
   int per_sm = 1;
-  {
-    cudaError_t e;
-    if (d.normalize) {
-      auto kern = vu ? fast_nv_bilinear_down_kernel<float, true> : fast_nv_bilinear_down_kernel<float, false>;
-      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
-    } else {
-      auto kern = vu ? fast_nv_bilinear_down_kernel<uint8_t, true> : fast_nv_bilinear_down_kernel<uint8_t, false>;
-      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
-    }
-    if (e != cudaSuccess) return (int)e;
-    if (per_sm < 1) return BANDCU_E_UNSUPPORTED;
-  }
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
+  if (e != cudaSuccess) return (int)e;
+  if (per_sm < 1) return BANDCU_E_UNSUPPORTED;
   long long want = (long long)p->num_sms * per_sm;
   int grid = (int)(P.n_items < want ? P.n_items : want);
   if (grid < 1) grid = 1;
-  return d.normalize ? launch_fast_t<float>(P, vu, grid, block, smem, stream)
-                     : launch_fast_t<uint8_t>(P, vu, grid, block, smem, stream);
+  kern<<<grid, block, smem, stream>>>(P);
+  count_launch();
+  return (int)cudaGetLastError();
 }
 
 }  // namespace bandcu

@@ -20,6 +20,8 @@ struct FastPlan;
 bool fast_plan_supported(const BandCuPlanDesc& d);
 int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out);
 void fast_plan_destroy(FastPlan* p);
+// results leave through shared memory + bulk stores (tensors in pinned host memory) when the batch allows it
+void fast_plan_set_bulk_store(FastPlan* p, int on);
 // What the host knows about a pointer-table batch (the table itself lives in device memory).
 struct TableHints {
   bool valid = false;    // false: strided batch, derive everything from BatchArgs::first

@@ -140,6 +140,11 @@ BANDCU_API int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan)
 BANDCU_API int bandcu_plan_destroy(BandCuPlan* plan);
 /* 1 if the plan runs on the staged/specialised fast kernel, 0 for the generic one. */
 BANDCU_API int bandcu_plan_is_fast(const BandCuPlan* plan);
+/* Output hand-off of the staged kernel. 0 (default): direct global stores (tensors in HBM). 1: the tensors of the
+ * following runs live in PINNED HOST memory; rows are assembled in shared memory and leave as cp.async.bulk stores,
+ * so results cross PCIe inside the kernel while it pulls the next source rows (no staging buffer, no D2H copy).
+ * Ignored by plans that do not run on the staged kernel (bandcu_plan_is_fast() == 0). */
+BANDCU_API int bandcu_plan_set_host_output(BandCuPlan* plan, int on);
 /* Run n frames whose pointers advance by a fixed stride (bytes). */
 BANDCU_API int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* first, long long in_stride,
                                        long long out_stride, int n, void* stream);

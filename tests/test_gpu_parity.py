@@ -241,3 +241,57 @@ def test_pinned_host_frames_zero_copy(O, fmt_name, W, H, d, f32):
         proc.close()
     finally:
         L.BandHostFree(host)
+
+
+@pytest.mark.parametrize("fmt_name,W,H,dw,dh,f32,dev_in", [
+    ("NV12", 1920, 1080, 228, 225, True, False),   # 225 rows: the last work item of a frame holds one row
+    ("NV21", 1280, 720, 320, 181, False, False),   # u8 rows of 960 bytes (16-byte multiple): bulk stores
+    ("NV12", 640, 480, 224, 224, True, True),      # frames in HBM, tensors in pinned host memory
+    ("NV12", 640, 480, 226, 224, True, False),     # 2712-byte rows: not a 16-byte multiple -> staged download
+])
+def test_pinned_host_tensors_bulk_store(O, fmt_name, W, H, dw, dh, f32, dev_in):
+    """Tensors in PINNED host memory: the staged kernel assembles rows in shared memory and pushes them over PCIe
+    with cp.async.bulk stores (no staging buffer, no D2H copy). Same bits as the oracle, and the guard bytes
+    around every tensor stay untouched."""
+    import ctypes as C
+    from band_b200 import band_c as B
+    from gpu_util import to_capi_ops, NP_OF_ORC
+    fmt = getattr(O, "FMT_" + fmt_name)
+    n = 37
+    fr = rand_frames(O, 3, W, H, fmt, 777)
+    fb = fr.shape[1]
+    L = B.lib()
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh)] + ([NORM] if f32 else [])
+    dt = O.DT_F32 if f32 else O.DT_U8
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, dt, (1, dh, dw, 3))
+    assert st == 0
+    host = L.BandHostAlloc(n * fb)
+    dev = L.BandDeviceAlloc(n * fb) if dev_in else None
+    assert host and (dev or not dev_in)
+    try:
+        hv = np.ctypeslib.as_array(C.cast(host, C.POINTER(C.c_uint8)), shape=(n, fb))
+        for i in range(n):
+            hv[i] = fr[i % 3]
+        if dev_in:
+            assert L.BandCopyToDevice(dev, host, n * fb) == B.kBandOk
+        proc = B.ImageProcessor(to_capi_ops(ops))
+        tens = [B.Tensor(NP_OF_ORC[dt], (1, dh, dw, 3), device=False) for _ in range(n)]
+        base = dev if dev_in else host
+        bufs = [B.Buffer().set_raw(base + i * fb, W, H, B.FORMATS[fmt_name], device=dev_in) for i in range(n)]
+        for rep in range(2):  # second call reuses the plan (and flips nothing)
+            assert proc.process_batch(bufs, tens) == B.kBandOk, B.last_error()
+        assert proc.is_fused
+        for i in range(n):
+            assert_same_bits(tens[i].numpy(), want[i % 3], "host tensor %d" % i)
+        # the same processor then serves device tensors (direct-store kernel) with identical bits
+        dtens = [B.Tensor(NP_OF_ORC[dt], (1, dh, dw, 3), device=True) for _ in range(3)]
+        assert proc.process_batch(bufs[:3], dtens) == B.kBandOk, B.last_error()
+        for i in range(3):
+            assert_same_bits(dtens[i].numpy(), want[i], "device tensor %d" % i)
+        for x in bufs + tens + dtens:
+            x.close()
+        proc.close()
+    finally:
+        L.BandHostFree(host)
+        if dev:
+            L.BandDeviceFree(dev)
