@@ -40,6 +40,9 @@ EXPORTED = [
     "BandImageProcessorSynchronize", "BandImageProcessorProcessBuffers", "BandImageProcessorGetStream", "BandImageProcessorIsFused",
     "BandCudaGetDeviceCount", "BandCudaSetDevice", "BandHostAlloc", "BandHostFree", "BandDeviceAlloc",
     "BandDeviceFree", "BandCopyToDevice", "BandCopyToHost", "BandCudaLaunchCount", "BandGetLastError",
+    "BandTensorRingBufferCreate", "BandTensorRingBufferDelete", "BandTensorRingBufferAlloc",
+    "BandTensorRingBufferIsHandleValid", "BandTensorRingBufferGetSlot", "BandTensorRingBufferPutTensor",
+    "BandTensorRingBufferGetTensor",
 ]
 
 
@@ -107,6 +110,15 @@ def lib():
     L.BandCopyToHost.argtypes = [vp, vp, sz]
     L.BandCudaLaunchCount.restype = C.c_longlong
     L.BandGetLastError.restype = C.c_char_p
+    L.BandTensorRingBufferCreate.argtypes = [C.POINTER(vp), C.POINTER(ci), sz, ci, ci]
+    L.BandTensorRingBufferCreate.restype = vp
+    L.BandTensorRingBufferDelete.argtypes = [vp]
+    L.BandTensorRingBufferAlloc.argtypes = [vp]
+    L.BandTensorRingBufferIsHandleValid.argtypes = [vp, ci]
+    L.BandTensorRingBufferGetSlot.argtypes = [vp, ci, ci]
+    L.BandTensorRingBufferGetSlot.restype = vp
+    L.BandTensorRingBufferPutTensor.argtypes = [vp, vp, ci, ci]
+    L.BandTensorRingBufferGetTensor.argtypes = [vp, vp, ci, ci]
     _lib = L
     return L
 
@@ -162,6 +174,65 @@ class Tensor:
     def close(self):
         if self.handle:
             lib().BandTensorDelete(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class SlotTensor(Tensor):
+    """A ring slot lent by BandTensorRingBufferGetSlot: owned by the ring, never deleted here."""
+
+    def __init__(self, handle, np_dtype, dims, device):
+        self.handle = handle
+        self.np_dtype = np.dtype(np_dtype)
+        self.dims = tuple(int(d) for d in dims)
+        self.device = bool(device)
+
+    def close(self):
+        self.handle = None
+
+
+class TensorRingBuffer:
+    """BandTensorRingBuffer (additive; band::TensorRingBuffer with host or HBM slots)."""
+
+    def __init__(self, model_tensors, tensor_indices, size=128, device=False):
+        n = len(model_tensors)
+        self.model_tensors = list(model_tensors)
+        self.indices = [int(i) for i in tensor_indices]
+        self.device = bool(device)
+        ta = (C.c_void_p * n)(*[t.handle for t in model_tensors])
+        ia = (C.c_int * n)(*self.indices)
+        self.handle = lib().BandTensorRingBufferCreate(ta, ia, n, int(size),
+                                                       kBandDeviceMemory if device else kBandHostMemory)
+        if not self.handle:
+            raise BandError("BandTensorRingBufferCreate failed: " + last_error())
+
+    def alloc(self):
+        return lib().BandTensorRingBufferAlloc(self.handle)
+
+    def is_handle_valid(self, handle):
+        return bool(lib().BandTensorRingBufferIsHandleValid(self.handle, handle))
+
+    def slot(self, tensor_index, handle):
+        h = lib().BandTensorRingBufferGetSlot(self.handle, tensor_index, handle)
+        if not h:
+            return None
+        like = self.model_tensors[self.indices.index(tensor_index)]
+        return SlotTensor(h, like.np_dtype, like.dims, self.device)
+
+    def put(self, src, tensor_index, handle):
+        return lib().BandTensorRingBufferPutTensor(self.handle, src.handle, tensor_index, handle)
+
+    def get(self, dst, tensor_index, handle):
+        return lib().BandTensorRingBufferGetTensor(self.handle, dst.handle, tensor_index, handle)
+
+    def close(self):
+        if self.handle:
+            lib().BandTensorRingBufferDelete(self.handle)
             self.handle = None
 
     def __del__(self):

@@ -50,8 +50,20 @@ Tensor::Tensor(DataType type, const std::vector<int>& dims, const std::string& n
   Allocate(GetBytes());
 }
 
+Tensor::Tensor(const interface::ITensor* like, MemorySpace space, char* external)
+    : type_(like->GetType()),
+      quantization_({QuantizationType::kNoQuantization, nullptr}),
+      dims_(like->GetDims(), like->GetDims() + like->GetNumDims()),
+      data_(external),
+      name_(like->GetName()),
+      space_(space),
+      owns_(false) {
+  absl::Status status = SetQuantization(like->GetQuantization());
+  if (!status.ok()) BAND_LOG(LogSeverity::kError, "Failed to set quantization: %s", status.message().c_str());
+}
+
 Tensor::~Tensor() {
-  if (data_) {
+  if (data_ && owns_) {
     if (space_ == MemorySpace::kDevice) bandcu_free(data_);
     else if (pinned_) bandcu_host_free(data_);
     else delete[] data_;

@@ -18,6 +18,9 @@ class Tensor : public interface::ITensor {
   // additive
   Tensor(DataType type, const std::vector<int>& dims, const std::string& name = "",
          MemorySpace space = MemorySpace::kHost);
+  // additive: a tensor shaped like `like` over EXTERNAL memory of the given space (not owned, never freed here);
+  // the slots of a TensorRingBuffer are such views into the ring's slab. external == nullptr => zero-byte tensor.
+  Tensor(const interface::ITensor* like, MemorySpace space, char* external);
   ~Tensor();
 
   DataType GetType() const override;
@@ -45,6 +48,7 @@ class Tensor : public interface::ITensor {
   std::string name_;
   MemorySpace space_ = MemorySpace::kHost;
   bool pinned_ = false;
+  bool owns_ = true;
 };
 }  // namespace band
 #endif  // BAND_TENSOR_H_

@@ -173,6 +173,28 @@ BAND_CAPI_EXPORT extern void* BandDeviceAlloc(size_t bytes);
 BAND_CAPI_EXPORT extern void BandDeviceFree(void* ptr);
 BAND_CAPI_EXPORT extern BandStatus BandCopyToDevice(void* device_dst, const void* host_src, size_t bytes);
 BAND_CAPI_EXPORT extern BandStatus BandCopyToHost(void* host_dst, const void* device_src, size_t bytes);
+/* ---- ADDITIVE: the engine's tensor ring with device-resident slots ----
+ * band::TensorRingBuffer (/root/reference/band/tensor_ring_buffer.h:33-66) is what Engine::RequestAsync copies
+ * model inputs into (/root/reference/band/engine.cc:506-520). Here its slots can live in HBM (one slab) and a slot
+ * can be lent out, so BandImageProcessorProcess[Batch] writes model input straight into the ring:
+ *     int h = BandTensorRingBufferAlloc(ring);
+ *     BandImageProcessorProcess(proc, frame, BandTensorRingBufferGetSlot(ring, tensor_index, h));
+ * `model_tensors` give the shape/type of each slot tensor (they are not retained); `tensor_indices[i]` is the
+ * model's index of tensor i. Slot tensors are owned by the ring: never BandTensorDelete them. */
+typedef struct BandTensorRingBuffer BandTensorRingBuffer;
+BAND_CAPI_EXPORT extern BandTensorRingBuffer* BandTensorRingBufferCreate(BandTensor* const* model_tensors,
+                                                                         const int* tensor_indices,
+                                                                         size_t num_tensors, int size,
+                                                                         BandMemorySpace space);
+BAND_CAPI_EXPORT extern void BandTensorRingBufferDelete(BandTensorRingBuffer* ring);
+BAND_CAPI_EXPORT extern int BandTensorRingBufferAlloc(BandTensorRingBuffer* ring);
+BAND_CAPI_EXPORT extern int BandTensorRingBufferIsHandleValid(BandTensorRingBuffer* ring, int handle);
+BAND_CAPI_EXPORT extern BandTensor* BandTensorRingBufferGetSlot(BandTensorRingBuffer* ring, int tensor_index,
+                                                                int handle);
+BAND_CAPI_EXPORT extern BandStatus BandTensorRingBufferPutTensor(BandTensorRingBuffer* ring, BandTensor* src,
+                                                                 int tensor_index, int handle);
+BAND_CAPI_EXPORT extern BandStatus BandTensorRingBufferGetTensor(BandTensorRingBuffer* ring, BandTensor* dst,
+                                                                 int tensor_index, int handle);
 /* Kernel launches issued so far by this process (for harness accounting). */
 BAND_CAPI_EXPORT extern long long BandCudaLaunchCount();
 BAND_CAPI_EXPORT extern const char* BandGetLastError();
