@@ -303,6 +303,8 @@ absl::Status ChainLowering::EmitInto(int dst_slot, const ImageLayout& dst) {
   d.stride0 = static_cast<int>(v.src.row_stride[0]);
   d.stride_uv = static_cast<int>(v.src.row_stride[1]);
   d.pixel_stride_uv = static_cast<int>(v.src.pixel_stride[1]);
+  d.src_width = v.src.width;
+  d.src_height = v.src.height;
   d.vw = v.pre_w;
   d.vh = v.pre_h;
   d.luma_map = v.luma;

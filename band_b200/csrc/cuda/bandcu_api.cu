@@ -39,6 +39,7 @@ using namespace bandcu;
 struct BandCuPlan {
   BandCuPlanDesc d;
   FastPlan* fast;
+  TilePlan* tile;
   PackedPlan* packed;
   // pointer-table staging for bandcu_plan_run()
   BandCuFrame* table_dev;
@@ -104,6 +105,14 @@ int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan) {
       return fail(e, "plan_create: fast plan setup");
     }
   }
+  if (tile_plan_supported(p->d)) {  // also built next to a fast plan: batches the row-staged kernel refuses land here
+    int e = tile_plan_create(p->d, &p->tile);
+    if (e != BANDCU_OK && e != BANDCU_E_UNSUPPORTED) {
+      if (p->fast) fast_plan_destroy(p->fast);
+      delete p;
+      return fail(e, "plan_create: tile plan setup");
+    }
+  }
   if (!p->fast && packed_plan_supported(p->d)) {
     int e = packed_plan_create(p->d, &p->packed);
     if (e != BANDCU_OK) {
@@ -122,6 +131,7 @@ int bandcu_plan_destroy(BandCuPlan* plan) {
   if (plan->table_dev) (void)cudaFree(plan->table_dev);
   if (plan->table_host) (void)cudaFreeHost(plan->table_host);
   if (plan->fast) fast_plan_destroy(plan->fast);
+  if (plan->tile) tile_plan_destroy(plan->tile);
   if (plan->packed) packed_plan_destroy(plan->packed);
   delete plan;
   return BANDCU_OK;
@@ -135,21 +145,34 @@ int bandcu_plan_set_host_output(BandCuPlan* plan, int on) {
   return BANDCU_OK;
 }
 
+// BANDCU_TRACE=1: one stderr line per batch naming the kernel family that ran it (diagnostics only).
+static void trace_path(const char* what, const BandCuPlan* plan, int n) {
+  static const bool on = getenv("BANDCU_TRACE") && getenv("BANDCU_TRACE")[0] == '1';
+  if (on) fprintf(stderr, "[bandcu] %s kernel: %d frame(s), plan fast=%d tile=%d packed=%d\n", what, n, plan->fast != nullptr,
+                  plan->tile != nullptr, plan->packed != nullptr);
+}
+
 static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hints, int n, cudaStream_t s) {
   if (plan->fast) {
     int e = launch_fast(plan->fast, plan->d, b, hints, n, s);
-    if (e == BANDCU_OK) return BANDCU_OK;
+    if (e == BANDCU_OK) { trace_path("row-staged", plan, n); return BANDCU_OK; }
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: fast kernel launch");
     // this batch's pointers/strides do not meet the staged kernel's alignment
     // rules: the generic kernel computes the identical result.
   }
+  if (plan->tile) {
+    int e = launch_tile(plan->tile, plan->d, b, hints, n, s);
+    if (e == BANDCU_OK) { trace_path("tile-staged", plan, n); return BANDCU_OK; }
+    if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: tile kernel launch");
+  }
   if (plan->packed) {
     int e = launch_packed(plan->packed, plan->d, b, hints, n, s);
-    if (e == BANDCU_OK) return BANDCU_OK;
+    if (e == BANDCU_OK) { trace_path("packed", plan, n); return BANDCU_OK; }
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: packed kernel launch");
   }
   int e = launch_generic(plan->d, b, n, s);
   if (e != 0) return fail(e, "plan_run: generic kernel launch");
+  trace_path("generic", plan, n);
   return BANDCU_OK;
 }
 
@@ -195,7 +218,13 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
   hints.semi_planar = frames[0].pu && frames[0].pv;
   hints.aligned16 = true;
   hints.out_aligned16 = true;
+  hints.planes_aligned4 = true;
+  hints.planes_aligned16 = true;
   for (int i = 0; i < n; ++i) {
+    const uintptr_t bits = reinterpret_cast<uintptr_t>(frames[i].p0) | reinterpret_cast<uintptr_t>(frames[i].pu) |
+                           reinterpret_cast<uintptr_t>(frames[i].pv);
+    if (bits & 3) hints.planes_aligned4 = false;
+    if (bits & 15) hints.planes_aligned16 = false;
     if (reinterpret_cast<uintptr_t>(frames[i].p0) & 15) hints.aligned16 = false;
     if (reinterpret_cast<uintptr_t>(frames[i].out) & 15) hints.out_aligned16 = false;
   }

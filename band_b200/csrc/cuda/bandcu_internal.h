@@ -29,9 +29,19 @@ struct TableHints {
   bool vu = false;       // V first (NV21)
   bool aligned16 = false;  // every luma / chroma base pointer is 16-byte aligned
   bool out_aligned16 = false;  // every output pointer is 16-byte aligned
+  bool planes_aligned4 = false;  // every p0 / pu / pv pointer is 4-byte aligned
+  bool planes_aligned16 = false;  // ... 16-byte aligned
 };
 // returns BANDCU_E_UNSUPPORTED if this particular batch (layout) cannot use it
 int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
+                cudaStream_t stream);
+// Tile-staged 4:2:0 -> RGB -> bilinear-down [-> Normalize] behind any Crop/Rotate/Flip index map, planar or
+// semi-planar chroma (bandcu_tile.cu).
+struct TilePlan;
+bool tile_plan_supported(const BandCuPlanDesc& d);
+int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out);  // BANDCU_E_UNSUPPORTED: tiles do not fit shared memory
+void tile_plan_destroy(TilePlan* p);
+int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
                 cudaStream_t stream);
 // Packed (gray / RGB / RGBA) bilinear Resize without index maps: four output pixels per thread.
 struct PackedPlan;

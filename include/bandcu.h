@@ -123,6 +123,9 @@ typedef struct BandCuPlanDesc {
   int normalize;      /* 0: store u8 results; 1: out = (T)((T)(v - mean) / std) */
   float mean, std_;
   long long dst_row_stride; /* bytes between output rows (contiguous NHWC: dst_width*channels*sizeof(T)) */
+  /* luma dimensions of the SOURCE planes (before any index map); 0 = unknown, which only disables the tile-staged
+   * kernel (it stages whole 32-bit words and must know they stay inside the plane rows) */
+  int src_width, src_height;
 } BandCuPlanDesc;
 
 typedef struct BandCuPlan BandCuPlan;
