@@ -34,13 +34,19 @@ struct TileParams {
   int v_first;         // interleaved: V is the first byte of a pair (NV21)
   int lut_f32;         // output goes through the Normalize table
   const float* lut;
+  int l_pitch, c_pitch;  // staged row pitches (bytes), the worst case over all tiles: launch constants
+  int l_rows_max, c_rows_max;  // staged rows, worst case (plane offsets in shared memory are launch constants too)
+  // Crop / Rotate / Flip compose into SIGNED PERMUTATIONS, so every mapped coordinate depends on the virtual row
+  // alone or on the virtual column alone and a shared-memory offset splits into f(row) + g(col):
+  //   luma(r,c)   = AL(tile) + lr_mul * r + lc_mul * c
+  //   chroma(r,c) = AC(tile) + cr_mul * ((cr_0 + cr_s * r) >> 1) + cc_mul * ((cc_0 + cc_s * c) >> 1)
+  int lr_mul, lc_mul;
+  int cr_0, cr_s, cr_mul, cc_0, cc_s, cc_mul;
+  int out_vec;         // output rows allow 128-bit (f32) / 32-bit (u8) stores
+  int l_lpr_shift, c_lpr_shift;  // log2(threads serving one staged row) for the luma / chroma planes
+  int off_terms;       // offset of the per-tile term tables in dynamic shared memory
 };
 
-struct TilePlan {
-  float* lut_dev;
-  int TR, TC;
-  size_t smem;
-};
 
 struct Rect {
   int r0, r1, c0, c1;  // inclusive
@@ -92,27 +98,31 @@ __host__ __device__ __forceinline__ int staged_pitch(int first_byte, int last_by
 }
 
 // G == 16: cp.async (LDGSTS) 16-byte copies, no register staging -- a thread's copies are all in flight at once.
-// G == 4 : 32-bit loads through registers (any word-aligned layout). No divisions inside the loop: (row, granule)
-// advance incrementally by blockDim.x.
+// G == 4 : 32-bit loads through registers (any word-aligned layout).
+// 2^lpr_shift threads serve one staged row (the next power of two >= granules per row, a launch constant), so the
+// loop has no division: (source, destination) advance by a fixed number of rows per pass.
 template <int G>
 __device__ __forceinline__ void stage_plane(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride,
-                                            int row0, int nrows, int first_byte, int pitch) {
+                                            int row0, int nrows, int first_byte, int pitch, int lpr_shift) {
   const int gpr = pitch / G;                       // granules per staged row
-  const int total = nrows * gpr;
-  const int step_r = (int)blockDim.x / gpr, step_g = (int)blockDim.x - step_r * gpr;
-  int r = (int)threadIdx.x / gpr, g = (int)threadIdx.x - r * gpr;
-  const uint8_t* src0 = plane + (long long)row0 * stride + (first_byte / G) * G;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const uint8_t* src = src0 + (long long)r * stride + g * G;
-    uint8_t* dst = smem_dst + r * pitch + g * G;
-    if (G == 16) {
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
-    } else {
-      *reinterpret_cast<uint32_t*>(dst) = __ldg(reinterpret_cast<const uint32_t*>(src));
+  const int lpr = 1 << lpr_shift;
+  const int rows_per_pass = (int)blockDim.x >> lpr_shift;
+  int r = (int)threadIdx.x >> lpr_shift;
+  const int g0 = (int)threadIdx.x & (lpr - 1);
+  if (g0 >= gpr) return;
+  const uint8_t* src = plane + (long long)(row0 + r) * stride + (first_byte / G) * G + g0 * G;
+  uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst) + (uint32_t)(r * pitch + g0 * G);
+  const long long src_step = (long long)rows_per_pass * stride;
+  const uint32_t dst_step = (uint32_t)(rows_per_pass * pitch);
+  for (; r < nrows; r += rows_per_pass, src += src_step, dst += dst_step) {
+    for (int g = g0, o = 0; g < gpr; g += lpr, o += lpr * G) {  // one trip unless a row has more than 32 granules
+      if (G == 16) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(src + o) : "memory");
+      } else {
+        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + o));
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(dst + o), "r"(v) : "memory");
+      }
     }
-    r += step_r;
-    g += step_g;
-    if (g >= gpr) { g -= gpr; ++r; }
   }
 }
 
@@ -144,99 +154,174 @@ __device__ __forceinline__ uint32_t t_vblend2(uint32_t top, uint32_t bot, uint32
   return ((top * w0 + bot * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
 }
 
-template <typename OT, int G>
+struct __align__(16) RowTerms {   // everything an output ROW contributes (32 bytes)
+  int lA, lB;       // luma offsets of virtual rows rA, rB
+  int kA, kB;       // chroma offsets
+  uint32_t w0, w1;  // InterpolateRow weights
+  int pad[2];
+};
+struct __align__(16) ColTerms {   // everything an output COLUMN contributes (32 bytes)
+  int lA, lB, kA, kB;
+  uint32_t wp;      // packed 7-bit column weights
+  int pad[3];
+};
+__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy) {
+  const BandCuPlanDesc& d = P.d;
+  long long y = (long long)d.y0 + (long long)oy * d.dy;
+  if (y > d.max_y) y = d.max_y;
+  const int yi = (int)(y >> 16);
+  RowTerms t;
+  t.w1 = d.linear ? 0u : (uint32_t)((y >> 8) & 255);
+  t.w0 = 256u - t.w1;
+  const int rA = min(max(yi, 0), d.vh - 1), rB = min(max(yi + 1, 0), d.vh - 1);
+  t.lA = P.lr_mul * rA;
+  t.lB = P.lr_mul * rB;
+  t.kA = P.cr_mul * ((P.cr_0 + P.cr_s * rA) >> 1);
+  t.kB = P.cr_mul * ((P.cr_0 + P.cr_s * rB) >> 1);
+  return t;
+}
+__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox) {
+  const BandCuPlanDesc& d = P.d;
+  const long long x = (long long)d.x0 + (long long)ox * d.dx;
+  const int xi = (int)(x >> 16);
+  const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
+  ColTerms t;
+  t.wp = xf | ((0x7fu ^ xf) << 16);
+  const int cA = min(max(xi, 0), d.vw - 1), cB = min(max(xi + 1, 0), d.vw - 1);
+  t.lA = P.lc_mul * cA;
+  t.lB = P.lc_mul * cB;
+  t.kA = P.cc_mul * ((P.cc_0 + P.cc_s * cA) >> 1);
+  t.kB = P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
+  return t;
+}
+// One output pixel from the staged planes: raw products, the 8-bit results sit in bits 23..30.
+__device__ __forceinline__ void tile_pixel(const uint8_t* sl, const uint8_t* su, const uint8_t* sv, const RowTerms& R,
+                                           const ColTerms& Cn, uint32_t& r, uint32_t& g, uint32_t& b) {
+  uint32_t tr, tg, tb, br, bg, bb;
+  {
+    const int oL = R.kA + Cn.kA, oR = R.kA + Cn.kB;
+    const TChroma ct = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
+    t_luma_pair_to_rgb(sl[R.lA + Cn.lA], sl[R.lA + Cn.lB], ct, tr, tg, tb);
+  }
+  if (R.w1) {
+    const int oL = R.kB + Cn.kA, oR = R.kB + Cn.kB;
+    const TChroma cb = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
+    t_luma_pair_to_rgb(sl[R.lB + Cn.lA], sl[R.lB + Cn.lB], cb, br, bg, bb);
+  } else {
+    br = tr; bg = tg; bb = tb;
+  }
+  r = t_vblend2(tr, br, R.w0, R.w1) * Cn.wp;
+  g = t_vblend2(tg, bg, R.w0, R.w1) * Cn.wp;
+  b = t_vblend2(tb, bb, R.w0, R.w1) * Cn.wp;
+}
+
+// SWAP: the luma map exchanges the axes (quarter-turns). Lanes then run along the output COLUMN so that a warp's
+// shared-memory reads walk consecutive source bytes (lanes along the output row would stride by whole staged rows:
+// 4-way bank conflicts measured, L1 at 84 %); each thread produces FOUR adjacent pixels of its output row and stores
+// them as 48 contiguous bytes (three 128-bit stores for f32). Without SWAP lanes run along the output row and a
+// warp stores 384 contiguous bytes per row.
+// The row and column terms of the tile (32 + 32 entries) are computed once by two warps while the cp.async copies
+// are in flight and read back as broadcasts.
+template <typename OT, int G, bool SWAP>
 __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __grid_constant__ TileParams P) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ float lut[256];
   const BandCuPlanDesc& d = P.d;
-  if (sizeof(OT) == 4) {
-    lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
-  }
-  const int tile = blockIdx.x;
-  const int ty = tile / P.tiles_x, tx = tile - ty * P.tiles_x;
-  const int oy0 = ty * P.TR, ox0 = tx * P.TC;
+  if (sizeof(OT) == 4) lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
+  const int oy0 = blockIdx.y * P.TR, ox0 = blockIdx.x * P.TC;
   const int oy1 = min(oy0 + P.TR, d.dst_height) - 1, ox1 = min(ox0 + P.TC, d.dst_width) - 1;
-  const FramePtrs f = frame_ptrs(P.batch, blockIdx.y);
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
 
   const Rect v = virtual_rect(d, oy0, oy1, ox0, ox1);
   Rect L, C;
   tile_rects(d, v, &L, &C);
-  // luma plane
-  const int l_first = L.c0, l_pitch = staged_pitch<G>(L.c0, L.c1);
-  const int l_rows = L.r1 - L.r0 + 1;
-  uint8_t* sl = smem;
-  stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, l_pitch);
-  // chroma plane(s)
   const int ps = d.pixel_stride_uv;
-  const int c_first = C.c0 * ps, c_last = C.c1 * ps + (P.interleaved ? 1 : 0);
-  const int c_pitch = staged_pitch<G>(c_first, c_last);
-  const int c_rows = C.r1 - C.r0 + 1;
-  uint8_t* su = sl + l_rows * l_pitch;
+  const int l_first = L.c0, c_first = C.c0 * ps;
+  const int l_rows = L.r1 - L.r0 + 1, c_rows = C.r1 - C.r0 + 1;
+  uint8_t* sl = smem;
+  uint8_t* su = sl + P.l_rows_max * P.l_pitch;
   uint8_t* sv;
+  stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift);
   if (P.interleaved) {
-    const uint8_t* base = P.v_first ? f.pv : f.pu;
-    stage_plane<G>(su, base, d.stride_uv, C.r0, c_rows, c_first, c_pitch);
+    stage_plane<G>(su, P.v_first ? f.pv : f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
     sv = su + (P.v_first ? 0 : 1);
     su = su + (P.v_first ? 1 : 0);
   } else {
-    sv = su + c_rows * c_pitch;
-    stage_plane<G>(su, f.pu, d.stride_uv, C.r0, c_rows, c_first, c_pitch);
-    stage_plane<G>(sv, f.pv, d.stride_uv, C.r0, c_rows, c_first, c_pitch);
+    sv = su + P.c_rows_max * P.c_pitch;
+    stage_plane<G>(su, f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
+    stage_plane<G>(sv, f.pv, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
   }
-  if (G == 16) asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+  if (G == 16) asm volatile("cp.async.commit_group;" ::: "memory");
+
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // 8 warps
+  RowTerms* rt = reinterpret_cast<RowTerms*>(smem + P.off_terms);        // [32], 32 bytes each
+  ColTerms* ct = reinterpret_cast<ColTerms*>(smem + P.off_terms + 1024);  // [32], 32 bytes each
+  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1));
+  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1));
+  if (G == 16) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
-  // affine address forms: luma(r,c) = AL + BL r + CL c over virtual coordinates; chroma over (r1>>1, c1>>1)
-  const int BL = d.luma_map.rr * l_pitch + d.luma_map.cr, CL = d.luma_map.rc * l_pitch + d.luma_map.cc;
-  const int AL = (d.luma_map.r0 - L.r0) * l_pitch + d.luma_map.c0 - (l_first / G) * G;
-  const int BC = d.chroma_map.rr * c_pitch + d.chroma_map.cr * ps, CC = d.chroma_map.rc * c_pitch + d.chroma_map.cc * ps;
-  const int AC = (d.chroma_map.r0 - C.r0) * c_pitch + d.chroma_map.c0 * ps - (c_first / G) * G;
-  auto luma_at = [&](int r, int c) -> uint32_t { return sl[AL + BL * r + CL * c]; };
-  auto chroma_off = [&](int r, int c) -> int {
-    const int r1 = t_map_row(d.pre_map, r, c) >> 1, c1 = t_map_col(d.pre_map, r, c) >> 1;
-    return AC + BC * r1 + CC * c1;
-  };
+  // tile-dependent constants of the two affine address forms
+  const int AL = (d.luma_map.r0 - L.r0) * P.l_pitch + d.luma_map.c0 - (l_first / G) * G;
+  const int AC = (d.chroma_map.r0 - C.r0) * P.c_pitch + d.chroma_map.c0 * ps - (c_first / G) * G;
+  const uint8_t* gl = sl + AL;
+  const uint8_t* gu = su + AC;
+  const uint8_t* gv = sv + AC;
 
-  const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5;  // 8 warps: lanes along the output row
-  for (int cx = lx; cx < P.TC; cx += 32) {
-    const int ox = ox0 + cx;
-    if (ox > ox1) break;
-    const long long x = (long long)d.x0 + (long long)ox * d.dx;
-    const int xi = (int)(x >> 16);
-    const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
-    const uint32_t wp = xf | ((0x7fu ^ xf) << 16);
-    const int cA = min(max(xi, 0), d.vw - 1), cB = min(max(xi + 1, 0), d.vw - 1);
-    for (int ry = ly; ry < P.TR; ry += 8) {
-      const int oy = oy0 + ry;
-      if (oy > oy1) break;
-      long long y = (long long)d.y0 + (long long)oy * d.dy;
-      if (y > d.max_y) y = d.max_y;
-      const int yi = (int)(y >> 16);
-      const uint32_t w1 = d.linear ? 0u : (uint32_t)((y >> 8) & 255), w0 = 256u - w1;
-      const int rA = min(max(yi, 0), d.vh - 1), rB = min(max(yi + 1, 0), d.vh - 1);
-      uint32_t tr, tg, tb, br, bg, bb;
-      {
-        const int oL = chroma_off(rA, cA), oR = chroma_off(rA, cB);
-        const TChroma ct = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
-        t_luma_pair_to_rgb(luma_at(rA, cA), luma_at(rA, cB), ct, tr, tg, tb);
-      }
-      if (w1) {
-        const int oL = chroma_off(rB, cA), oR = chroma_off(rB, cB);
-        const TChroma cb = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
-        t_luma_pair_to_rgb(luma_at(rB, cA), luma_at(rB, cB), cb, br, bg, bb);
-      } else {
-        br = tr; bg = tg; bb = tb;
-      }
-      const uint32_t r = t_vblend2(tr, br, w0, w1) * wp;
-      const uint32_t g = t_vblend2(tg, bg, w0, w1) * wp;
-      const uint32_t b = t_vblend2(tb, bb, w0, w1) * wp;
-      uint8_t* o = f.out + (long long)oy * d.dst_row_stride + (size_t)ox * (3 * sizeof(OT));
+  if (!SWAP) {
+    const int ox = ox0 + lane;  // TC == 32
+    if (ox > ox1) return;
+    const ColTerms Cn = ct[lane];
+    uint8_t* o = f.out + (long long)(oy0 + wid) * d.dst_row_stride + (size_t)ox * (3 * sizeof(OT));
+    for (int ry = wid; oy0 + ry <= oy1; ry += 8, o += 8 * d.dst_row_stride) {
+      const RowTerms R = rt[ry];
+      uint32_t r, g, b;
+      tile_pixel(gl, gu, gv, R, Cn, r, g, b);
       if (sizeof(OT) == 1) {
         o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(g >> 23); o[2] = (uint8_t)(b >> 23);
       } else {
         float* of = reinterpret_cast<float*>(o);
         of[0] = lut[(r >> 23) & 0xFF]; of[1] = lut[(g >> 23) & 0xFF]; of[2] = lut[(b >> 23) & 0xFF];
       }
+    }
+    return;
+  }
+
+  // SWAP: lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3
+  const int oy = oy0 + lane;
+  const int cx0 = wid * 4;
+  if (oy > oy1 || ox0 + cx0 > ox1) return;
+  const RowTerms R = rt[lane];
+  uint32_t px[12];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const ColTerms Cn = ct[min(cx0 + j, 31)];
+    uint32_t r, g, b;
+    tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+    px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
+  }
+  uint8_t* o = f.out + (long long)oy * d.dst_row_stride + (size_t)(ox0 + cx0) * (3 * sizeof(OT));
+  const int n_px = min(4, ox1 - (ox0 + cx0) + 1);
+  if (sizeof(OT) == 1) {
+    if (n_px == 4 && P.out_vec) {
+      uint32_t* o4 = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+      for (int q = 0; q < 3; ++q) o4[q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 12; ++e)
+        if (e < 3 * n_px) o[e] = (uint8_t)px[e];
+    }
+  } else {
+    float* of = reinterpret_cast<float*>(o);
+    if (n_px == 4 && P.out_vec) {
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        reinterpret_cast<float4*>(of)[q] = make_float4(lut[px[4 * q]], lut[px[4 * q + 1]], lut[px[4 * q + 2]], lut[px[4 * q + 3]]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 12; ++e)
+        if (e < 3 * n_px) of[e] = lut[px[e]];
     }
   }
 }
@@ -246,10 +331,16 @@ __global__ void tile_build_lut_kernel(float* lut, float mean, float sd) {
   if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
 }
 
-// Worst-case shared memory of a TR x TC tile: evaluated on the host over every tile (cheap: a few thousand tiles).
-static size_t tile_smem_bytes(const BandCuPlanDesc& d, int TR, int TC, bool interleaved) {
+// Worst-case staged geometry of a TR x TC tiling (evaluated on the host over every tile: a few thousand at most).
+struct TileGeom {
+  int l_pitch, c_pitch, l_rows, c_rows;
+  size_t stage_bytes;  // luma + chroma plane(s)
+};
+template <int G>
+static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool interleaved) {
   const int tiles_x = (d.dst_width + TC - 1) / TC, tiles_y = (d.dst_height + TR - 1) / TR;
-  size_t worst = 0;
+  TileGeom g = {0, 0, 0, 0, 0};
+  const int ps = d.pixel_stride_uv;
   for (int ty = 0; ty < tiles_y; ++ty) {
     for (int tx = 0; tx < tiles_x; ++tx) {
       const int oy0 = ty * TR, ox0 = tx * TC;
@@ -258,15 +349,27 @@ static size_t tile_smem_bytes(const BandCuPlanDesc& d, int TR, int TC, bool inte
       const Rect v = virtual_rect(d, oy0, oy1, ox0, ox1);
       Rect L, C;
       tile_rects(d, v, &L, &C);
-      const int ps = d.pixel_stride_uv;
-      // sized for the 16-byte granule (never smaller than the 4-byte one)
-      const size_t lb = (size_t)(L.r1 - L.r0 + 1) * staged_pitch<16>(L.c0, L.c1);
-      const size_t cb = (size_t)(C.r1 - C.r0 + 1) * staged_pitch<16>(C.c0 * ps, C.c1 * ps + (interleaved ? 1 : 0));
-      const size_t total = lb + (interleaved ? cb : 2 * cb);
-      if (total > worst) worst = total;
+      g.l_pitch = max(g.l_pitch, staged_pitch<G>(L.c0, L.c1));
+      g.c_pitch = max(g.c_pitch, staged_pitch<G>(C.c0 * ps, C.c1 * ps + (interleaved ? 1 : 0)));
+      g.l_rows = max(g.l_rows, L.r1 - L.r0 + 1);
+      g.c_rows = max(g.c_rows, C.r1 - C.r0 + 1);
     }
   }
-  return worst;
+  g.stage_bytes = (size_t)g.l_rows * g.l_pitch + (size_t)(interleaved ? 1 : 2) * g.c_rows * g.c_pitch;
+  g.stage_bytes = (g.stage_bytes + 15) / 16 * 16;
+  return g;
+}
+
+struct TilePlan {
+  float* lut_dev;
+  int TR, TC;
+  TileGeom g16, g4;
+};
+
+static bool is_permutation(const BandCuAffine& m) {
+  const bool straight = m.rr != 0 && m.cc != 0 && m.rc == 0 && m.cr == 0;
+  const bool swapped = m.rr == 0 && m.cc == 0 && m.rc != 0 && m.cr != 0;
+  return straight || swapped;
 }
 
 bool tile_plan_supported(const BandCuPlanDesc& d) {
@@ -276,6 +379,7 @@ bool tile_plan_supported(const BandCuPlanDesc& d) {
   if (d.flavor != BANDCU_FLAVOR_ARGB || d.scale_mode != BANDCU_SCALE_BILINEAR_DOWN) return false;
   if (d.pixel_stride_uv != 1 && d.pixel_stride_uv != 2) return false;
   if (d.normalize ? d.out_dtype != BANDCU_DT_F32 : d.out_dtype != BANDCU_DT_U8) return false;
+  if (!is_permutation(d.luma_map) || !is_permutation(d.pre_map) || !is_permutation(d.chroma_map)) return false;
   // 32-bit word staging: rows must start word aligned and whole words must stay inside the plane rows
   if (d.src_width <= 0 || d.src_width % 4 != 0 || d.stride0 % 4 != 0 || d.stride_uv % 4 != 0) return false;
   if ((((d.src_width + 1) / 2) * d.pixel_stride_uv) % 4 != 0) return false;
@@ -283,19 +387,14 @@ bool tile_plan_supported(const BandCuPlanDesc& d) {
 }
 
 int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
-  // the chroma layout (planar / interleaved) is a property of the pointers, known per batch; size for the larger
   const bool inter = d.pixel_stride_uv == 2;
-  int TR = 32, TC = 32;
-  size_t smem = tile_smem_bytes(d, TR, TC, inter);
-  const size_t cap = 100 * 1024;  // keep >= 2 CTAs per SM
-  while (smem > cap && (TR > 8 || TC > 8)) {
-    if (TR >= TC && TR > 8) TR >>= 1; else if (TC > 8) TC >>= 1; else TR >>= 1;
-    smem = tile_smem_bytes(d, TR, TC, inter);
-  }
-  if (smem > 200 * 1024 || TC < 32) return BANDCU_E_UNSUPPORTED;  // lanes run along the output row: keep TC == 32
+  const int TR = 32, TC = 32;  // lanes run along one tile edge: both stay 32
+  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter), g4 = tile_geometry<4>(d, TR, TC, inter);
+  if (g16.stage_bytes + 2048 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
-  p->TR = TR; p->TC = TC; p->smem = smem;
+  p->TR = TR; p->TC = TC;
+  p->g16 = g16; p->g4 = g4;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
@@ -312,6 +411,13 @@ void tile_plan_destroy(TilePlan* p) {
   if (!p) return;
   if (p->lut_dev) (void)cudaFree(p->lut_dev);
   delete p;
+}
+
+typedef void (*TileKernel)(const TileParams);
+template <typename OT>
+static TileKernel pick_tile_kernel(bool g16, bool swap) {
+  if (g16) return swap ? tile_yuv_bilinear_down_kernel<OT, 16, true> : tile_yuv_bilinear_down_kernel<OT, 16, false>;
+  return swap ? tile_yuv_bilinear_down_kernel<OT, 4, true> : tile_yuv_bilinear_down_kernel<OT, 4, false>;
 }
 
 int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
@@ -356,12 +462,39 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
     }
   }
   if (!aligned4) return BANDCU_E_UNSUPPORTED;
-  void (*kern)(const TileParams);
-  if (aligned16) kern = d.normalize ? tile_yuv_bilinear_down_kernel<float, 16> : tile_yuv_bilinear_down_kernel<uint8_t, 16>;
-  else kern = d.normalize ? tile_yuv_bilinear_down_kernel<float, 4> : tile_yuv_bilinear_down_kernel<uint8_t, 4>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem);
+  const TileGeom& g = aligned16 ? p->g16 : p->g4;
+  P.l_pitch = g.l_pitch; P.c_pitch = g.c_pitch;
+  P.l_rows_max = g.l_rows; P.c_rows_max = g.c_rows;
+  // separable address forms (signed permutations: each mapped coordinate depends on one virtual coordinate)
+  const int ps = d.pixel_stride_uv;
+  P.lr_mul = d.luma_map.rr * g.l_pitch + d.luma_map.cr;
+  P.lc_mul = d.luma_map.rc * g.l_pitch + d.luma_map.cc;
+  const int BC = d.chroma_map.rr * g.c_pitch + d.chroma_map.cr * ps;  // per chroma-index row
+  const int CC = d.chroma_map.rc * g.c_pitch + d.chroma_map.cc * ps;  // per chroma-index column
+  if (d.pre_map.rr != 0) {  // conversion-image row <- virtual row
+    P.cr_0 = d.pre_map.r0; P.cr_s = d.pre_map.rr; P.cr_mul = BC;
+    P.cc_0 = d.pre_map.c0; P.cc_s = d.pre_map.cc; P.cc_mul = CC;
+  } else {                  // conversion-image row <- virtual column
+    P.cr_0 = d.pre_map.c0; P.cr_s = d.pre_map.cr; P.cr_mul = CC;
+    P.cc_0 = d.pre_map.r0; P.cc_s = d.pre_map.rc; P.cc_mul = BC;
+  }
+  const bool swap = d.luma_map.rr == 0;
+  auto shift_for = [](int granules) { int sh = 0; while ((1 << sh) < granules && sh < 5) ++sh; return sh; };
+  const int G = aligned16 ? 16 : 4;
+  P.l_lpr_shift = shift_for(g.l_pitch / G);
+  P.c_lpr_shift = shift_for(g.c_pitch / G);
+  P.off_terms = (int)g.stage_bytes;
+  const size_t smem = g.stage_bytes + 2048;  // + row / column term tables
+  {
+    const int need = d.normalize ? 15 : 3;
+    bool ok;
+    if (batch.table) ok = hints.out_aligned16;
+    else ok = (reinterpret_cast<uintptr_t>(batch.first.out) & need) == 0 && (n == 1 || (batch.out_stride & need) == 0);
+    P.out_vec = (ok && (d.dst_row_stride & need) == 0) ? 1 : 0;
+  }
+  TileKernel kern = d.normalize ? pick_tile_kernel<float>(aligned16, swap) : pick_tile_kernel<uint8_t>(aligned16, swap);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  const int tiles = P.tiles_x * P.tiles_y;
   for (int done = 0; done < n;) {
     const int chunk = n - done > 65535 ? 65535 : n - done;
     TileParams Q = P;
@@ -374,7 +507,7 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
       Q.batch.first.pv += o;
       Q.batch.first.out += (long long)done * Q.batch.out_stride;
     }
-    kern<<<dim3(tiles, chunk, 1), 256, p->smem, stream>>>(Q);
+    kern<<<dim3(P.tiles_x, P.tiles_y, chunk), 256, smem, stream>>>(Q);
     count_launch();
     done += chunk;
   }

@@ -1,0 +1,81 @@
+"""Tile-staged kernel (band_b200/csrc/cuda/bandcu_tile.cu): 4:2:0 -> RGB -> bilinear down [-> Normalize] behind
+Crop / Rotate / Flip index maps, planar and semi-planar chroma, both staging granules (16-byte cp.async and 32-bit
+words), both lane mappings (quarter-turn maps walk output columns), partial edge tiles. Bit-compared with the oracle
+and with the generic pixel-per-thread kernel (BANDCU_DISABLE_TILE=1) on the same inputs."""
+import os
+
+import numpy as np
+import pytest
+
+from gpu_util import assert_same_bits, gpu_chain, oracle_chain, rand_frames
+
+pytestmark = pytest.mark.gpu
+NORM = (5, 0, 0, 0, 0, 127.5, 127.5)
+
+
+def _run_both(O, ops, fr, W, H, fmt, dt, dims, resident):
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, dt, dims)
+    assert st == 0, st
+    st, got = gpu_chain(ops, fr, W, H, fmt, dt, dims, device_resident=resident)
+    assert st == 0
+    assert_same_bits(got, want, "tile kernel vs oracle")
+    os.environ["BANDCU_DISABLE_TILE"] = "1"   # read when the plan is created
+    try:
+        st, gen = gpu_chain(ops, fr, W, H, fmt, dt, dims, device_resident=resident)
+    finally:
+        del os.environ["BANDCU_DISABLE_TILE"]
+    assert st == 0
+    assert_same_bits(gen, want, "generic kernel vs oracle")
+
+
+@pytest.mark.parametrize("fmt_name", ["YV12", "YV21", "NV12", "NV21"])
+@pytest.mark.parametrize("angle", [0, 90, 180, 270])
+@pytest.mark.parametrize("f32", [True, False])
+def test_rotate_csc_resize_every_layout(O, fmt_name, angle, f32):
+    """640x352 (16-byte granule): every 4:2:0 layout x every rotation, output 150x97 (partial edge tiles)."""
+    W, H = 640, 352
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = ([(O.OP_ROTATE, angle)] if angle else []) + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 150, 97)] + ([NORM] if f32 else [])
+    fr = rand_frames(O, 3, W, H, fmt, 1000 + angle)
+    _run_both(O, ops, fr, W, H, fmt, O.DT_F32 if f32 else O.DT_U8, (1, 97, 150, 3), resident=True)
+
+
+@pytest.mark.parametrize("fmt_name,W,H", [("YV12", 648, 360), ("NV21", 324, 180), ("YV21", 328, 250)])
+@pytest.mark.parametrize("angle", [90, 270])
+def test_word_granule_and_odd_crops(O, fmt_name, W, H, angle):
+    """Widths that are multiples of 4/8 but not of 16/32 take the 32-bit staging path; the crop starts on odd
+    luma coordinates, so the chroma sample of a pixel is not the one under it in the source."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    # after a quarter-turn the frame is H wide and W high
+    ops = [(O.OP_ROTATE, angle), (O.OP_CROP, 3, 5, H - 8, W - 12), (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 96, 130), NORM]
+    fr = rand_frames(O, 2, W, H, fmt, 77)
+    _run_both(O, ops, fr, W, H, fmt, O.DT_F32, (1, 130, 96, 3), resident=False)
+
+
+@pytest.mark.parametrize("fmt_name", ["YV12", "NV12"])
+@pytest.mark.parametrize("flip", [(1, 0), (0, 1), (1, 1)])
+def test_flip_crop_csc_resize(O, fmt_name, flip):
+    W, H = 1280, 720
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = [(O.OP_FLIP, flip[0], flip[1]), (O.OP_CROP, 100, 50, 1179, 669), (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 300, 300)]
+    fr = rand_frames(O, 2, W, H, fmt, 31)
+    _run_both(O, ops, fr, W, H, fmt, O.DT_U8, (1, 300, 300, 3), resident=True)
+
+
+def test_planar_1080p_to_224_f32_identity_map(O):
+    """Planar 4:2:0 without any index map (the row-staged kernel only takes semi-planar chroma)."""
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
+    fr = rand_frames(O, 3, 1920, 1080, O.FMT_YV12, 8)
+    _run_both(O, ops, fr, 1920, 1080, O.FMT_YV12, O.DT_F32, (1, 224, 224, 3), resident=True)
+
+
+def test_saturating_frames_through_the_tile_kernel(O):
+    """All-0 / all-255 / extreme-chroma frames exercise every clamp of the packed YuvPixel arithmetic."""
+    W, H = 640, 480
+    fb = O.frame_bytes(W, H, O.FMT_YV12)
+    fr = np.zeros((4, fb), dtype=np.uint8)
+    fr[1] = 255
+    fr[2, :W * H] = 255            # Y = 255, U = V = 0
+    fr[3, W * H:] = 255            # Y = 0,   U = V = 255
+    ops = [(O.OP_ROTATE, 90), (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 100, 120)]
+    _run_both(O, ops, fr, W, H, O.FMT_YV12, O.DT_U8, (1, 120, 100, 3), resident=False)
