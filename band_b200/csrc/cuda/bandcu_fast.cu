@@ -56,6 +56,7 @@ struct FastParams {
   int groups_per_frame;
   long long n_items;
   int use_bulk;        // 1: cp.async.bulk staging, 0: producer-warp byte copies
+  int v_off;           // planar chroma: byte offset of the V row inside a chroma slot (the U row sits at 0)
   int out_row_bytes;   // dw * 3 * sizeof(OT)
   int out_buf_bytes;   // BULKOUT: R * out_row_bytes (one of two output staging buffers)
   int off_out;         // BULKOUT: byte offset of the output staging buffers in shared memory
@@ -131,17 +132,22 @@ constexpr int kOffLut = kOffRowInfo + 4 * kMaxStages * kMaxRows;  // replicated 
 constexpr int kLutBytes = 256 * 4 * 8;  // 256 entries x kLutCopies
 constexpr int kOffStages = ((kOffLut + kLutBytes + 127) / 128) * 128;
 
+// Chroma layout of the source (template parameter CH).
+enum { kChromaUV = 0 /* NV12: U,V interleaved */, kChromaVU = 1 /* NV21 */, kChromaPlanar = 2 /* YV12 / YV21 */ };
+
 // Producer (warp 0): stage the source rows of one work item. Slot layout per output row j:
 //   [4j+0] luma yi   [4j+1] luma yi+1 (only if yf)   [4j+2] chroma ct   [4j+3] chroma cb (only if yf && cb != ct)
 // rowinfo[j] = yf | 0x100 when the bottom luma row has its own chroma row (slot 3).
-template <bool VU>
+// Planar chroma: a chroma slot holds the U row at offset 0 and the V row at offset P.v_off (two copies).
+template <int CH>
 __device__ __forceinline__ void produce_item(const FastParams& P, long long item, uint8_t* stage, uint32_t* rowinfo,
                                              uint64_t* full) {
   const int lane = threadIdx.x;
   const int f = (int)(item / P.groups_per_frame);
   const int g = (int)(item - (long long)f * P.groups_per_frame);
   const FramePtrs fp = frame_ptrs(P.batch, f);
-  const uint8_t* uv = VU ? fp.pv : fp.pu;  // first byte of each interleaved pair
+  const uint8_t* uv = CH == kChromaVU ? fp.pv : fp.pu;  // first byte of each interleaved pair; planar: the U plane
+  const int hb = (P.W + 1) >> 1;                         // planar: bytes per chroma row of one plane
   const int oy0 = g * P.R;
   const int nrows = min(P.R, P.dh - oy0);
   const int ybytes = P.W, cbytes = ((P.W + 1) >> 1) << 1;
@@ -167,8 +173,15 @@ __device__ __forceinline__ void produce_item(const FastParams& P, long long item
       uint8_t* dst = stage + (size_t)k * P.row_pitch;
       if (slot == 0) bulk_g2s(dst, fp.p0 + (long long)s.yi * P.stride0, ybytes, full);
       else if (slot == 1) { if (s.yf) bulk_g2s(dst, fp.p0 + (long long)(s.yi + 1) * P.stride0, ybytes, full); }
-      else if (slot == 2) bulk_g2s(dst, uv + (long long)s.ct * P.stride_uv, cbytes, full);
-      else { if (s.yf && s.cb != s.ct) bulk_g2s(dst, uv + (long long)s.cb * P.stride_uv, cbytes, full); }
+      else if (slot == 2 || (s.yf && s.cb != s.ct)) {
+        const long long off = (long long)(slot == 2 ? s.ct : s.cb) * P.stride_uv;
+        if (CH == kChromaPlanar) {
+          bulk_g2s(dst, fp.pu + off, hb, full);
+          bulk_g2s(dst + P.v_off, fp.pv + off, hb, full);
+        } else {
+          bulk_g2s(dst, uv + off, cbytes, full);
+        }
+      }
     }
   } else {
     // byte-granular staging by the producer warp (any alignment / odd widths)
@@ -182,7 +195,12 @@ __device__ __forceinline__ void produce_item(const FastParams& P, long long item
       else if (slot == 2) { src = uv + (long long)s.ct * P.stride_uv; nb = cbytes; }
       else { if (!s.yf || s.cb == s.ct) continue; src = uv + (long long)s.cb * P.stride_uv; nb = cbytes; }
       uint8_t* dst = stage + (size_t)k * P.row_pitch;
-      for (int i = lane; i < nb; i += 32) dst[i] = src[i];
+      if (CH == kChromaPlanar && slot >= 2) {
+        const uint8_t* srcv = fp.pv + (src - fp.pu);
+        for (int i = lane; i < hb; i += 32) { dst[i] = src[i]; dst[P.v_off + i] = srcv[i]; }
+      } else {
+        for (int i = lane; i < nb; i += 32) dst[i] = src[i];
+      }
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(full);  // release: the warp's stores above are visible to waiters
@@ -227,11 +245,17 @@ struct ChromaPair {
   uint32_t kg;  // 8696 - 25 U - 52 V       (s16 lanes)
   uint32_t kb;  // 128 U                    (u16 lanes)
 };
-template <bool VU>
-__device__ __forceinline__ ChromaPair chroma_pair(uint32_t a_left, uint32_t a_right) {
-  const uint32_t w = __byte_perm(lds_u16(a_left), lds_u16(a_right), 0x5410);
-  const uint32_t u2 = __byte_perm(w, 0u, VU ? 0x4341 : 0x4240);  // U_left | U_right << 16
-  const uint32_t v2 = __byte_perm(w, 0u, VU ? 0x4240 : 0x4341);
+template <int CH>
+__device__ __forceinline__ ChromaPair chroma_pair(uint32_t a_left, uint32_t a_right, uint32_t v_off) {
+  uint32_t u2, v2;  // U_left | U_right << 16, V_left | V_right << 16
+  if (CH == kChromaPlanar) {
+    u2 = lds_u8(a_left) | (lds_u8(a_right) << 16);
+    v2 = lds_u8(a_left + v_off) | (lds_u8(a_right + v_off) << 16);
+  } else {
+    const uint32_t w = __byte_perm(lds_u16(a_left), lds_u16(a_right), 0x5410);
+    u2 = __byte_perm(w, 0u, CH == kChromaVU ? 0x4341 : 0x4240);
+    v2 = __byte_perm(w, 0u, CH == kChromaVU ? 0x4240 : 0x4341);
+  }
   ChromaPair c;
   c.kr = __vadd2(v2 * 102u, 0xC878C878u /* -14216 */);
   const uint32_t t = u2 * 25u + v2 * 52u;  // lanes <= 19635
@@ -269,7 +293,7 @@ constexpr int kLutCopies = 8;  // the Normalize table is replicated so that lane
 // output buffers and leave as cp.async.bulk stores (whole rows, maximum-payload TLPs), which overlap the
 // producer's bulk loads of the next items on the other direction of the link (scripts/pcie_tma_probe.cu:
 // 49 GB/s in + 26 GB/s out at once, against 52 GB/s total when a copy engine drains a staging buffer).
-template <typename OT, bool VU, bool BULKOUT>
+template <typename OT, int CH, bool BULKOUT>
 __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __grid_constant__ FastParams P) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + kOffFull);
@@ -298,7 +322,7 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
     uint32_t wrap = 0;  // how many times the ring has wrapped
     for (long long item = blockIdx.x; item < P.n_items; item += gridDim.x) {
       if (wrap) mbar_wait(&empty[s], (wrap - 1) & 1);  // consumers released the previous use of this stage
-      produce_item<VU>(P, item, stages + (size_t)s * P.stage_bytes, rowinfo + s * kMaxRows, &full[s]);
+      produce_item<CH>(P, item, stages + (size_t)s * P.stage_bytes, rowinfo + s * kMaxRows, &full[s]);
       if (++s == P.S) { s = 0; ++wrap; }
     }
     return;
@@ -339,16 +363,18 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
         const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
         const uint32_t wp = xf | ((0x7fu ^ xf) << 16);
         // byte offsets inside one staged row group: luma pair, left / right chroma pair (slot 2 = top chroma row)
-        const uint32_t cL = 2u * pitch + ((xi >> 1) << 1), cR = 2u * pitch + (((xi + 1u) >> 1) << 1);
+        const uint32_t csh = CH == kChromaPlanar ? 0u : 1u;  // planar rows hold one byte per chroma sample
+        const uint32_t cL = 2u * pitch + ((xi >> 1) << csh), cR = 2u * pitch + (((xi + 1u) >> 1) << csh);
+        const uint32_t v_off = (uint32_t)P.v_off;
         uint32_t row = stage;                                   // slot 0 of output row j
         uint8_t* o = gout + (size_t)ox * (3 * sizeof(OT));      // output pixel of row j
 #pragma unroll 2
         for (int j = 0; j < nrows; ++j, row += 4u * pitch, o += orow_stride) {
           const uint32_t info = lds_u32(ri + 4u * (uint32_t)j);
           const uint32_t w1 = info & 0xFFu, w0 = 256u - w1;
-          const ChromaPair ctop = chroma_pair<VU>(row + cL, row + cR);
+          const ChromaPair ctop = chroma_pair<CH>(row + cL, row + cR, v_off);
           ChromaPair cbot = ctop;
-          if (info & 0x100u) cbot = chroma_pair<VU>(row + cL + pitch, row + cR + pitch);  // slot 3: warp-uniform
+          if (info & 0x100u) cbot = chroma_pair<CH>(row + cL + pitch, row + cR + pitch, v_off);  // slot 3: warp-uniform
           uint32_t tr, tg, tb, br, bg, bb;
           luma_pair_to_rgb(row + xi, ctop, tr, tg, tb);
           luma_pair_to_rgb(row + xi + pitch, cbot, br, bg, bb);
@@ -409,7 +435,7 @@ static int env_int(const char* name, int lo, int hi, int dflt) {
 bool fast_plan_supported(const BandCuPlanDesc& d) {
   const char* off = getenv("BANDCU_DISABLE_FAST");
   if (off && off[0] == '1') return false;
-  if (d.src_kind != BANDCU_SRC_YUV420 || d.pixel_stride_uv != 2) return false;
+  if (d.src_kind != BANDCU_SRC_YUV420 || (d.pixel_stride_uv != 2 && d.pixel_stride_uv != 1)) return false;
   if (d.cvt != BANDCU_CVT_YUV2RGB || d.channels != 3) return false;
   if (d.flavor != BANDCU_FLAVOR_ARGB || d.scale_mode != BANDCU_SCALE_BILINEAR_DOWN) return false;
   if (!is_identity(d.luma_map) || !is_identity(d.pre_map) || !is_identity(d.chroma_map)) return false;
@@ -449,9 +475,15 @@ void fast_plan_destroy(FastPlan* p) {
 
 typedef void (*FastKernel)(const FastParams);
 template <typename OT>
-static FastKernel pick_kernel(bool vu, bool bulk_out) {
-  if (bulk_out) return vu ? fast_nv_bilinear_down_kernel<OT, true, true> : fast_nv_bilinear_down_kernel<OT, false, true>;
-  return vu ? fast_nv_bilinear_down_kernel<OT, true, false> : fast_nv_bilinear_down_kernel<OT, false, false>;
+static FastKernel pick_kernel(int ch, bool bulk_out) {
+  if (bulk_out) {
+    return ch == kChromaPlanar ? fast_nv_bilinear_down_kernel<OT, kChromaPlanar, true>
+           : ch == kChromaVU   ? fast_nv_bilinear_down_kernel<OT, kChromaVU, true>
+                               : fast_nv_bilinear_down_kernel<OT, kChromaUV, true>;
+  }
+  return ch == kChromaPlanar ? fast_nv_bilinear_down_kernel<OT, kChromaPlanar, false>
+         : ch == kChromaVU   ? fast_nv_bilinear_down_kernel<OT, kChromaVU, false>
+                             : fast_nv_bilinear_down_kernel<OT, kChromaUV, false>;
 }
 
 void fast_plan_set_bulk_store(FastPlan* p, int on) {
@@ -460,17 +492,21 @@ void fast_plan_set_bulk_store(FastPlan* p, int on) {
 
 int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
                 cudaStream_t stream) {
-  bool vu;
-  if (batch.table) {
+  int ch;
+  if (d.pixel_stride_uv == 1) {
+    ch = kChromaPlanar;
+    if (batch.table ? !hints.valid : (!batch.first.pu || !batch.first.pv)) return BANDCU_E_UNSUPPORTED;
+  } else if (batch.table) {
     if (!hints.valid || !hints.semi_planar) return BANDCU_E_UNSUPPORTED;
-    vu = hints.vu;
+    ch = hints.vu ? kChromaVU : kChromaUV;
   } else {
     const uint8_t* pu = batch.first.pu;
     const uint8_t* pv = batch.first.pv;
-    if (pv == pu + 1) vu = false;       // NV12: U first
-    else if (pu == pv + 1) vu = true;   // NV21: V first
+    if (pv == pu + 1) ch = kChromaUV;        // NV12: U first
+    else if (pu == pv + 1) ch = kChromaVU;   // NV21: V first
     else return BANDCU_E_UNSUPPORTED;
   }
+  const bool vu = ch == kChromaVU;
   FastParams P;
   memset(&P, 0, sizeof(P));
   P.W = d.vw; P.H = d.vh;
@@ -480,6 +516,7 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.dst_row_stride = d.dst_row_stride;
   const int cbytes = ((d.vw + 1) >> 1) << 1;
   P.row_pitch = ((cbytes + 15) / 16) * 16 + 16;  // +16: xi+1 may touch one byte past the row when xf == 0
+  P.v_off = ((((d.vw + 1) >> 1) + 15) / 16) * 16;
   // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
   P.R = p->R; P.S = p->S;
   P.passes = (d.dst_width + 511) / 512;
@@ -510,7 +547,12 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.lut = p->lut_dev;
   P.batch = batch;
   bool aligned = (d.vw % 16 == 0) && (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0);
-  if (batch.table) {
+  if (ch == kChromaPlanar) {
+    aligned = aligned && (d.vw % 32 == 0);  // each plane's chroma row is its own 16-byte granular copy
+    if (batch.table) aligned = aligned && hints.planes_aligned16;
+    else aligned = aligned && ((reinterpret_cast<uintptr_t>(batch.first.p0) | reinterpret_cast<uintptr_t>(batch.first.pu) |
+                                reinterpret_cast<uintptr_t>(batch.first.pv)) & 15) == 0 && (n == 1 || batch.in_stride % 16 == 0);
+  } else if (batch.table) {
     aligned = aligned && hints.aligned16;
   } else {
     const uint8_t* uv0 = vu ? batch.first.pv : batch.first.pu;
@@ -521,7 +563,7 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   const char* nb = getenv("BANDCU_FAST_NO_BULK");
   if (nb && nb[0] == '1') P.use_bulk = 0;
   // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
-  FastKernel kern = d.normalize ? pick_kernel<float>(vu, bulk_out) : pick_kernel<uint8_t>(vu, bulk_out);
+  FastKernel kern = d.normalize ? pick_kernel<float>(ch, bulk_out) : pick_kernel<uint8_t>(ch, bulk_out);
   int per_sm = 1;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);

@@ -230,7 +230,7 @@ def c5_cases(steps, cpu, pairs=None):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="c1,c2,c3,c4,c5")
+    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--cpu", action="store_true")
     ap.add_argument("--device", type=int, default=0)
@@ -263,6 +263,13 @@ def main():
                     "frames_per_s": tot_frames / (tot_ms * 1e-3), "ms_per_step": tot_ms, "frames_per_step": tot_frames,
                     "achieved_GBps": tot_bytes / (tot_ms * 1e-3) / 1e9,
                     "frac_of_measured_hbm": tot_bytes / (tot_ms * 1e-3) / 1e9 / peak()})
+    if "x" in want:  # beyond BASELINE: planar 1080p, and the portrait-camera case (NV21 sensor frame + Rotate 90)
+        from oracle import oracle as O
+        out.append(tensor_case("x_1080p_yv12_to_224_f32", 1920, 1080, "YV12", 224, 224, True, 1024, a.steps, a.cpu))
+        out.append(tensor_case("x_1080p_nv21_rot90_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
+                               pre_ops=[(B.BAND_ROTATE, 90)], pre_ops_o=[(O.OP_ROTATE, 90)]))
+        out.append(tensor_case("x_1080p_yv12_rot270_to_300_u8", 1920, 1080, "YV12", 300, 300, False, 1024, a.steps, a.cpu,
+                               pre_ops=[(B.BAND_ROTATE, 270)], pre_ops_o=[(O.OP_ROTATE, 270)]))
     if "c5" in want:
         pairs = [tuple(int(v) for v in p.split(":")) for p in a.c5_pairs.split(",") if p] or None
         out += c5_cases(a.steps, a.cpu, pairs)

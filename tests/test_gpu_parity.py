@@ -205,7 +205,8 @@ def test_reference_resize_hippo(O, hippo):
 
 
 @pytest.mark.parametrize("fmt_name,W,H,d,f32", [("NV12", 1920, 1080, 224, True), ("NV21", 1920, 1080, 300, False),
-                                                ("NV21", 640, 480, 224, True)])
+                                                ("NV21", 640, 480, 224, True), ("YV12", 1920, 1080, 224, True),
+                                                ("YV21", 1280, 720, 300, False), ("YV12", 648, 360, 200, True)])
 def test_pinned_host_frames_zero_copy(O, fmt_name, W, H, d, f32):
     """Frames in PINNED host memory (BandHostAlloc): the staged kernel pulls the rows it samples straight over
     PCIe (no staging copy). Same bits as the oracle."""

@@ -79,3 +79,29 @@ def test_saturating_frames_through_the_tile_kernel(O):
     fr[3, W * H:] = 255            # Y = 0,   U = V = 255
     ops = [(O.OP_ROTATE, 90), (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 100, 120)]
     _run_both(O, ops, fr, W, H, O.FMT_YV12, O.DT_U8, (1, 120, 100, 3), resident=False)
+
+
+@pytest.mark.parametrize("fmt_name,W,H,dw,dh,f32", [
+    ("YV12", 1920, 1080, 300, 300, False),   # planar chroma through the ROW-staged kernel (two bulk copies per chroma row)
+    ("YV21", 1280, 720, 513, 400, True),
+    ("YV12", 648, 360, 111, 97, True),       # 324-byte chroma rows: not 16-byte granular -> producer-warp byte staging
+    ("YV21", 642, 362, 100, 90, False),      # width not a multiple of 4: neither staged kernel's bulk path applies
+])
+def test_planar_identity_map_row_staged(O, fmt_name, W, H, dw, dh, f32):
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh)] + ([NORM] if f32 else [])
+    fr = rand_frames(O, 5, W, H, fmt, 4321)
+    dt = O.DT_F32 if f32 else O.DT_U8
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, dt, (1, dh, dw, 3))
+    assert st == 0
+    for resident in (True, False):
+        st, got = gpu_chain(ops, fr, W, H, fmt, dt, (1, dh, dw, 3), device_resident=resident)
+        assert st == 0
+        assert_same_bits(got, want, "planar %s resident=%s" % (fmt_name, resident))
+    os.environ["BANDCU_DISABLE_FAST"] = "1"
+    try:
+        st, got = gpu_chain(ops, fr, W, H, fmt, dt, (1, dh, dw, 3), device_resident=True)
+    finally:
+        del os.environ["BANDCU_DISABLE_FAST"]
+    assert st == 0
+    assert_same_bits(got, want, "planar %s without the row-staged kernel" % fmt_name)
