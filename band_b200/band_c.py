@@ -19,7 +19,7 @@ kBandOk, kBandErr = 0, 1
  kBandInt8, kBandFloat16, kBandFloat64) = range(12)
 (kBandGrayScale, kBandRGB, kBandRGBA, kBandYV12, kBandYV21, kBandNV21, kBandNV12, kBandRaw) = range(8)
 (BAND_CROP, BAND_RESIZE, BAND_ROTATE, BAND_FLIP, BAND_COLOR_SPACE_CONVERT, BAND_NORMALIZE,
- BAND_DATA_TYPE_CONVERT) = range(7)
+ BAND_DATA_TYPE_CONVERT, BAND_AUTO_ORIENT) = range(8)
 kBandHostMemory, kBandDeviceMemory = 0, 1
 
 FORMATS = {"GRAY": kBandGrayScale, "RGB": kBandRGB, "RGBA": kBandRGBA, "YV12": kBandYV12, "YV21": kBandYV21,
@@ -42,7 +42,7 @@ EXPORTED = [
     "BandDeviceFree", "BandCopyToDevice", "BandCopyToHost", "BandCudaLaunchCount", "BandGetLastError",
     "BandTensorRingBufferCreate", "BandTensorRingBufferDelete", "BandTensorRingBufferAlloc",
     "BandTensorRingBufferIsHandleValid", "BandTensorRingBufferGetSlot", "BandTensorRingBufferPutTensor",
-    "BandTensorRingBufferGetTensor",
+    "BandTensorRingBufferGetTensor", "BandBufferSetOrientation",
 ]
 
 
@@ -110,6 +110,7 @@ def lib():
     L.BandCopyToHost.argtypes = [vp, vp, sz]
     L.BandCudaLaunchCount.restype = C.c_longlong
     L.BandGetLastError.restype = C.c_char_p
+    L.BandBufferSetOrientation.argtypes = [vp, ci]
     L.BandTensorRingBufferCreate.argtypes = [C.POINTER(vp), C.POINTER(ci), sz, ci, ci]
     L.BandTensorRingBufferCreate.restype = vp
     L.BandTensorRingBufferDelete.argtypes = [vp]
@@ -262,6 +263,11 @@ class Buffer:
         if f(self.handle, y, u, v, width, height, row_stride_y, row_stride_uv, pixel_stride_uv, fmt) != kBandOk:
             raise BandError("BandBufferSetFromYUVData failed")
         self.keep = keep
+        return self
+
+    def set_orientation(self, exif):
+        if lib().BandBufferSetOrientation(self.handle, int(exif)) != kBandOk:
+            raise BandError("BandBufferSetOrientation failed")
         return self
 
     @staticmethod

@@ -66,6 +66,8 @@ class Buffer {
   DataType GetDataType() const;
   BufferFormat GetBufferFormat() const;
   BufferOrientation GetOrientation() const;
+  // additive: the camera layer knows the sensor orientation only after the view exists (BandBufferSetOrientation)
+  void SetOrientation(BufferOrientation orientation) { orientation_ = orientation; }
   MemorySpace GetMemorySpace() const { return space_; }  // additive
 
   absl::Status CopyFrom(const Buffer& rhs);

@@ -118,6 +118,7 @@ ImageLayout ImageLayout::Of(const Buffer& b) {
     l.width = static_cast<int>(b.GetDimension()[0]);
     l.height = static_cast<int>(b.GetDimension()[1]);
   }
+  l.orientation = static_cast<int>(b.GetOrientation());
   l.num_planes = static_cast<int>(std::min<size_t>(b.GetNumPlanes(), 3));
   for (int k = 0; k < l.num_planes; ++k) {
     l.row_stride[k] = b[k].row_stride_bytes;
@@ -127,7 +128,8 @@ ImageLayout ImageLayout::Of(const Buffer& b) {
 }
 
 bool ImageLayout::operator==(const ImageLayout& o) const {
-  if (format != o.format || dtype != o.dtype || width != o.width || height != o.height || num_planes != o.num_planes)
+  if (format != o.format || dtype != o.dtype || width != o.width || height != o.height || num_planes != o.num_planes ||
+      orientation != o.orientation)
     return false;
   for (int k = 0; k < num_planes; ++k)
     if (row_stride[k] != o.row_stride[k] || pixel_stride[k] != o.pixel_stride[k]) return false;

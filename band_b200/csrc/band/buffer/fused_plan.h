@@ -37,6 +37,7 @@ struct ImageLayout {
   size_t row_stride[3] = {0, 0, 0};
   size_t pixel_stride[3] = {0, 0, 0};
   int num_planes = 0;
+  int orientation = 1;  // BufferOrientation: AutoOrient lowers differently per value, so it keys the plan
   static ImageLayout Of(const Buffer& b);
   bool operator==(const ImageLayout& o) const;
 };

@@ -30,6 +30,7 @@ IBufferOperator::Type Crop::GetOpType() const { return Type::kImage; }
 IBufferOperator::Type Resize::GetOpType() const { return Type::kImage; }
 IBufferOperator::Type Rotate::GetOpType() const { return Type::kImage; }
 IBufferOperator::Type Flip::GetOpType() const { return Type::kImage; }
+IBufferOperator::Type AutoOrient::GetOpType() const { return Type::kImage; }
 IBufferOperator::Type ColorSpaceConvert::GetOpType() const { return Type::kImage; }
 // image_operator.cc:72: value-initialised Type, i.e. kImage
 IBufferOperator::Type AutoConvert::GetOpType() const { return Type(); }
@@ -38,6 +39,7 @@ IBufferOperator* Crop::Clone() const { return new Crop(*this); }
 IBufferOperator* Resize::Clone() const { return new Resize(*this); }
 IBufferOperator* Rotate::Clone() const { return new Rotate(*this); }
 IBufferOperator* Flip::Clone() const { return new Flip(*this); }
+IBufferOperator* AutoOrient::Clone() const { return new AutoOrient(*this); }
 IBufferOperator* ColorSpaceConvert::Clone() const { return new ColorSpaceConvert(*this); }
 IBufferOperator* AutoConvert::Clone() const { return new AutoConvert(*this); }
 
@@ -217,6 +219,66 @@ absl::Status Flip::Lower(cuda::ChainLowering& lowering, const Buffer& input) con
   if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
     return absl::InvalidArgumentError("Flip: input and output buffer formats must match");
   return lowering.Flip(horizontal_, vertical_);
+}
+
+// ---- AutoOrient (additive; applies band/common.h:146-161 BufferOrientation) ----
+void AutoOrient::Decompose(BufferOrientation orientation, bool* mirror, int* angle_deg) {
+  // Rotate() is counter-clockwise (libyuv_image_operator.cc:697-708). Derivations: transpose out[r][c] = in[c][r] is a
+  // horizontal mirror followed by Rotate(90); transverse out[r][c] = in[H-1-c][W-1-r] a mirror followed by Rotate(270).
+  switch (orientation) {
+    case BufferOrientation::kTopRight: *mirror = true; *angle_deg = 0; break;
+    case BufferOrientation::kBottomRight: *mirror = false; *angle_deg = 180; break;
+    case BufferOrientation::kBottomLeft: *mirror = true; *angle_deg = 180; break;   // == vertical mirror
+    case BufferOrientation::kLeftTop: *mirror = true; *angle_deg = 90; break;       // transpose
+    case BufferOrientation::kRightTop: *mirror = false; *angle_deg = 270; break;    // quarter-turn clockwise
+    case BufferOrientation::kRightBottom: *mirror = true; *angle_deg = 270; break;  // transverse
+    case BufferOrientation::kLeftBottom: *mirror = false; *angle_deg = 90; break;   // quarter-turn counter-clockwise
+    default: *mirror = false; *angle_deg = 0; break;
+  }
+}
+
+absl::Status AutoOrient::ValidateInput(const Buffer& input) const {
+  if (IsRaw(input)) return RawNotSupported("AutoOrient");
+  const size_t o = static_cast<size_t>(input.GetOrientation());
+  if (o < 1 || o > 8) return absl::InvalidArgumentError(absl::StrFormat("AutoOrient: invalid orientation %d", static_cast<int>(o)));
+  return absl::OkStatus();
+}
+
+absl::Status AutoOrient::ValidateOutput(const Buffer& input) const {
+  if (!input.IsBufferFormatCompatible(*output_))
+    return absl::InvalidArgumentError("AutoOrient: output buffer format type is not compatible.");
+  bool mirror;
+  int angle;
+  Decompose(input.GetOrientation(), &mirror, &angle);
+  const std::vector<size_t>& in = input.GetDimension();
+  const std::vector<size_t>& out = output_->GetDimension();
+  const bool fits = QuarterTurn(angle) ? (in[0] == out[1] && in[1] == out[0]) : (in == out);
+  if (!fits) return absl::InvalidArgumentError("AutoOrient: output buffer has invalid dimensions.");
+  return absl::OkStatus();
+}
+
+absl::Status AutoOrient::CreateOutput(const Buffer& input) {
+  bool mirror;
+  int angle;
+  Decompose(input.GetOrientation(), &mirror, &angle);
+  const bool turn = QuarterTurn(angle);
+  const size_t w = input.GetDimension()[turn ? 1 : 0], h = input.GetDimension()[turn ? 0 : 1];
+  Buffer* created = Buffer::CreateEmpty(w, h, input.GetBufferFormat(), input.GetDataType(), BufferOrientation::kTopLeft,
+                                        OutputSpace());
+  if (created == nullptr) return absl::InternalError("AutoOrient: failed to create the output buffer");
+  OwnOutput(created);
+  return absl::OkStatus();
+}
+
+absl::Status AutoOrient::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
+  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+    return absl::InvalidArgumentError("AutoOrient: input and output buffer formats must match");
+  bool mirror;
+  int angle;
+  Decompose(input.GetOrientation(), &mirror, &angle);
+  if (mirror) RETURN_IF_ERROR(lowering.Flip(true, false));
+  if (angle != 0) RETURN_IF_ERROR(lowering.Rotate(angle));
+  return absl::OkStatus();
 }
 
 // ---- ColorSpaceConvert (image_operator.cc:359-419) ---------------------------

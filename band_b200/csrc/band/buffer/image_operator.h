@@ -88,6 +88,26 @@ class Flip : public IBufferOperator {
   bool horizontal_, vertical_;
 };
 
+// ADDITIVE. The reference carries Buffer::GetOrientation() (EXIF 1..8, band/common.h:146-161) from the
+// camera to the processor and never applies it. AutoOrient turns the frame upright: the orientation becomes the
+// equivalent Flip / Rotate pair (2: mirror, 3: 180, 4: vertical mirror, 5: transpose, 6: quarter-turn clockwise,
+// 7: transverse, 8: quarter-turn counter-clockwise), which the plan compiler folds into the same index map as any
+// other Crop / Rotate / Flip -- no extra pass. Output: same format, dimensions swapped for 5..8, kTopLeft.
+class AutoOrient : public IBufferOperator {
+ public:
+  AutoOrient() = default;
+  Type GetOpType() const override;
+  absl::Status ValidateInput(const Buffer& input) const override;
+  absl::Status ValidateOutput(const Buffer& input) const override;
+  absl::Status CreateOutput(const Buffer& input) override;
+  // orientation -> (mirror horizontally first, then rotate counter-clockwise by angle)
+  static void Decompose(BufferOrientation orientation, bool* mirror, int* angle_deg);
+
+ protected:
+  absl::Status Lower(cuda::ChainLowering& lowering, const Buffer& input) const override;
+  IBufferOperator* Clone() const override;
+};
+
 class ColorSpaceConvert : public IBufferOperator {
  public:
   ColorSpaceConvert() : output_format_(BufferFormat::kRaw), is_format_specified_(false) {}

@@ -111,8 +111,8 @@ BandStatus BandAddOperator(BandImageProcessorBuilder* builder, BandImageProcesso
     BAND_LOG(LogSeverity::kError, "BandImageProcessorBuilder is null");
     return kBandErr;
   }
-  static const int kArity[] = {4, 2, 1, 2, 1, 2, 0};
-  if (field < BAND_CROP || field > BAND_DATA_TYPE_CONVERT || count != kArity[field]) return kBandErr;
+  static const int kArity[] = {4, 2, 1, 2, 1, 2, 0, 0};
+  if (field < BAND_CROP || field > BAND_AUTO_ORIENT || count != kArity[field]) return kBandErr;
   va_list vl;
   va_start(vl, count);
   std::unique_ptr<band::IBufferOperator> op;
@@ -146,9 +146,25 @@ BandStatus BandAddOperator(BandImageProcessorBuilder* builder, BandImageProcesso
     case BAND_DATA_TYPE_CONVERT:
       op = std::make_unique<band::buffer::DataTypeConvert>();
       break;
+    case BAND_AUTO_ORIENT:
+      op = std::make_unique<band::buffer::AutoOrient>();
+      break;
   }
   va_end(vl);
   builder->impl->AddOperation(std::move(op));
+  return kBandOk;
+}
+
+BandStatus BandBufferSetOrientation(BandBuffer* buffer, int exif_orientation) {
+  if (!buffer || !buffer->impl) {
+    BAND_LOG(LogSeverity::kError, "BandBufferSetOrientation: buffer is null or has no data");
+    return kBandErr;
+  }
+  if (exif_orientation < 1 || exif_orientation > 8) {
+    BAND_LOG(LogSeverity::kError, "BandBufferSetOrientation: orientation %d is not in 1..8", exif_orientation);
+    return kBandErr;
+  }
+  buffer->impl->SetOrientation(static_cast<band::BufferOrientation>(exif_orientation));
   return kBandOk;
 }
 

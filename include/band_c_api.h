@@ -83,7 +83,8 @@ typedef enum BandImageProcessorBuilderField {
   BAND_FLIP,                /* 2 int (bool): horizontal, vertical */
   BAND_COLOR_SPACE_CONVERT, /* 1 int: BandBufferFormat */
   BAND_NORMALIZE,           /* 2 double: mean, std */
-  BAND_DATA_TYPE_CONVERT    /* 0 */
+  BAND_DATA_TYPE_CONVERT,   /* 0 */
+  BAND_AUTO_ORIENT          /* 0; ADDITIVE: apply the buffer's EXIF orientation (BandBufferSetOrientation) */
 } BandImageProcessorBuilderField;
 
 /* ---- handles ---------------------------------------------------------------- */
@@ -141,6 +142,9 @@ BAND_CAPI_EXPORT extern BandStatus BandBufferSetFromDeviceYUVData(BandBuffer* bu
                                                                   size_t width, size_t height, size_t row_stride_y,
                                                                   size_t row_stride_uv, size_t pixel_stride_uv,
                                                                   BandBufferFormat buffer_format);
+/* EXIF orientation 1..8 of the frame (band::BufferOrientation, band/common.h:146-161; default 1 = upright). The
+ * reference carries it and never applies it; here the BAND_AUTO_ORIENT operator does. Call after SetFrom*. */
+BAND_CAPI_EXPORT extern BandStatus BandBufferSetOrientation(BandBuffer* buffer, int exif_orientation);
 /* n independent frames of one layout -> n tensors of one shape, as fused batch launches. */
 BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatch(BandImageProcessor* image_processor,
                                                                   BandBuffer* const* buffers,
