@@ -103,8 +103,11 @@ __host__ __device__ __forceinline__ int staged_pitch(int first_byte, int last_by
 // loop has no division: (source, destination) advance by a fixed number of rows per pass.
 template <int G>
 __device__ __forceinline__ void stage_plane(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride,
-                                            int row0, int nrows, int first_byte, int pitch, int lpr_shift) {
-  const int gpr = pitch / G;                       // granules per staged row
+                                            int row0, int nrows, int first_byte, int pitch, int lpr_shift,
+                                            int row_bytes) {
+  // granules per staged row: the launch-wide pitch, but never past the end of the plane row (the pitch is the worst
+  // case over all tiles and odd; a tile at the right edge must not read into memory behind the last row)
+  const int gpr = min(pitch / G, (row_bytes - (first_byte / G) * G + G - 1) / G);
   const int lpr = 1 << lpr_shift;
   const int rows_per_pass = (int)blockDim.x >> lpr_shift;
   int r = (int)threadIdx.x >> lpr_shift;
@@ -238,18 +241,19 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   const int ps = d.pixel_stride_uv;
   const int l_first = L.c0, c_first = C.c0 * ps;
   const int l_rows = L.r1 - L.r0 + 1, c_rows = C.r1 - C.r0 + 1;
+  const int c_row_bytes = ((d.src_width + 1) >> 1) * ps;  // bytes of one chroma plane row
   uint8_t* sl = smem;
   uint8_t* su = sl + P.l_rows_max * P.l_pitch;
   uint8_t* sv;
-  stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift);
+  stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
   if (P.interleaved) {
-    stage_plane<G>(su, P.v_first ? f.pv : f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
+    stage_plane<G>(su, P.v_first ? f.pv : f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
     sv = su + (P.v_first ? 0 : 1);
     su = su + (P.v_first ? 1 : 0);
   } else {
     sv = su + P.c_rows_max * P.c_pitch;
-    stage_plane<G>(su, f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
-    stage_plane<G>(sv, f.pv, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift);
+    stage_plane<G>(su, f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
+    stage_plane<G>(sv, f.pv, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
   }
   if (G == 16) asm volatile("cp.async.commit_group;" ::: "memory");
 

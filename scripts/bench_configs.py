@@ -243,6 +243,7 @@ def main():
         out.append(tensor_case("north_star_1080p_nv12_to_224_f32", 1920, 1080, "NV12", 224, 224, True, 1024, a.steps, a.cpu))
     if "c1" in want:
         out += c1_latency(a.steps)
+    if "c1" in want or "c1b" in want:
         out.append(tensor_case("c1_batch_640x480_nv21_to_224_f32", 640, 480, "NV21", 224, 224, True, 4096, a.steps, a.cpu))
     if "c2" in want:
         out.append(tensor_case("c2_1080p_nv12_to_300_u8", 1920, 1080, "NV12", 300, 300, False, 1024, a.steps, a.cpu))
