@@ -295,7 +295,8 @@ __device__ __forceinline__ void luma_pair_to_rgb(uint32_t a, const ChromaPair& c
 }
 // InterpolateRow_C on both lanes: (top*(256-f) + bottom*f + 128) >> 8; f == 0 keeps top whatever bottom holds.
 __device__ __forceinline__ uint32_t vblend2(uint32_t top, uint32_t bot, uint32_t w0, uint32_t w1) {
-  return ((top * w0 + bot * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
+  // bytes 1 and 3 of the sums are the two results: one PRMT instead of shift + mask
+  return __byte_perm(top * w0 + bot * w1 + 0x00800080u, 0u, 0x4341);
 }
 // ScaleARGBFilterCols_C on a packed pair: (L*(0x7f^xf) + R*xf) >> 7, truncating. wp = xf | (0x7f^xf) << 16, so
 // (L | R<<16) * wp = L*xf + (L*(0x7f^xf) + R*xf) << 16 (+ a term beyond bit 31); L*xf < 65536 never carries.

@@ -154,7 +154,8 @@ __device__ __forceinline__ void t_luma_pair_to_rgb(uint32_t yL, uint32_t yR, con
   B2 = (b >> 6) & 0x00FF00FFu;
 }
 __device__ __forceinline__ uint32_t t_vblend2(uint32_t top, uint32_t bot, uint32_t w0, uint32_t w1) {
-  return ((top * w0 + bot * w1 + 0x00800080u) >> 8) & 0x00FF00FFu;
+  // bytes 1 and 3 of the sums are the two results: one PRMT instead of shift + mask
+  return __byte_perm(top * w0 + bot * w1 + 0x00800080u, 0u, 0x4341);
 }
 
 struct __align__(16) RowTerms {   // everything an output ROW contributes (32 bytes)

@@ -151,6 +151,53 @@ def dist_setup(n_gpus):
     return rank, local, world, shard.init_dist("nccl")
 
 
+_ALL_CPUS = None
+
+
+def unbind():
+    """Back to every host CPU (the CPU baseline uses all of them)."""
+    if _ALL_CPUS:
+        os.sched_setaffinity(0, _ALL_CPUS)
+
+
+def bind_near_gpu(local):
+    """Pin this rank's threads to the CPUs of its GPU's NUMA node before any pinned allocation, so the frames and
+    tensors of the e2e path sit in the memory closest to the GPU's PCIe root (one host thread per GPU).
+    Returns a short description for the JSON line; never fatal."""
+    if os.environ.get("BENCH_NO_AFFINITY") == "1":
+        return "off"
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local).pci_bus_id if hasattr(torch.cuda.get_device_properties(local), "pci_bus_id") else None
+        if bus is None:
+            import pynvml
+            pynvml.nvmlInit()
+            bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local)).busId
+            if isinstance(bus, bytes):
+                bus = bus.decode()
+        bus = str(bus).lower()
+        if len(bus.split(":")[0]) == 8:   # nvml prints an 8-digit domain, sysfs uses 4
+            bus = bus[4:]
+        base = "/sys/bus/pci/devices/" + bus
+        node = int(open(base + "/numa_node").read().strip())
+        cpus = open(base + "/local_cpulist").read().strip()
+        ids = set()
+        for part in cpus.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                ids.update(range(int(a), int(b) + 1))
+            elif part:
+                ids.add(int(part))
+        global _ALL_CPUS
+        _ALL_CPUS = os.sched_getaffinity(0)
+        ids &= _ALL_CPUS
+        if ids:
+            os.sched_setaffinity(0, ids)
+        return "numa_node %d, %d cpus" % (node, len(ids))
+    except Exception as e:  # noqa: BLE001
+        return "unavailable (%s)" % type(e).__name__
+
+
 def barrier_max(dist, local, value_ms):
     """max over ranks of a device-measured duration (no data-path collective: timing only)."""
     from band_b200 import shard
@@ -176,6 +223,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback")
     torch.cuda.set_device(local)
+    affinity = bind_near_gpu(local)
     hotpath.set_device(local)
     L, SL = B.lib(), S.lib()
     ops = hotpath.chain_ops(DW, DH, True, MEAN, STD)
@@ -291,7 +339,7 @@ def run_ours(args):
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": E * FRAME_BYTES * world,
                 "d2h_bytes_per_step": E * OUT_BYTES * world, "frames_per_step_per_gpu": E, "steps": args.e2e_steps,
                 "timing": "host clock around synchronous BandImageProcessorProcessBatch calls (pinned host buffers and tensors), max over ranks",
-                "gpu_launches": e2e_launches,
+                "gpu_launches": e2e_launches, "host_affinity": affinity,
                 "note": "h2d/d2h_bytes_per_step count the full frames and tensors handed to the call; the fused kernel reads the "
                         "pinned frames in place over PCIe (only the source rows the resize samples cross the bus) and pushes "
                         "the tensors into pinned host memory with cp.async.bulk stores -- no staging copy either way"},
@@ -303,6 +351,7 @@ def run_ours(args):
                      "kernel_ms": kernel_ms, "bytes_per_launch_algorithmic": ALG_BYTES * F},
         "clocks": clocks, "parity": parity,
     }
+    unbind()
     if rank == 0 and world == 1 and not args.no_cpu:
         th = host_threads()
         fps1, _ = cpu_frames_per_s(4, th)                     # short probe to size the sample
