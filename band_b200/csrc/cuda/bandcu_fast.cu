@@ -537,6 +537,8 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.v_off = ((((d.vw + 1) >> 1) + 15) / 16) * 16;
   // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
   P.R = p->R; P.S = p->S;
+  // small batches (the single-frame latency case): fewer rows per item so that every SM gets work
+  while (P.R > 1 && (long long)n * ((d.dst_height + P.R - 1) / P.R) < 2LL * p->num_sms) P.R >>= 1;
   P.passes = (d.dst_width + 511) / 512;
   P.cols = (((d.dst_width + P.passes - 1) / P.passes) + 31) / 32 * 32;
   const int esize = d.normalize ? 4 : 1;
