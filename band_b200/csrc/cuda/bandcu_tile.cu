@@ -43,6 +43,11 @@ struct TileParams {
   int lr_mul, lc_mul;
   int cr_0, cr_s, cr_mul, cc_0, cc_s, cc_mul;
   int out_vec;         // output rows allow 128-bit (f32) / 32-bit (u8) stores
+  // skip != 0: the luma plane is staged per SAMPLE, not per rectangle: slot 2i+k holds the source row of the k-th
+  // (top/left, bottom/right) sample of the tile's i-th position along the axis that maps to source rows. A down-scale
+  // by s >= 2 along that axis touches only 2 of every s source rows: C3 stages 64 luma rows per tile instead of 134.
+  int skip;
+  int l_row_0, l_row_mul;  // source luma row = l_row_0 + l_row_mul * (virtual index along the row axis)
   int l_lpr_shift, c_lpr_shift;  // log2(threads serving one staged row) for the luma / chroma planes
   int off_terms;       // offset of the per-tile term tables in dynamic shared memory
 };
@@ -101,6 +106,31 @@ __host__ __device__ __forceinline__ int staged_pitch(int first_byte, int last_by
 // G == 4 : 32-bit loads through registers (any word-aligned layout).
 // 2^lpr_shift threads serve one staged row (the next power of two >= granules per row, a launch constant), so the
 // loop has no division: (source, destination) advance by a fixed number of rows per pass.
+// Per-sample luma staging (skip mode): staged row `slot` comes from source row row_of(slot).
+template <int G, typename RowOf>
+__device__ __forceinline__ void stage_rows(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride, int nslots,
+                                           int first_byte, int pitch, int lpr_shift, int row_bytes, RowOf row_of) {
+  const int gpr = min(pitch / G, (row_bytes - (first_byte / G) * G + G - 1) / G);
+  const int lpr = 1 << lpr_shift;
+  const int rows_per_pass = (int)blockDim.x >> lpr_shift;
+  const int g0 = (int)threadIdx.x & (lpr - 1);
+  if (g0 >= gpr) return;
+  const uint8_t* col0 = plane + (first_byte / G) * G + g0 * G;
+  const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(smem_dst) + (uint32_t)(g0 * G);
+  for (int r = (int)threadIdx.x >> lpr_shift; r < nslots; r += rows_per_pass) {
+    const uint8_t* src = col0 + (long long)row_of(r) * stride;
+    const uint32_t dst = dst0 + (uint32_t)(r * pitch);
+    for (int g = g0, o = 0; g < gpr; g += lpr, o += lpr * G) {
+      if (G == 16) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(src + o) : "memory");
+      } else {
+        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + o));
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(dst + o), "r"(v) : "memory");
+      }
+    }
+  }
+}
+
 template <int G>
 __device__ __forceinline__ void stage_plane(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride,
                                             int row0, int nrows, int first_byte, int pitch, int lpr_shift,
@@ -169,7 +199,21 @@ struct __align__(16) ColTerms {   // everything an output COLUMN contributes (32
   uint32_t wp;      // packed 7-bit column weights
   int pad[3];
 };
-__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy) {
+// Clamped virtual rows (columns) sampled by output row oy (column ox): fetch_px's clamps.
+__device__ __forceinline__ void virt_rows(const BandCuPlanDesc& d, int oy, int* rA, int* rB) {
+  long long y = (long long)d.y0 + (long long)oy * d.dy;
+  if (y > d.max_y) y = d.max_y;
+  const int yi = (int)(y >> 16);
+  *rA = min(max(yi, 0), d.vh - 1);
+  *rB = min(max(yi + 1, 0), d.vh - 1);
+}
+__device__ __forceinline__ void virt_cols(const BandCuPlanDesc& d, int ox, int* cA, int* cB) {
+  const int xi = (int)(((long long)d.x0 + (long long)ox * d.dx) >> 16);
+  *cA = min(max(xi, 0), d.vw - 1);
+  *cB = min(max(xi + 1, 0), d.vw - 1);
+}
+// `slot_pitch` != 0: this axis selects the staged luma row (skip mode): offsets are slot * pitch for tile position i.
+__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy, int i, int slot_pitch) {
   const BandCuPlanDesc& d = P.d;
   long long y = (long long)d.y0 + (long long)oy * d.dy;
   if (y > d.max_y) y = d.max_y;
@@ -178,13 +222,13 @@ __device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy) {
   t.w1 = d.linear ? 0u : (uint32_t)((y >> 8) & 255);
   t.w0 = 256u - t.w1;
   const int rA = min(max(yi, 0), d.vh - 1), rB = min(max(yi + 1, 0), d.vh - 1);
-  t.lA = P.lr_mul * rA;
-  t.lB = P.lr_mul * rB;
+  t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lr_mul * rA;
+  t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lr_mul * rB;
   t.kA = P.cr_mul * ((P.cr_0 + P.cr_s * rA) >> 1);
   t.kB = P.cr_mul * ((P.cr_0 + P.cr_s * rB) >> 1);
   return t;
 }
-__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox) {
+__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i, int slot_pitch) {
   const BandCuPlanDesc& d = P.d;
   const long long x = (long long)d.x0 + (long long)ox * d.dx;
   const int xi = (int)(x >> 16);
@@ -192,8 +236,8 @@ __device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox) {
   ColTerms t;
   t.wp = xf | ((0x7fu ^ xf) << 16);
   const int cA = min(max(xi, 0), d.vw - 1), cB = min(max(xi + 1, 0), d.vw - 1);
-  t.lA = P.lc_mul * cA;
-  t.lB = P.lc_mul * cB;
+  t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lc_mul * cA;
+  t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lc_mul * cB;
   t.kA = P.cc_mul * ((P.cc_0 + P.cc_s * cA) >> 1);
   t.kB = P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
   return t;
@@ -246,7 +290,17 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   uint8_t* sl = smem;
   uint8_t* su = sl + P.l_rows_max * P.l_pitch;
   uint8_t* sv;
-  stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
+  if (P.skip) {
+    const int npos = SWAP ? (ox1 - ox0 + 1) : (oy1 - oy0 + 1);
+    stage_rows<G>(sl, f.p0, d.stride0, 2 * npos, l_first, P.l_pitch, P.l_lpr_shift, d.src_width, [&](int slot) {
+      int a, b;
+      if (SWAP) virt_cols(d, ox0 + (slot >> 1), &a, &b);
+      else virt_rows(d, oy0 + (slot >> 1), &a, &b);
+      return P.l_row_0 + P.l_row_mul * ((slot & 1) ? b : a);
+    });
+  } else {
+    stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
+  }
   if (P.interleaved) {
     stage_plane<G>(su, P.v_first ? f.pv : f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
     sv = su + (P.v_first ? 0 : 1);
@@ -261,13 +315,13 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // 8 warps
   RowTerms* rt = reinterpret_cast<RowTerms*>(smem + P.off_terms);        // [32], 32 bytes each
   ColTerms* ct = reinterpret_cast<ColTerms*>(smem + P.off_terms + 1024);  // [32], 32 bytes each
-  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1));
-  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1));
+  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1), min(lane, oy1 - oy0), (P.skip && !SWAP) ? P.l_pitch : 0);
+  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1), min(lane, ox1 - ox0), (P.skip && SWAP) ? P.l_pitch : 0);
   if (G == 16) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
   // tile-dependent constants of the two affine address forms
-  const int AL = (d.luma_map.r0 - L.r0) * P.l_pitch + d.luma_map.c0 - (l_first / G) * G;
+  const int AL = (P.skip ? 0 : (d.luma_map.r0 - L.r0) * P.l_pitch) + d.luma_map.c0 - (l_first / G) * G;
   const int AC = (d.chroma_map.r0 - C.r0) * P.c_pitch + d.chroma_map.c0 * ps - (c_first / G) * G;
   const uint8_t* gl = sl + AL;
   const uint8_t* gu = su + AC;
@@ -342,7 +396,7 @@ struct TileGeom {
   size_t stage_bytes;  // luma + chroma plane(s)
 };
 template <int G>
-static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool interleaved) {
+static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool interleaved, bool skip) {
   const int tiles_x = (d.dst_width + TC - 1) / TC, tiles_y = (d.dst_height + TR - 1) / TR;
   TileGeom g = {0, 0, 0, 0, 0};
   const int ps = d.pixel_stride_uv;
@@ -360,6 +414,7 @@ static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool inte
       g.c_rows = max(g.c_rows, C.r1 - C.r0 + 1);
     }
   }
+  if (skip) g.l_rows = 2 * (d.luma_map.rr != 0 ? TR : TC);  // two sampled source rows per tile position
   g.stage_bytes = (size_t)g.l_rows * g.l_pitch + (size_t)(interleaved ? 1 : 2) * g.c_rows * g.c_pitch;
   g.stage_bytes = (g.stage_bytes + 15) / 16 * 16;
   return g;
@@ -369,6 +424,7 @@ struct TilePlan {
   float* lut_dev;
   int TR, TC;
   TileGeom g16, g4;
+  bool skip;
 };
 
 static bool is_permutation(const BandCuAffine& m) {
@@ -394,12 +450,16 @@ bool tile_plan_supported(const BandCuPlanDesc& d) {
 int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   const bool inter = d.pixel_stride_uv == 2;
   const int TR = 32, TC = 32;  // lanes run along one tile edge: both stay 32
-  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter), g4 = tile_geometry<4>(d, TR, TC, inter);
+  // per-sample luma staging pays once the down-scale along the axis that maps to source rows reaches 2
+  const char* ns = getenv("BANDCU_TILE_NO_SKIP");
+  const bool skip = !(ns && ns[0] == '1') && (d.luma_map.rr != 0 ? d.dy : d.dx) >= 0x20000;
+  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter, skip), g4 = tile_geometry<4>(d, TR, TC, inter, skip);
   if (g16.stage_bytes + 2048 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
   p->TR = TR; p->TC = TC;
   p->g16 = g16; p->g4 = g4;
+  p->skip = skip;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
@@ -472,6 +532,9 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.l_rows_max = g.l_rows; P.c_rows_max = g.c_rows;
   // separable address forms (signed permutations: each mapped coordinate depends on one virtual coordinate)
   const int ps = d.pixel_stride_uv;
+  P.skip = p->skip ? 1 : 0;
+  P.l_row_0 = d.luma_map.r0;
+  P.l_row_mul = d.luma_map.rr != 0 ? d.luma_map.rr : d.luma_map.rc;
   P.lr_mul = d.luma_map.rr * g.l_pitch + d.luma_map.cr;
   P.lc_mul = d.luma_map.rc * g.l_pitch + d.luma_map.cc;
   const int BC = d.chroma_map.rr * g.c_pitch + d.chroma_map.cr * ps;  // per chroma-index row

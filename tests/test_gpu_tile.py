@@ -105,3 +105,28 @@ def test_planar_identity_map_row_staged(O, fmt_name, W, H, dw, dh, f32):
         del os.environ["BANDCU_DISABLE_FAST"]
     assert st == 0
     assert_same_bits(got, want, "planar %s without the row-staged kernel" % fmt_name)
+
+
+@pytest.mark.parametrize("fmt_name", ["YV12", "NV21"])
+@pytest.mark.parametrize("pre", [[(2, 90)], [(3, 1, 0)], [(2, 270), (3, 0, 1)]])
+def test_mild_down_scale_stages_whole_rectangles(O, fmt_name, pre):
+    """Ratios below 2 keep rectangle staging of the luma plane (consecutive samples share source rows); ratios of 2
+    and more stage per sample. 640x352 -> 250x400 after a quarter-turn is 1.41 x 1.6; the flip case is 1.6 x 1.41 on
+    one axis and crosses the threshold on neither."""
+    W, H = 640, 352
+    fmt = getattr(O, "FMT_" + fmt_name)
+    turned = any(op[0] == 2 and op[1] in (90, 270) for op in pre)
+    dw, dh = (250, 400) if turned else (400, 250)
+    ops = list(pre) + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh), NORM]
+    fr = rand_frames(O, 2, W, H, fmt, 99)
+    _run_both(O, ops, fr, W, H, fmt, O.DT_F32, (1, dh, dw, 3), resident=True)
+    # and the same chain with per-sample staging switched off must agree too (both modes, same bits)
+    os.environ["BANDCU_TILE_NO_SKIP"] = "1"
+    try:
+        ops2 = list(pre) + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw // 3, dh // 3)]
+        st, want = oracle_chain(O, ops2, fr, W, H, fmt, O.DT_U8, (1, dh // 3, dw // 3, 3))
+        st2, got = gpu_chain(ops2, fr, W, H, fmt, O.DT_U8, (1, dh // 3, dw // 3, 3), device_resident=True)
+    finally:
+        del os.environ["BANDCU_TILE_NO_SKIP"]
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, "rectangle staging at a large ratio")
