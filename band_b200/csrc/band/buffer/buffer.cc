@@ -249,6 +249,16 @@ DataType Buffer::GetDataType() const { return data_type_; }
 BufferFormat Buffer::GetBufferFormat() const { return buffer_format_; }
 BufferOrientation Buffer::GetOrientation() const { return orientation_; }
 
+bool Buffer::IsPinnedHost() const {
+  if (pinned_cache_ < 0) {
+    int pinned = (space_ == MemorySpace::kHost && !data_planes_.empty()) ? 1 : 0;
+    for (size_t k = 0; pinned && k < data_planes_.size(); ++k)
+      if (data_planes_[k].data == nullptr || bandcu_pointer_kind(data_planes_[k].data) != 1) pinned = 0;
+    pinned_cache_ = pinned;
+  }
+  return pinned_cache_ == 1;
+}
+
 bool Buffer::IsYUV(BufferFormat f) {
   return f == BufferFormat::kNV21 || f == BufferFormat::kNV12 || f == BufferFormat::kYV21 || f == BufferFormat::kYV12;
 }

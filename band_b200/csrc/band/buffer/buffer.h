@@ -68,6 +68,9 @@ class Buffer {
   BufferOrientation GetOrientation() const;
   // additive: the camera layer knows the sensor orientation only after the view exists (BandBufferSetOrientation)
   void SetOrientation(BufferOrientation orientation) { orientation_ = orientation; }
+  // additive: every plane of this HOST buffer lies in pinned (page-locked, device-mapped) memory. Asked of the CUDA
+  // runtime once per buffer and remembered: batch calls hand the same views over and over.
+  bool IsPinnedHost() const;
   MemorySpace GetMemorySpace() const { return space_; }  // additive
 
   absl::Status CopyFrom(const Buffer& rhs);
@@ -91,6 +94,7 @@ class Buffer {
   DataType data_type_ = DataType::kUInt8;
   BufferOrientation orientation_;
   MemorySpace space_ = MemorySpace::kHost;
+  mutable int pinned_cache_ = -1;  // IsPinnedHost(): -1 unknown, 0 no, 1 yes (a view's planes never change)
   // owning buffers keep their allocation alive here; the deleter knows the space
   std::shared_ptr<unsigned char> storage_;
 };

@@ -823,10 +823,8 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   // space under UVA) the kernel pulls those rows straight over PCIe: rows the resize never samples never
   // cross the bus and there is no staging copy at all. Pageable frames are staged through HBM as before.
   bool zero_copy = in_host && !writes_input_ && IsSingleFastLaunch() && getenv("BAND_NO_ZERO_COPY") == nullptr;
-  for (int f = 0; zero_copy && f < m; ++f) {
-    for (int k = 0; k < input_.num_planes; ++k)
-      if (bandcu_pointer_kind((*inputs[f])[k].data) != 1) { zero_copy = false; break; }
-  }
+  for (int f = 0; zero_copy && f < m; ++f)
+    if (!inputs[f]->IsPinnedHost()) zero_copy = false;
   const bool in_staged = in_host && !zero_copy;
   // Zero-copy output: the staged kernel assembles rows in shared memory and pushes them into PINNED host tensors
   // with bulk stores, so results cross PCIe while the next source rows are being pulled (both directions of the
@@ -837,7 +835,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
                  GetDataTypeBytes(output_.dtype)) % 16 == 0;
   for (int f = 0; zc_out && f < m; ++f) {
     const unsigned char* p = (*outputs[f])[0].data;
-    if ((reinterpret_cast<uintptr_t>(p) & 15) != 0 || bandcu_pointer_kind(p) != 1) zc_out = false;
+    if ((reinterpret_cast<uintptr_t>(p) & 15) != 0 || !outputs[f]->IsPinnedHost()) zc_out = false;
   }
   if (IsSingleFastLaunch() && bandcu_plan_set_host_output(segments_[0].plan, zc_out ? 1 : 0) != BANDCU_OK)
     return CudaError("bandcu_plan_set_host_output");

@@ -38,9 +38,9 @@ ALG_BYTES = FRAME_BYTES + OUT_BYTES                            # 3 712 512 (SURV
 WORKLOAD = "1080p NV12 -> ColorSpaceConvert(RGB) -> Resize(224,224) -> Normalize(127.5,127.5) f32 [1,224,224,3]"
 METRIC = "frames/s (1080p NV12->224x224 RGB f32)"
 # dram__bytes_read.sum + dram__bytes_write.sum of the fused kernel per frame, from the committed ncu --set full
-# capture (profiles/r01_ncu_full_fast_v3.txt: 770.769 MB + 279.967 MB over a 512-frame launch). Below the
+# capture (profiles/r01_ncu_full_fast_v4.txt: 770.881 MB + 279.695 MB over a 512-frame launch). Below the
 # algorithmic figure because the down-scaler never reads the source rows it does not sample.
-NCU_TRAFFIC_PER_FRAME = (770.769152e6 + 279.966720e6) / 512
+NCU_TRAFFIC_PER_FRAME = (770.880512e6 + 279.695104e6) / 512
 
 
 def measured_peak():
@@ -337,8 +337,8 @@ def run_ours(args):
         "gpu_launches": gpu_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": args.traffic if args.traffic is not None else NCU_TRAFFIC_PER_FRAME * F,
-                     "traffic_source": "ncu --set full, profiles/r01_ncu_full_fast_v3.txt, scaled per frame",
-                     "peak_source": peak_src, "kernel": "fast_nv_bilinear_down_kernel<float,false>",
+                     "traffic_source": "ncu --set full, profiles/r01_ncu_full_fast_v4.txt, scaled per frame",
+                     "peak_source": peak_src, "kernel": "fast_nv_bilinear_down_kernel<float, kChromaUV, BULKOUT=false>",
                      "kernel_ms": kernel_ms, "bytes_per_launch_algorithmic": ALG_BYTES * F},
         "clocks": clocks, "parity": None,
     }
