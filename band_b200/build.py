@@ -96,6 +96,21 @@ def build_testing(force=False):
     return out
 
 
+def build_tools(force=False):
+    """lib/band_preproc_benchmark: the C++ benchmark CLI (tools/band_preproc_benchmark.cc), a client of the two C ABIs."""
+    out = os.path.join(LIBDIR, "band_preproc_benchmark")
+    src = os.path.join(ROOT, "tools", "band_preproc_benchmark.cc")
+    if not os.path.exists(src):
+        return None
+    host = os.path.join(LIBDIR, "libband_c.so")
+    if not force and not _stale(out, [src, host]):
+        return out
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    _run([cxx, "-O2", "-std=c++17", "-Wall", "-Wextra", "-I" + INCLUDE, "-o", out, src, "-L" + LIBDIR, "-lband_c", "-lbandcu",
+          "-Wl,-rpath,$ORIGIN", "-lpthread"])
+    return out
+
+
 def build_oracle(force=False):
     """oracle/_build/liborc.so (checker + timed CPU baseline; never loaded by the product)."""
     odir = os.path.join(ROOT, "oracle")
@@ -118,6 +133,9 @@ def build_all(force=False, verbose=False):
     if b:
         libs.append(b)
     t = build_testing(force)
+    if t:
+        libs.append(t)
+    t = build_tools(force)
     if t:
         libs.append(t)
     libs.append(build_oracle(force))

@@ -213,3 +213,27 @@ def test_crop_then_rgb_to_yuv_chain(O):
     st, got, info = gpu_image_chain(ops, fr, W, H, O.FMT_RGB, O.FMT_NV21, O.DT_U8, w, h)
     assert st == 0 and info[:3] == (w, h, O.FMT_NV21)
     assert_same_bits(got, cur, "rotate+crop+rgb->nv21")
+
+
+def test_cpp_benchmark_tool_runs_the_fused_path(tmp_path):
+    """tools/band_preproc_benchmark.cc: the C++ CLI (a client of the two C ABIs only) runs a small config on the GPU and
+    reports one fused launch per step."""
+    import json
+    import os
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "band_b200", "lib", "band_preproc_benchmark")
+    assert os.path.exists(exe), "run __graft_entry__.build()"
+    cfg = tmp_path / "cfg.json"
+    cfg.write_text(json.dumps({"format": "NV21", "width": 640, "height": 480,
+                               "operators": [["color_space_convert", "RGB"], ["resize", 224, 224], ["normalize", 127.5, 127.5]],
+                               "output": {"dtype": "float32", "dims": [1, 224, 224, 3]},
+                               "frames_per_step": 64, "steps": 3, "warmup": 1, "devices": [0]}))
+    out = subprocess.run([exe, str(cfg)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    rep = json.loads(out.stdout.strip().splitlines()[-1])
+    assert rep["fused_single_launch"] == 1 and rep["launches_per_step"] == 1.0 and rep["frames_per_s"] > 0
+    bad = tmp_path / "bad.json"
+    bad.write_text('{"operators": [["sharpen", 1]]}')
+    out = subprocess.run([exe, str(bad)], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 2 and "unknown operator" in out.stderr
