@@ -56,6 +56,7 @@ struct FastParams {
   int groups_per_frame;
   long long n_items;
   int use_bulk;        // 1: cp.async.bulk staging, 0: producer-warp byte copies
+  long long luma_off, chroma_off;  // Crop folded into the frame: byte offsets of the crop origin in the luma / chroma planes
   int v_off;           // planar chroma: byte offset of the V row inside a chroma slot (the U row sits at 0)
   int out_row_bytes;   // dw * 3 * sizeof(OT)
   int out_buf_bytes;   // BULKOUT: R * out_row_bytes (one of two output staging buffers)
@@ -161,7 +162,10 @@ template <int CH>
 __device__ __forceinline__ void produce_item(const FastParams& P, int f, int g, uint8_t* stage, uint32_t* rowinfo,
                                              uint64_t* full) {
   const int lane = threadIdx.x;
-  const FramePtrs fp = frame_ptrs(P.batch, f);
+  FramePtrs fp = frame_ptrs(P.batch, f);
+  fp.p0 += P.luma_off;
+  fp.pu += P.chroma_off;
+  fp.pv += P.chroma_off;
   const uint8_t* uv = CH == kChromaVU ? fp.pv : fp.pu;  // first byte of each interleaved pair; planar: the U plane
   const int hb = (P.W + 1) >> 1;                         // planar: bytes per chroma row of one plane
   const int oy0 = g * P.R;
@@ -439,9 +443,16 @@ __global__ void build_lut_kernel(float* lut, float mean, float sd) {
   if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
 }
 
-static bool is_identity(const BandCuAffine& m) {
-  return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
+// Crop only (a translation): the crop origin becomes a byte offset into each plane and the kernel runs unchanged on
+// the cropped width. CropNv / CropYv take the chroma origin at (x0/2, y0/2) (libyuv_image_operator.cc:950-1037), which
+// is what the plan's chroma map carries; a crop AFTER the conversion (pre_map translation) samples chroma at
+// ((y0+r)>>1, (x0+c)>>1), the same thing only for even origins.
+static bool is_translation(const BandCuAffine& m) { return m.rr == 1 && m.rc == 0 && m.cr == 0 && m.cc == 1 && m.r0 >= 0 && m.c0 >= 0; }
+static bool crop_only(const BandCuPlanDesc& d) {
+  return is_translation(d.luma_map) && is_translation(d.pre_map) && is_translation(d.chroma_map) &&
+         (d.pre_map.r0 & 1) == 0 && (d.pre_map.c0 & 1) == 0;
 }
+
 
 static int env_int(const char* name, int lo, int hi, int dflt) {
   const char* v = getenv(name);
@@ -456,7 +467,7 @@ bool fast_plan_supported(const BandCuPlanDesc& d) {
   if (d.src_kind != BANDCU_SRC_YUV420 || (d.pixel_stride_uv != 2 && d.pixel_stride_uv != 1)) return false;
   if (d.cvt != BANDCU_CVT_YUV2RGB || d.channels != 3) return false;
   if (d.flavor != BANDCU_FLAVOR_ARGB || d.scale_mode != BANDCU_SCALE_BILINEAR_DOWN) return false;
-  if (!is_identity(d.luma_map) || !is_identity(d.pre_map) || !is_identity(d.chroma_map)) return false;
+  if (!crop_only(d)) return false;  // identity maps included
   if (d.normalize ? (d.out_dtype != BANDCU_DT_F32) : false) return false;
   if (d.vw < 2 || d.vw > 8192 || d.dst_width > 4096) return false;
   // 32-bit x stepping inside the kernel
@@ -535,6 +546,9 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   const int cbytes = ((d.vw + 1) >> 1) << 1;
   P.row_pitch = ((cbytes + 15) / 16) * 16 + 16;  // +16: xi+1 may touch one byte past the row when xf == 0
   P.v_off = ((((d.vw + 1) >> 1) + 15) / 16) * 16;
+  P.luma_off = (long long)d.luma_map.r0 * d.stride0 + d.luma_map.c0;
+  P.chroma_off = (long long)(d.chroma_map.r0 + d.pre_map.r0 / 2) * d.stride_uv +
+                 (long long)(d.chroma_map.c0 + d.pre_map.c0 / 2) * d.pixel_stride_uv;
   // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
   P.R = p->R; P.S = p->S;
   // small batches (the single-frame latency case): fewer rows per item so that every SM gets work
@@ -566,7 +580,8 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.n_items = (long long)n * P.groups_per_frame;
   P.lut = p->lut_dev;
   P.batch = batch;
-  bool aligned = (d.vw % 16 == 0) && (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0);
+  bool aligned = (d.vw % 16 == 0) && (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0) && (P.luma_off % 16 == 0) &&
+                 (P.chroma_off % 16 == 0);
   if (ch == kChromaPlanar) {
     aligned = aligned && (d.vw % 32 == 0);  // each plane's chroma row is its own 16-byte granular copy
     if (batch.table) aligned = aligned && hints.planes_aligned16;

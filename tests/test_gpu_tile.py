@@ -130,3 +130,32 @@ def test_mild_down_scale_stages_whole_rectangles(O, fmt_name, pre):
         del os.environ["BANDCU_TILE_NO_SKIP"]
     assert st == 0 and st2 == 0
     assert_same_bits(got, want, "rectangle staging at a large ratio")
+
+
+@pytest.mark.parametrize("fmt_name", ["NV12", "YV12"])
+@pytest.mark.parametrize("order,box", [
+    ("crop_first", (64, 32, 1343, 751)),    # 16-byte aligned origin: row-staged kernel, bulk path (center-crop style)
+    ("crop_first", (3, 5, 1202, 700)),      # odd origin: chroma origin is (x0/2, y0/2); byte staging
+    ("csc_first", (128, 64, 1151, 655)),    # crop AFTER the conversion, even origin: same samples as a chroma translation
+    ("csc_first", (5, 3, 1004, 602)),       # odd origin after the conversion: chroma phase differs -> tile-staged kernel
+])
+def test_crop_folds_into_the_row_staged_kernel(O, fmt_name, order, box):
+    W, H = 1408, 800
+    fmt = getattr(O, "FMT_" + fmt_name)
+    crop = (O.OP_CROP,) + box
+    csc = (O.OP_CSC, O.FMT_RGB)
+    ops = ([crop, csc] if order == "crop_first" else [csc, crop]) + [(O.OP_RESIZE, 224, 224), NORM]
+    fr = rand_frames(O, 3, W, H, fmt, 555)
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, O.DT_F32, (1, 224, 224, 3))
+    assert st == 0
+    for resident in (True, False):
+        st, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, 224, 224, 3), device_resident=resident)
+        assert st == 0
+        assert_same_bits(got, want, "%s %s resident=%s" % (order, box, resident))
+    os.environ["BANDCU_DISABLE_FAST"] = "1"
+    try:
+        st, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, 224, 224, 3), device_resident=True)
+    finally:
+        del os.environ["BANDCU_DISABLE_FAST"]
+    assert st == 0
+    assert_same_bits(got, want, "%s %s without the row-staged kernel" % (order, box))
