@@ -42,7 +42,8 @@ EXPORTED = [
     "BandDeviceFree", "BandCopyToDevice", "BandCopyToHost", "BandCudaLaunchCount", "BandGetLastError",
     "BandTensorRingBufferCreate", "BandTensorRingBufferDelete", "BandTensorRingBufferAlloc",
     "BandTensorRingBufferIsHandleValid", "BandTensorRingBufferGetSlot", "BandTensorRingBufferPutTensor",
-    "BandTensorRingBufferGetTensor", "BandBufferSetOrientation",
+    "BandTensorRingBufferGetTensor", "BandBufferSetOrientation", "BandImageProcessorRecordBatch",
+    "BandRecordedBatchReplay", "BandRecordedBatchDelete",
 ]
 
 
@@ -111,6 +112,10 @@ def lib():
     L.BandCudaLaunchCount.restype = C.c_longlong
     L.BandGetLastError.restype = C.c_char_p
     L.BandBufferSetOrientation.argtypes = [vp, ci]
+    L.BandImageProcessorRecordBatch.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
+    L.BandImageProcessorRecordBatch.restype = vp
+    L.BandRecordedBatchReplay.argtypes = [vp, ci]
+    L.BandRecordedBatchDelete.argtypes = [vp]
     L.BandTensorRingBufferCreate.argtypes = [C.POINTER(vp), C.POINTER(ci), sz, ci, ci]
     L.BandTensorRingBufferCreate.restype = vp
     L.BandTensorRingBufferDelete.argtypes = [vp]
@@ -313,6 +318,24 @@ class ImageProcessor:
         ba = (C.c_void_p * n)(*[b.handle for b in buffers])
         ta = (C.c_void_p * n)(*[t.handle for t in tensors])
         return lib().BandImageProcessorProcessBatch(self.handle, ba, ta, n)
+
+    def record_batch(self, buffers, tensors):
+        """BandImageProcessorRecordBatch -> opaque handle (replay with replay(), free with release())."""
+        n = len(buffers)
+        ba = (C.c_void_p * n)(*[b.handle for b in buffers])
+        ta = (C.c_void_p * n)(*[t.handle for t in tensors])
+        h = lib().BandImageProcessorRecordBatch(self.handle, ba, ta, n)
+        if not h:
+            raise BandError("BandImageProcessorRecordBatch failed: " + last_error())
+        return h
+
+    @staticmethod
+    def replay(recorded, synchronize=True):
+        return lib().BandRecordedBatchReplay(recorded, 1 if synchronize else 0)
+
+    @staticmethod
+    def release(recorded):
+        lib().BandRecordedBatchDelete(recorded)
 
     def process_batch_handles(self, buffer_array, tensor_array, n):
         """Same call with pre-built ctypes arrays (keeps Python overhead out of timed loops)."""

@@ -5,6 +5,7 @@
 #include "band/buffer/buffer.h"
 #include "band/buffer/fused_plan.h"
 #include "band/logger.h"
+#include "bandcu.h"
 
 namespace band {
 
@@ -89,6 +90,33 @@ absl::Status BufferProcessor::ProcessBatchAsync(const Buffer* const* inputs, Buf
   if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::ProcessBatchAsync failed %s", status.ToString().c_str());
   return status;
 }
+
+absl::Status BufferProcessor::RecordBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n,
+                                          void** graph_exec) {
+  if (n == 0 || inputs == nullptr || outputs == nullptr || inputs[0] == nullptr || outputs[0] == nullptr)
+    return absl::InvalidArgumentError("RecordBatch: null buffer list");
+  for (size_t f = 0; f < n; ++f) {
+    const bool in_ok = inputs[f] && (inputs[f]->GetMemorySpace() == MemorySpace::kDevice || inputs[f]->IsPinnedHost());
+    const bool out_ok = outputs[f] && (outputs[f]->GetMemorySpace() == MemorySpace::kDevice || outputs[f]->IsPinnedHost());
+    if (!in_ok || !out_ok)
+      return absl::InvalidArgumentError("RecordBatch: frames and outputs must be device-resident or pinned host memory");
+  }
+  RETURN_IF_ERROR(Prepare(*inputs[0], *outputs[0]));
+  absl::Status status = plan_->Record(inputs, outputs, static_cast<int>(n), graph_exec);
+  if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::RecordBatch failed %s", status.ToString().c_str());
+  return status;
+}
+
+absl::Status BufferProcessor::ReplayBatch(void* graph_exec, bool synchronize) {
+  if (!plan_ || graph_exec == nullptr) return absl::InvalidArgumentError("ReplayBatch: nothing recorded");
+  if (bandcu_graph_launch(graph_exec, plan_->ComputeStream()) != BANDCU_OK)
+    return absl::InternalError(bandcu_last_error_string());
+  if (synchronize && bandcu_stream_sync(plan_->ComputeStream()) != BANDCU_OK)
+    return absl::InternalError(bandcu_last_error_string());
+  return absl::OkStatus();
+}
+
+void BufferProcessor::ReleaseRecordedBatch(void* graph_exec) { bandcu_graph_destroy(graph_exec); }
 
 absl::Status BufferProcessor::Synchronize() { return plan_ ? plan_->Synchronize() : absl::OkStatus(); }
 void* BufferProcessor::GetComputeStream() const { return plan_ ? plan_->ComputeStream() : nullptr; }

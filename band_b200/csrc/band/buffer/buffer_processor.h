@@ -54,6 +54,11 @@ class BufferProcessor {
   // Additive: enqueue only; results are complete after Synchronize(). The buffers must stay alive until then.
   virtual absl::Status ProcessBatchAsync(const Buffer* const* inputs, Buffer* const* outputs, size_t n);
   absl::Status Synchronize();
+  // Additive: record one batch into a CUDA graph (cuda::FusedPlan::Record); *graph_exec is replayed with ReplayBatch
+  // and released with ReleaseRecordedBatch. Frames and outputs must be device-resident (or pinned) and stay in place.
+  absl::Status RecordBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n, void** graph_exec);
+  absl::Status ReplayBatch(void* graph_exec, bool synchronize = true);
+  static void ReleaseRecordedBatch(void* graph_exec);
   // CUDA stream the fused launches go to (nullptr before the first Process*); for event timing.
   void* GetComputeStream() const;
   // Additive introspection for tests / benchmarks.

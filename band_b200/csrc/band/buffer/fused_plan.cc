@@ -667,6 +667,26 @@ absl::Status FusedPlan::Synchronize() {
   return absl::OkStatus();
 }
 
+absl::Status FusedPlan::Record(const Buffer* const* inputs, Buffer* const* outputs, int n, void** graph_exec) {
+  if (graph_exec == nullptr || n <= 0) return absl::InvalidArgumentError("Record: bad arguments");
+  *graph_exec = nullptr;
+  // one ordinary pass first: it creates the streams, sizes every plan-owned allocation and proves the batch valid,
+  // so that the recorded pass consists of kernel launches only
+  RETURN_IF_ERROR(Run(inputs, outputs, n, /*synchronize=*/true));
+  if (bandcu_stream_begin_capture(stream_) != BANDCU_OK) return CudaError("bandcu_stream_begin_capture");
+  absl::Status st = Run(inputs, outputs, n, /*synchronize=*/false);
+  void* exec = nullptr;
+  const int rc = bandcu_stream_end_capture(stream_, &exec);  // always close the capture, also after a failed Run
+  in_flight_ = false;                                         // nothing was enqueued: the launches went into the graph
+  if (!st.ok()) {
+    if (exec) bandcu_graph_destroy(exec);
+    return st;
+  }
+  if (rc != BANDCU_OK) return CudaError("bandcu_stream_end_capture");
+  *graph_exec = exec;
+  return absl::OkStatus();
+}
+
 bool FusedPlan::IsSingleFastLaunch() const {
   return segments_.size() == 1 && segments_[0].kind == Segment::Kind::kPixel && segments_[0].plan &&
          bandcu_plan_is_fast(segments_[0].plan) == 1;

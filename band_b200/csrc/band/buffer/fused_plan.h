@@ -82,6 +82,10 @@ class FusedPlan {
   absl::Status Run(const Buffer* const* inputs, Buffer* const* outputs, int n, bool synchronize = true);
   // Waits for everything a Run(..., false) enqueued (compute and copy-out streams).
   absl::Status Synchronize();
+  // Records one Run() over DEVICE-resident (or pinned, zero-copy) frames into a CUDA graph and returns the executable
+  // graph (bandcu_graph_launch / bandcu_graph_destroy). Replaying it costs one graph launch: no validation, no pointer
+  // resolution, no per-segment launch calls. The frames and outputs must stay where they are while the graph is used.
+  absl::Status Record(const Buffer* const* inputs, Buffer* const* outputs, int n, void** graph_exec);
   // The stream the kernels are launched on (created on first use); for CUDA-event timing by harnesses.
   void* ComputeStream();
   size_t NumSegments() const { return segments_.size(); }

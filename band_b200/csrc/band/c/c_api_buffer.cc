@@ -222,6 +222,56 @@ BandStatus BandImageProcessorProcessBatchAsync(BandImageProcessor* image_process
   return ProcessBatchImpl(image_processor, buffers, target_tensors, count, true);
 }
 
+struct BandRecordedBatch {
+  band::BufferProcessor* processor = nullptr;  // not owned
+  void* graph_exec = nullptr;
+};
+
+BandRecordedBatch* BandImageProcessorRecordBatch(BandImageProcessor* image_processor, BandBuffer* const* buffers,
+                                                 BandTensor* const* target_tensors, size_t count) {
+  if (!image_processor || !buffers || !target_tensors || count == 0) {
+    BAND_LOG(LogSeverity::kError, "BandImageProcessorRecordBatch: null argument");
+    return nullptr;
+  }
+  std::vector<const Buffer*> in(count);
+  std::vector<Buffer*> out(count);
+  for (size_t i = 0; i < count; ++i) {
+    if (!buffers[i] || !buffers[i]->impl || !target_tensors[i]) {
+      BAND_LOG(LogSeverity::kError, "BandImageProcessorRecordBatch: entry %d is null", static_cast<int>(i));
+      return nullptr;
+    }
+    in[i] = buffers[i]->impl.get();
+    out[i] = target_tensors[i]->View();
+    if (!out[i]) return nullptr;
+  }
+  void* exec = nullptr;
+  absl::Status status = image_processor->impl->RecordBatch(in.data(), out.data(), count, &exec);
+  if (!status.ok()) {
+    g_last_error = status.ToString();
+    return nullptr;
+  }
+  BandRecordedBatch* r = new BandRecordedBatch();
+  r->processor = image_processor->impl.get();
+  r->graph_exec = exec;
+  return r;
+}
+
+BandStatus BandRecordedBatchReplay(BandRecordedBatch* recorded, int synchronize) {
+  if (!recorded) {
+    BAND_LOG(LogSeverity::kError, "BandRecordedBatch is null");
+    return kBandErr;
+  }
+  absl::Status status = recorded->processor->ReplayBatch(recorded->graph_exec, synchronize != 0);
+  if (!status.ok()) g_last_error = status.ToString();
+  return status.ok() ? kBandOk : kBandErr;
+}
+
+void BandRecordedBatchDelete(BandRecordedBatch* recorded) {
+  if (!recorded) return;
+  band::BufferProcessor::ReleaseRecordedBatch(recorded->graph_exec);
+  delete recorded;
+}
+
 BandStatus BandImageProcessorProcessBuffers(BandImageProcessor* image_processor, BandBuffer* const* inputs,
                                             BandBuffer* const* outputs, size_t count, int async) {
   if (!image_processor || !inputs || !outputs) return kBandErr;

@@ -212,6 +212,11 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
     }
     if (uniform) return bandcu_plan_run_strided(plan, frames, is, os, n, stream);
   }
+  {  // a table upload cannot be part of a recorded graph (see bandcu_stream_begin_capture)
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone)
+      return fail(BANDCU_E_UNSUPPORTED, "plan_run: a pointer-table batch cannot be recorded into a CUDA graph");
+  }
   // what the staged kernel needs to know about the table, established on the host
   TableHints hints;
   hints.valid = true;
@@ -367,6 +372,33 @@ int bandcu_stream_destroy(void* stream) {
 }
 int bandcu_stream_sync(void* stream) {
   CU_TRY(cudaStreamSynchronize((cudaStream_t)stream), "cudaStreamSynchronize");
+  return BANDCU_OK;
+}
+int bandcu_stream_begin_capture(void* stream) {
+  if (!stream) return fail(BANDCU_E_INVALID, "begin_capture: the default stream cannot be captured");
+  CU_TRY(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeRelaxed), "cudaStreamBeginCapture");
+  return BANDCU_OK;
+}
+int bandcu_stream_end_capture(void* stream, void** graph_exec) {
+  if (!graph_exec) return fail(BANDCU_E_INVALID, "end_capture: null out pointer");
+  *graph_exec = nullptr;
+  cudaGraph_t graph = nullptr;
+  CU_TRY(cudaStreamEndCapture((cudaStream_t)stream, &graph), "cudaStreamEndCapture");
+  cudaGraphExec_t exec = nullptr;
+  cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+  (void)cudaGraphDestroy(graph);
+  if (e != cudaSuccess) return fail((int)e, "cudaGraphInstantiate");
+  *graph_exec = (void*)exec;
+  return BANDCU_OK;
+}
+int bandcu_graph_launch(void* graph_exec, void* stream) {
+  if (!graph_exec) return fail(BANDCU_E_INVALID, "graph_launch: null graph");
+  CU_TRY(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream), "cudaGraphLaunch");
+  count_launch();
+  return BANDCU_OK;
+}
+int bandcu_graph_destroy(void* graph_exec) {
+  if (graph_exec) CU_TRY(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec), "cudaGraphExecDestroy");
   return BANDCU_OK;
 }
 int bandcu_event_create(void** ev) {

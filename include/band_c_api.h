@@ -163,6 +163,17 @@ BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBuffers(BandImagePro
                                                                     BandBuffer* const* inputs,
                                                                     BandBuffer* const* outputs, size_t count,
                                                                     int async);
+/* Record one batch into a CUDA graph and replay it: for launch-bound use (one camera frame per call into a fixed
+ * tensor, BASELINE's single-frame latency configuration) a replay is ONE graph launch -- no validation, no plan lookup,
+ * no pointer resolution. Frames and tensors must be device-resident or pinned host memory, stay where they are while
+ * the recording is used, and (count > 1) be laid out at a uniform stride. The processor must outlive the recording. */
+typedef struct BandRecordedBatch BandRecordedBatch;
+BAND_CAPI_EXPORT extern BandRecordedBatch* BandImageProcessorRecordBatch(BandImageProcessor* image_processor,
+                                                                         BandBuffer* const* buffers,
+                                                                         BandTensor* const* target_tensors,
+                                                                         size_t count);
+BAND_CAPI_EXPORT extern BandStatus BandRecordedBatchReplay(BandRecordedBatch* recorded, int synchronize);
+BAND_CAPI_EXPORT extern void BandRecordedBatchDelete(BandRecordedBatch* recorded);
 /* cudaStream_t the processor launches on (NULL before its first Process*); lets a harness bracket the
  * launches with CUDA events. */
 BAND_CAPI_EXPORT extern void* BandImageProcessorGetStream(BandImageProcessor* image_processor);

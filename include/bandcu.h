@@ -208,6 +208,14 @@ BANDCU_API int bandcu_memset(void* dst, int value, size_t bytes, void* stream);
 BANDCU_API int bandcu_stream_create(void** stream);
 BANDCU_API int bandcu_stream_destroy(void* stream);
 BANDCU_API int bandcu_stream_sync(void* stream);
+/* ---- CUDA graphs: record what a stream is given between begin/end, replay it with one launch ----
+ * (launch-bound cases, e.g. the single-frame latency configuration). Capture is thread-local and relaxed: allocation
+ * calls made by the recording thread stay legal. A pointer-table batch cannot be recorded (its table upload would be
+ * replayed from plan-owned memory that later runs rewrite): bandcu_plan_run() fails while its stream is capturing. */
+BANDCU_API int bandcu_stream_begin_capture(void* stream);
+BANDCU_API int bandcu_stream_end_capture(void* stream, void** graph_exec);
+BANDCU_API int bandcu_graph_launch(void* graph_exec, void* stream);
+BANDCU_API int bandcu_graph_destroy(void* graph_exec);
 BANDCU_API int bandcu_event_create(void** ev);
 BANDCU_API int bandcu_event_create_sync(void** ev); /* ordering only (timing disabled) */
 BANDCU_API int bandcu_event_destroy(void* ev);

@@ -178,6 +178,20 @@ def c1_latency(steps):
         out.append({"case": "c1_single_640x480_nv21_to_224_f32_" + ("resident" if resident else "pinned_host"),
                     "latency_us_median": float(np.median(ts)), "latency_us_p10": float(np.percentile(ts, 10)),
                     "latency_us_p90": float(np.percentile(ts, 90)), "note": "host clock around the synchronous call"})
+        # the same call recorded into a CUDA graph (BandImageProcessorRecordBatch) and replayed
+        rec = proc.record_batch([buf], [t])
+        for _ in range(20):
+            assert proc.replay(rec) == B.kBandOk
+        ts = []
+        for _ in range(max(steps, 200)):
+            t0 = time.perf_counter()
+            proc.replay(rec)
+            ts.append((time.perf_counter() - t0) * 1e6)
+        ts = np.array(ts)
+        out.append({"case": "c1_single_640x480_nv21_to_224_f32_" + ("resident" if resident else "pinned_host") + "_cuda_graph",
+                    "latency_us_median": float(np.median(ts)), "latency_us_p10": float(np.percentile(ts, 10)),
+                    "latency_us_p90": float(np.percentile(ts, 90)), "note": "host clock around a synchronous graph replay"})
+        proc.release(rec)
         buf.close(); t.close(); proc.close()
     return out
 

@@ -237,3 +237,50 @@ def test_cpp_benchmark_tool_runs_the_fused_path(tmp_path):
     bad.write_text('{"operators": [["sharpen", 1]]}')
     out = subprocess.run([exe, str(bad)], capture_output=True, text=True, timeout=60)
     assert out.returncode == 2 and "unknown operator" in out.stderr
+
+
+def test_recorded_batch_replays_with_new_frame_contents(O):
+    """BandImageProcessorRecordBatch: one frame recorded into a CUDA graph; the replay sees whatever the frame memory holds
+    at replay time (a camera ring slot refilled in place) and produces the oracle's bits. Pointer-table batches and
+    pageable host frames are refused."""
+    from band_b200 import band_c as B
+    from gpu_util import rand_frames, oracle_chain, to_capi_ops, assert_same_bits
+    W, H, d = 640, 480, 224
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, d, d), (O.OP_NORMALIZE, 0, 0, 0, 0, 127.5, 127.5)]
+    fr = rand_frames(O, 3, W, H, O.FMT_NV21, 2024)
+    st, want = oracle_chain(O, ops, fr, W, H, O.FMT_NV21, O.DT_F32, (1, d, d, 3))
+    assert st == 0
+    L = B.lib()
+    fb = fr.shape[1]
+    dev = L.BandDeviceAlloc(fb)
+    assert dev and L.BandCopyToDevice(dev, fr[0].ctypes.data, fb) == B.kBandOk
+    buf = B.Buffer().set_raw(dev, W, H, B.kBandNV21, device=True)
+    t = B.Tensor(np.float32, (1, d, d, 3), device=True)
+    proc = B.ImageProcessor(to_capi_ops(ops))
+    rec = proc.record_batch([buf], [t])
+    try:
+        assert_same_bits(t.numpy(), want[0], "the recording pass itself")
+        for k in (1, 2, 0):
+            assert L.BandCopyToDevice(dev, fr[k].ctypes.data, fb) == B.kBandOk
+            n0 = L.BandCudaLaunchCount()
+            assert proc.replay(rec) == B.kBandOk, B.last_error()
+            assert L.BandCudaLaunchCount() - n0 == 1
+            assert_same_bits(t.numpy(), want[k], "replay %d" % k)
+        # ordinary calls still work next to a recording
+        assert proc.process(buf, t) == B.kBandOk
+    finally:
+        proc.release(rec)
+    # refused: pageable host frame
+    hb = B.Buffer.from_numpy(fr[0], W, H, B.kBandNV21)
+    with pytest.raises(B.BandError):
+        proc.record_batch([hb], [t])
+    # refused: two frames whose tensors are separate allocations at no uniform stride -> pointer table
+    t2 = B.Tensor(np.float32, (1, d, d, 3), device=True)
+    t3 = B.Tensor(np.float32, (1, d, d, 3), device=True)
+    dev3 = L.BandDeviceAlloc(3 * fb + 4096)
+    bufs = [B.Buffer().set_raw(dev3 + o, W, H, B.kBandNV21, device=True) for o in (0, fb + 256, 2 * fb + 1024)]
+    with pytest.raises(B.BandError):
+        proc.record_batch(bufs, [t, t2, t3])
+    assert proc.process(buf, t) == B.kBandOk      # the processor survives a refused recording
+    L.BandDeviceFree(dev)
+    L.BandDeviceFree(dev3)
