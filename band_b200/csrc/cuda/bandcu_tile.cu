@@ -48,6 +48,10 @@ struct TileParams {
   // by s >= 2 along that axis touches only 2 of every s source rows: C3 stages 64 luma rows per tile instead of 134.
   int skip;
   int l_row_0, l_row_mul;  // source luma row = l_row_0 + l_row_mul * (virtual index along the row axis)
+  // skip_c: the same for the chroma plane(s), once the ratio along that axis reaches 6 (chroma is half resolution):
+  // source chroma row = c_row_0 + c_row_mul * ((q_0 + q_s * virtual index) >> 1), (q_0, q_s) = that axis's pre-map terms
+  int skip_c;
+  int c_row_0, c_row_mul;
   int l_lpr_shift, c_lpr_shift;  // log2(threads serving one staged row) for the luma / chroma planes
   int off_terms;       // offset of the per-tile term tables in dynamic shared memory
 };
@@ -213,7 +217,7 @@ __device__ __forceinline__ void virt_cols(const BandCuPlanDesc& d, int ox, int* 
   *cB = min(max(xi + 1, 0), d.vw - 1);
 }
 // `slot_pitch` != 0: this axis selects the staged luma row (skip mode): offsets are slot * pitch for tile position i.
-__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy, int i, int slot_pitch) {
+__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy, int i, int slot_pitch, int slot_pitch_c) {
   const BandCuPlanDesc& d = P.d;
   long long y = (long long)d.y0 + (long long)oy * d.dy;
   if (y > d.max_y) y = d.max_y;
@@ -224,11 +228,11 @@ __device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy, int i
   const int rA = min(max(yi, 0), d.vh - 1), rB = min(max(yi + 1, 0), d.vh - 1);
   t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lr_mul * rA;
   t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lr_mul * rB;
-  t.kA = P.cr_mul * ((P.cr_0 + P.cr_s * rA) >> 1);
-  t.kB = P.cr_mul * ((P.cr_0 + P.cr_s * rB) >> 1);
+  t.kA = slot_pitch_c ? (2 * i) * slot_pitch_c : P.cr_mul * ((P.cr_0 + P.cr_s * rA) >> 1);
+  t.kB = slot_pitch_c ? (2 * i + 1) * slot_pitch_c : P.cr_mul * ((P.cr_0 + P.cr_s * rB) >> 1);
   return t;
 }
-__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i, int slot_pitch) {
+__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i, int slot_pitch, int slot_pitch_c) {
   const BandCuPlanDesc& d = P.d;
   const long long x = (long long)d.x0 + (long long)ox * d.dx;
   const int xi = (int)(x >> 16);
@@ -238,8 +242,8 @@ __device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i
   const int cA = min(max(xi, 0), d.vw - 1), cB = min(max(xi + 1, 0), d.vw - 1);
   t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lc_mul * cA;
   t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lc_mul * cB;
-  t.kA = P.cc_mul * ((P.cc_0 + P.cc_s * cA) >> 1);
-  t.kB = P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
+  t.kA = slot_pitch_c ? (2 * i) * slot_pitch_c : P.cc_mul * ((P.cc_0 + P.cc_s * cA) >> 1);
+  t.kB = slot_pitch_c ? (2 * i + 1) * slot_pitch_c : P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
   return t;
 }
 // One output pixel from the staged planes: raw products, the 8-bit results sit in bits 23..30.
@@ -301,28 +305,41 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   } else {
     stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
   }
+  const int npos_c = SWAP ? (ox1 - ox0 + 1) : (oy1 - oy0 + 1);
+  auto chroma_row_of = [&](int slot) {
+    int a, b, q;
+    if (SWAP) { virt_cols(d, ox0 + (slot >> 1), &a, &b); q = (P.cc_0 + P.cc_s * ((slot & 1) ? b : a)) >> 1; }
+    else { virt_rows(d, oy0 + (slot >> 1), &a, &b); q = (P.cr_0 + P.cr_s * ((slot & 1) ? b : a)) >> 1; }
+    return P.c_row_0 + P.c_row_mul * q;
+  };
+  auto stage_chroma = [&](uint8_t* dst, const uint8_t* plane) {
+    if (P.skip_c) stage_rows<G>(dst, plane, d.stride_uv, 2 * npos_c, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes, chroma_row_of);
+    else stage_plane<G>(dst, plane, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
+  };
   if (P.interleaved) {
-    stage_plane<G>(su, P.v_first ? f.pv : f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
+    stage_chroma(su, P.v_first ? f.pv : f.pu);
     sv = su + (P.v_first ? 0 : 1);
     su = su + (P.v_first ? 1 : 0);
   } else {
     sv = su + P.c_rows_max * P.c_pitch;
-    stage_plane<G>(su, f.pu, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
-    stage_plane<G>(sv, f.pv, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
+    stage_chroma(su, f.pu);
+    stage_chroma(sv, f.pv);
   }
   if (G == 16) asm volatile("cp.async.commit_group;" ::: "memory");
 
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // 8 warps
   RowTerms* rt = reinterpret_cast<RowTerms*>(smem + P.off_terms);        // [32], 32 bytes each
   ColTerms* ct = reinterpret_cast<ColTerms*>(smem + P.off_terms + 1024);  // [32], 32 bytes each
-  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1), min(lane, oy1 - oy0), (P.skip && !SWAP) ? P.l_pitch : 0);
-  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1), min(lane, ox1 - ox0), (P.skip && SWAP) ? P.l_pitch : 0);
+  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1), min(lane, oy1 - oy0), (P.skip && !SWAP) ? P.l_pitch : 0,
+                                 (P.skip_c && !SWAP) ? P.c_pitch : 0);
+  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1), min(lane, ox1 - ox0), (P.skip && SWAP) ? P.l_pitch : 0,
+                                      (P.skip_c && SWAP) ? P.c_pitch : 0);
   if (G == 16) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
   // tile-dependent constants of the two affine address forms
   const int AL = (P.skip ? 0 : (d.luma_map.r0 - L.r0) * P.l_pitch) + d.luma_map.c0 - (l_first / G) * G;
-  const int AC = (d.chroma_map.r0 - C.r0) * P.c_pitch + d.chroma_map.c0 * ps - (c_first / G) * G;
+  const int AC = (P.skip_c ? 0 : (d.chroma_map.r0 - C.r0) * P.c_pitch) + d.chroma_map.c0 * ps - (c_first / G) * G;
   const uint8_t* gl = sl + AL;
   const uint8_t* gu = su + AC;
   const uint8_t* gv = sv + AC;
@@ -396,7 +413,7 @@ struct TileGeom {
   size_t stage_bytes;  // luma + chroma plane(s)
 };
 template <int G>
-static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool interleaved, bool skip) {
+static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool interleaved, bool skip, bool skip_c) {
   const int tiles_x = (d.dst_width + TC - 1) / TC, tiles_y = (d.dst_height + TR - 1) / TR;
   TileGeom g = {0, 0, 0, 0, 0};
   const int ps = d.pixel_stride_uv;
@@ -415,6 +432,7 @@ static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool inte
     }
   }
   if (skip) g.l_rows = 2 * (d.luma_map.rr != 0 ? TR : TC);  // two sampled source rows per tile position
+  if (skip_c) g.c_rows = 2 * (d.luma_map.rr != 0 ? TR : TC);
   g.stage_bytes = (size_t)g.l_rows * g.l_pitch + (size_t)(interleaved ? 1 : 2) * g.c_rows * g.c_pitch;
   g.stage_bytes = (g.stage_bytes + 15) / 16 * 16;
   return g;
@@ -424,7 +442,7 @@ struct TilePlan {
   float* lut_dev;
   int TR, TC;
   TileGeom g16, g4;
-  bool skip;
+  bool skip, skip_c;
 };
 
 static bool is_permutation(const BandCuAffine& m) {
@@ -453,13 +471,20 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   // per-sample luma staging pays once the down-scale along the axis that maps to source rows reaches 2
   const char* ns = getenv("BANDCU_TILE_NO_SKIP");
   const bool skip = !(ns && ns[0] == '1') && (d.luma_map.rr != 0 ? d.dy : d.dx) >= 0x20000;
-  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter, skip), g4 = tile_geometry<4>(d, TR, TC, inter, skip);
+  // chroma too once the ratio reaches 6 (below that nearly every half-resolution row is sampled and the per-slot row
+  // arithmetic costs more than it saves: measured at 4.8), if chroma rows follow the same virtual axis as luma rows (they do for every
+  // chain the plan compiler emits; checked, not assumed)
+  const bool luma_rows_from_vrows = d.luma_map.rr != 0;
+  const bool chroma_rows_from_vrows = d.pre_map.rr != 0 ? d.chroma_map.rr != 0 : d.chroma_map.rc != 0;
+  const bool skip_c = skip && luma_rows_from_vrows == chroma_rows_from_vrows && (luma_rows_from_vrows ? d.dy : d.dx) >= 0x60000;
+  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter, skip, skip_c), g4 = tile_geometry<4>(d, TR, TC, inter, skip, skip_c);
   if (g16.stage_bytes + 2048 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
   p->TR = TR; p->TC = TC;
   p->g16 = g16; p->g4 = g4;
   p->skip = skip;
+  p->skip_c = skip_c;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
@@ -533,6 +558,9 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   // separable address forms (signed permutations: each mapped coordinate depends on one virtual coordinate)
   const int ps = d.pixel_stride_uv;
   P.skip = p->skip ? 1 : 0;
+  P.skip_c = p->skip_c ? 1 : 0;
+  P.c_row_0 = d.chroma_map.r0;
+  P.c_row_mul = d.chroma_map.rr != 0 ? d.chroma_map.rr : d.chroma_map.rc;
   P.l_row_0 = d.luma_map.r0;
   P.l_row_mul = d.luma_map.rr != 0 ? d.luma_map.rr : d.luma_map.rc;
   P.lr_mul = d.luma_map.rr * g.l_pitch + d.luma_map.cr;

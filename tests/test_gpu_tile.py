@@ -159,3 +159,14 @@ def test_crop_folds_into_the_row_staged_kernel(O, fmt_name, order, box):
         del os.environ["BANDCU_DISABLE_FAST"]
     assert st == 0
     assert_same_bits(got, want, "%s %s without the row-staged kernel" % (order, box))
+
+
+@pytest.mark.parametrize("fmt_name", ["NV12", "YV21"])
+@pytest.mark.parametrize("pre,dw,dh", [([(2, 90)], 50, 100), ([(3, 1, 1)], 120, 44), ([(2, 270), (0, 8, 16, 327, 591)], 40, 64)])
+def test_large_ratios_stage_chroma_per_sample_too(O, fmt_name, pre, dw, dh):
+    """Ratios of 6 and more along the row-mapped axis: luma AND chroma planes are staged per sample."""
+    W, H = 640, 352
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = list(pre) + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh), NORM]
+    fr = rand_frames(O, 2, W, H, fmt, 606)
+    _run_both(O, ops, fr, W, H, fmt, O.DT_F32, (1, dh, dw, 3), resident=True)
