@@ -139,6 +139,8 @@ int bandcu_plan_destroy(BandCuPlan* plan) {
 
 int bandcu_plan_is_fast(const BandCuPlan* plan) { return plan && plan->fast ? 1 : 0; }
 
+int bandcu_plan_staging_kind(const BandCuPlan* plan) { return !plan ? 0 : plan->fast ? 1 : plan->tile ? 2 : 0; }
+
 int bandcu_plan_set_host_output(BandCuPlan* plan, int on) {
   if (!plan) return fail(BANDCU_E_INVALID, "plan_set_host_output: null plan");
   if (plan->fast) fast_plan_set_bulk_store(plan->fast, on);

@@ -125,7 +125,7 @@ def check(code, what=""):
 
 
 EXPORTED = [
-    "bandcu_plan_create", "bandcu_plan_destroy", "bandcu_plan_is_fast", "bandcu_plan_set_host_output", "bandcu_stream_begin_capture", "bandcu_stream_end_capture",
+    "bandcu_plan_create", "bandcu_plan_destroy", "bandcu_plan_is_fast", "bandcu_plan_set_host_output", "bandcu_plan_staging_kind", "bandcu_stream_begin_capture", "bandcu_stream_end_capture",
     "bandcu_graph_launch", "bandcu_graph_destroy", "bandcu_plan_run_strided", "bandcu_plan_run",
     "bandcu_launch_count", "bandcu_yuv_map", "bandcu_rgb_to_yuv420", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
     "bandcu_malloc", "bandcu_free", "bandcu_host_alloc", "bandcu_host_free", "bandcu_memcpy_h2d", "bandcu_memcpy_d2h",

@@ -143,6 +143,9 @@ BANDCU_API int bandcu_plan_create(const BandCuPlanDesc* desc, BandCuPlan** plan)
 BANDCU_API int bandcu_plan_destroy(BandCuPlan* plan);
 /* 1 if the plan runs on the staged/specialised fast kernel, 0 for the generic one. */
 BANDCU_API int bandcu_plan_is_fast(const BandCuPlan* plan);
+/* 1 if the plan has a staged kernel that reads every needed source byte exactly once, in bulk (row-staged: 1,
+ * tile-staged: 2), so that pinned host frames can be read in place over PCIe; 0 otherwise. */
+BANDCU_API int bandcu_plan_staging_kind(const BandCuPlan* plan);
 /* Output hand-off of the staged kernel. 0 (default): direct global stores (tensors in HBM). 1: the tensors of the
  * following runs live in PINNED HOST memory; rows are assembled in shared memory and leave as cp.async.bulk stores,
  * so results cross PCIe inside the kernel while it pulls the next source rows (no staging buffer, no D2H copy).
