@@ -552,7 +552,9 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   // geometry: rows per item, row groups, ring depth; shrink until the ring fits shared memory
   // rows per work item: 4 for wide sources (1080p: 31 KB per stage), 8 for narrow ones (640 wide: the same stage size,
   // half the barrier traffic; measured +11 % on 640x480 -> 224, -25 % on 1080p)
-  P.R = p->R ? p->R : (P.row_pitch <= 1024 ? 8 : 4);
+  // wide rows with >= 288 output columns: 6 (two resident CTAs still hold >= 20 consumer warps per SM; +4-5 % on 300 and 513 wide
+  // outputs, -3 % on 224 wide ones, which stay at 4)
+  P.R = p->R ? p->R : (P.row_pitch <= 1024 ? 8 : (d.dst_width >= 288 ? 6 : 4));
   P.S = p->S;
   // small batches (the single-frame latency case): fewer rows per item so that every SM gets work
   while (P.R > 1 && (long long)n * ((d.dst_height + P.R - 1) / P.R) < 2LL * p->num_sms) P.R >>= 1;
