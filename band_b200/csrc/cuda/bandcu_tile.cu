@@ -363,41 +363,48 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
     return;
   }
 
-  // SWAP: lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3
+  // SWAP: lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3. The 8-bit results go through
+  // a [32][25]-word shared array (odd pitch: the per-lane row writes and the row-major reads are both conflict-free)
+  // and leave as row-major 16-byte (f32) / 4-byte (u8) pieces: a warp writes 1.3 output rows of the tile per store
+  // instruction. (Storing from the compute layout -- each lane its own output row -- cost 32 L1 wavefronts per store
+  // instruction, a third of the kernel's L1 data-pipe load: profiles/r01_ncu_full_tile_v6.txt.)
+  uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_terms + 2048);
   const int oy = oy0 + lane;
   const int cx0 = wid * 4;
-  if (oy > oy1 || ox0 + cx0 > ox1) return;
-  const RowTerms R = rt[lane];
-  uint32_t px[12];
+  if (oy <= oy1 && ox0 + cx0 <= ox1) {
+    const RowTerms R = rt[lane];
+    uint32_t px[12];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const ColTerms Cn = ct[min(cx0 + j, 31)];
-    uint32_t r, g, b;
-    tile_pixel(gl, gu, gv, R, Cn, r, g, b);
-    px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
-  }
-  uint8_t* o = f.out + (long long)oy * d.dst_row_stride + (size_t)(ox0 + cx0) * (3 * sizeof(OT));
-  const int n_px = min(4, ox1 - (ox0 + cx0) + 1);
-  if (sizeof(OT) == 1) {
-    if (n_px == 4 && P.out_vec) {
-      uint32_t* o4 = reinterpret_cast<uint32_t*>(o);
-#pragma unroll
-      for (int q = 0; q < 3; ++q) o4[q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
-    } else {
-#pragma unroll
-      for (int e = 0; e < 12; ++e)
-        if (e < 3 * n_px) o[e] = (uint8_t)px[e];
+    for (int j = 0; j < 4; ++j) {
+      const ColTerms Cn = ct[min(cx0 + j, 31)];
+      uint32_t r, g, b;
+      tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+      px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
     }
-  } else {
-    float* of = reinterpret_cast<float*>(o);
-    if (n_px == 4 && P.out_vec) {
 #pragma unroll
-      for (int q = 0; q < 3; ++q)
-        reinterpret_cast<float4*>(of)[q] = make_float4(lut[px[4 * q]], lut[px[4 * q + 1]], lut[px[4 * q + 2]], lut[px[4 * q + 3]]);
-    } else {
-#pragma unroll
-      for (int e = 0; e < 12; ++e)
-        if (e < 3 * n_px) of[e] = lut[px[e]];
+    for (int q = 0; q < 3; ++q)
+      os[lane * 25 + wid * 3 + q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
+  }
+  __syncthreads();
+  const int nrows = oy1 - oy0 + 1, ncols = ox1 - ox0 + 1;
+  uint8_t* obase = f.out + (long long)oy0 * d.dst_row_stride + (size_t)ox0 * (3 * sizeof(OT));
+  if (P.out_vec && ncols == 32) {  // 24 aligned pieces per row (ox0 is a multiple of 32)
+    for (int idx = threadIdx.x; idx < nrows * 24; idx += 256) {
+      const int row = idx / 24, q = idx - row * 24;
+      const uint32_t w = os[row * 25 + q];
+      uint8_t* o = obase + (long long)row * d.dst_row_stride;
+      if (sizeof(OT) == 1) reinterpret_cast<uint32_t*>(o)[q] = w;
+      else reinterpret_cast<float4*>(o)[q] = make_float4(lut[w & 0xFF], lut[(w >> 8) & 0xFF], lut[(w >> 16) & 0xFF], lut[w >> 24]);
+    }
+  } else {  // right-edge tiles, unaligned outputs: element by element, still row-major
+    const uint8_t* ob = reinterpret_cast<const uint8_t*>(os);
+    for (int e = threadIdx.x; e < nrows * 96; e += 256) {
+      const int row = e / 96, c = e - row * 96;
+      if (c >= 3 * ncols) continue;
+      const uint32_t v = ob[row * 100 + c];
+      uint8_t* o = obase + (long long)row * d.dst_row_stride;
+      if (sizeof(OT) == 1) o[c] = (uint8_t)v;
+      else reinterpret_cast<float*>(o)[c] = lut[v];
     }
   }
 }
@@ -478,7 +485,7 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   const bool chroma_rows_from_vrows = d.pre_map.rr != 0 ? d.chroma_map.rr != 0 : d.chroma_map.rc != 0;
   const bool skip_c = skip && luma_rows_from_vrows == chroma_rows_from_vrows && (luma_rows_from_vrows ? d.dy : d.dx) >= 0x60000;
   const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter, skip, skip_c), g4 = tile_geometry<4>(d, TR, TC, inter, skip, skip_c);
-  if (g16.stage_bytes + 2048 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
+  if (g16.stage_bytes + 2048 + 3200 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
   p->TR = TR; p->TC = TC;
@@ -575,12 +582,24 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
     P.cc_0 = d.pre_map.r0; P.cc_s = d.pre_map.rc; P.cc_mul = BC;
   }
   const bool swap = d.luma_map.rr == 0;
-  auto shift_for = [](int granules) { int sh = 0; while ((1 << sh) < granules && sh < 5) ++sh; return sh; };
+  // threads per staged row (2^shift): the split of the 256 threads over (rows, granules) that costs a thread the fewest
+  // instructions: passes * (row set-up + trips * copy). Per-sample rows pay ~30 instructions of set-up (the row's
+  // source index), rectangle rows ~6; a copy ~4. C3: 64 sampled luma rows of 11 granules -> 4 threads per row, one pass,
+  // three copies each (was 16 threads per row, four passes).
+  auto shift_for = [](int granules, int rows, int setup) {
+    int best = 0, best_cost = 1 << 30;
+    for (int sh = 0; sh <= 5; ++sh) {
+      const int lpr = 1 << sh, rows_per_pass = 256 >> sh;
+      const int cost = ((rows + rows_per_pass - 1) / rows_per_pass) * (setup + ((granules + lpr - 1) / lpr) * 4);
+      if (cost <= best_cost) { best_cost = cost; best = sh; }  // ties: more threads per row (longer contiguous runs)
+    }
+    return best;
+  };
   const int G = aligned16 ? 16 : 4;
-  P.l_lpr_shift = shift_for(g.l_pitch / G);
-  P.c_lpr_shift = shift_for(g.c_pitch / G);
+  P.l_lpr_shift = shift_for(g.l_pitch / G, g.l_rows, p->skip ? 30 : 6);
+  P.c_lpr_shift = shift_for(g.c_pitch / G, g.c_rows, p->skip_c ? 30 : 6);
   P.off_terms = (int)g.stage_bytes;
-  const size_t smem = g.stage_bytes + 2048;  // + row / column term tables
+  const size_t smem = g.stage_bytes + 2048 + 3200;  // + row / column term tables + the [32][25]-word output tile
   {
     const int need = d.normalize ? 15 : 3;
     bool ok;
