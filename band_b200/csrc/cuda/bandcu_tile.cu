@@ -344,46 +344,42 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   const uint8_t* gu = su + AC;
   const uint8_t* gv = sv + AC;
 
+  // The 8-bit results of the tile go through a [32][25]-word shared array (odd pitch: the compute layout's writes and
+  // the row-major reads are both conflict-free) and leave as row-major 16-byte (f32) / 4-byte (u8) pieces: a warp
+  // writes 1.3 output rows of the tile per store instruction. (Storing from the quarter-turn compute layout -- each
+  // lane its own output row -- cost 32 L1 wavefronts per store instruction, a third of the kernel's L1 data-pipe
+  // load: profiles/r01_ncu_full_tile_v6.txt.)
+  uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_terms + 2048);
   if (!SWAP) {
-    const int ox = ox0 + lane;  // TC == 32
-    if (ox > ox1) return;
-    const ColTerms Cn = ct[lane];
-    uint8_t* o = f.out + (long long)(oy0 + wid) * d.dst_row_stride + (size_t)ox * (3 * sizeof(OT));
-    for (int ry = wid; oy0 + ry <= oy1; ry += 8, o += 8 * d.dst_row_stride) {
-      const RowTerms R = rt[ry];
-      uint32_t r, g, b;
-      tile_pixel(gl, gu, gv, R, Cn, r, g, b);
-      if (sizeof(OT) == 1) {
-        o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(g >> 23); o[2] = (uint8_t)(b >> 23);
-      } else {
-        float* of = reinterpret_cast<float*>(o);
-        of[0] = lut[(r >> 23) & 0xFF]; of[1] = lut[(g >> 23) & 0xFF]; of[2] = lut[(b >> 23) & 0xFF];
+    // lane = output column inside the tile (TC == 32); warp w owns rows w, w+8, ...
+    if (ox0 + lane <= ox1) {
+      const ColTerms Cn = ct[lane];
+      uint8_t* ob = reinterpret_cast<uint8_t*>(os) + lane * 3;
+      for (int ry = wid; oy0 + ry <= oy1; ry += 8) {
+        const RowTerms R = rt[ry];
+        uint32_t r, g, b;
+        tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+        ob[ry * 100] = (uint8_t)(r >> 23); ob[ry * 100 + 1] = (uint8_t)(g >> 23); ob[ry * 100 + 2] = (uint8_t)(b >> 23);
       }
     }
-    return;
-  }
-
-  // SWAP: lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3. The 8-bit results go through
-  // a [32][25]-word shared array (odd pitch: the per-lane row writes and the row-major reads are both conflict-free)
-  // and leave as row-major 16-byte (f32) / 4-byte (u8) pieces: a warp writes 1.3 output rows of the tile per store
-  // instruction. (Storing from the compute layout -- each lane its own output row -- cost 32 L1 wavefronts per store
-  // instruction, a third of the kernel's L1 data-pipe load: profiles/r01_ncu_full_tile_v6.txt.)
-  uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_terms + 2048);
-  const int oy = oy0 + lane;
-  const int cx0 = wid * 4;
-  if (oy <= oy1 && ox0 + cx0 <= ox1) {
-    const RowTerms R = rt[lane];
-    uint32_t px[12];
+  } else {
+    // lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3
+    const int oy = oy0 + lane;
+    const int cx0 = wid * 4;
+    if (oy <= oy1 && ox0 + cx0 <= ox1) {
+      const RowTerms R = rt[lane];
+      uint32_t px[12];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const ColTerms Cn = ct[min(cx0 + j, 31)];
-      uint32_t r, g, b;
-      tile_pixel(gl, gu, gv, R, Cn, r, g, b);
-      px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
+      for (int j = 0; j < 4; ++j) {
+        const ColTerms Cn = ct[min(cx0 + j, 31)];
+        uint32_t r, g, b;
+        tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+        px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
+      }
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        os[lane * 25 + wid * 3 + q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
     }
-#pragma unroll
-    for (int q = 0; q < 3; ++q)
-      os[lane * 25 + wid * 3 + q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
   }
   __syncthreads();
   const int nrows = oy1 - oy0 + 1, ncols = ox1 - ox0 + 1;

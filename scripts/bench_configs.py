@@ -285,6 +285,8 @@ def main():
                                pre_ops=[(B.BAND_ROTATE, 90)], pre_ops_o=[(O.OP_ROTATE, 90)]))
         out.append(tensor_case("x_1080p_yv12_rot270_to_300_u8", 1920, 1080, "YV12", 300, 300, False, 1024, a.steps, a.cpu,
                                pre_ops=[(B.BAND_ROTATE, 270)], pre_ops_o=[(O.OP_ROTATE, 270)]))
+        out.append(tensor_case("x_1080p_nv21_rot180_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
+                               pre_ops=[(B.BAND_ROTATE, 180)], pre_ops_o=[(O.OP_ROTATE, 180)]))
     if "c5" in want:
         pairs = [tuple(int(v) for v in p.split(":")) for p in a.c5_pairs.split(",") if p] or None
         out += c5_cases(a.steps, a.cpu, pairs)
