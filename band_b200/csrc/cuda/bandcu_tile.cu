@@ -19,15 +19,25 @@
 // integers per plane: address = A + B*r + C*c.
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "bandcu_device.cuh"
 #include "bandcu_internal.h"
 
 namespace bandcu {
 
+// Source rectangles of one output tile (the same for every frame of a plan): computed once on the host at plan creation
+// instead of by every CTA (three affine bounding boxes: ~170 of the ~1060 instructions a warp spent per tile).
+struct __align__(16) TileEntry {
+  int l_r0, l_rows, l_first;  // luma: first source row, rows, first source byte of a row
+  int c_r0, c_rows, c_first;  // chroma plane(s): the same, in plane bytes
+  int pad[2];
+};
+
 struct TileParams {
   BandCuPlanDesc d;
   BatchArgs batch;
+  const TileEntry* geom;  // [tiles_y][tiles_x]
   int TR, TC;          // output rows / columns per tile
   int tiles_x, tiles_y;
   int interleaved;     // 1: semi-planar chroma (one staged plane, U/V one byte apart)
@@ -284,12 +294,10 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   const int oy1 = min(oy0 + P.TR, d.dst_height) - 1, ox1 = min(ox0 + P.TC, d.dst_width) - 1;
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
 
-  const Rect v = virtual_rect(d, oy0, oy1, ox0, ox1);
-  Rect L, C;
-  tile_rects(d, v, &L, &C);
+  const TileEntry te = P.geom[blockIdx.y * P.tiles_x + blockIdx.x];
   const int ps = d.pixel_stride_uv;
-  const int l_first = L.c0, c_first = C.c0 * ps;
-  const int l_rows = L.r1 - L.r0 + 1, c_rows = C.r1 - C.r0 + 1;
+  const int l_first = te.l_first, c_first = te.c_first;
+  const int l_rows = te.l_rows, c_rows = te.c_rows;
   const int c_row_bytes = ((d.src_width + 1) >> 1) * ps;  // bytes of one chroma plane row
   uint8_t* sl = smem;
   uint8_t* su = sl + P.l_rows_max * P.l_pitch;
@@ -303,7 +311,7 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
       return P.l_row_0 + P.l_row_mul * ((slot & 1) ? b : a);
     });
   } else {
-    stage_plane<G>(sl, f.p0, d.stride0, L.r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
+    stage_plane<G>(sl, f.p0, d.stride0, te.l_r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
   }
   const int npos_c = SWAP ? (ox1 - ox0 + 1) : (oy1 - oy0 + 1);
   auto chroma_row_of = [&](int slot) {
@@ -314,7 +322,7 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   };
   auto stage_chroma = [&](uint8_t* dst, const uint8_t* plane) {
     if (P.skip_c) stage_rows<G>(dst, plane, d.stride_uv, 2 * npos_c, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes, chroma_row_of);
-    else stage_plane<G>(dst, plane, d.stride_uv, C.r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
+    else stage_plane<G>(dst, plane, d.stride_uv, te.c_r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
   };
   if (P.interleaved) {
     stage_chroma(su, P.v_first ? f.pv : f.pu);
@@ -338,8 +346,8 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   __syncthreads();
 
   // tile-dependent constants of the two affine address forms
-  const int AL = (P.skip ? 0 : (d.luma_map.r0 - L.r0) * P.l_pitch) + d.luma_map.c0 - (l_first / G) * G;
-  const int AC = (P.skip_c ? 0 : (d.chroma_map.r0 - C.r0) * P.c_pitch) + d.chroma_map.c0 * ps - (c_first / G) * G;
+  const int AL = (P.skip ? 0 : (d.luma_map.r0 - te.l_r0) * P.l_pitch) + d.luma_map.c0 - (l_first / G) * G;
+  const int AC = (P.skip_c ? 0 : (d.chroma_map.r0 - te.c_r0) * P.c_pitch) + d.chroma_map.c0 * ps - (c_first / G) * G;
   const uint8_t* gl = sl + AL;
   const uint8_t* gu = su + AC;
   const uint8_t* gv = sv + AC;
@@ -443,6 +451,7 @@ static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool inte
 
 struct TilePlan {
   float* lut_dev;
+  TileEntry* geom_dev;
   int TR, TC;
   TileGeom g16, g4;
   bool skip, skip_c;
@@ -484,17 +493,38 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   if (g16.stage_bytes + 2048 + 3200 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
+  p->geom_dev = nullptr;
+  {
+    const int tiles_x = (d.dst_width + TC - 1) / TC, tiles_y = (d.dst_height + TR - 1) / TR;
+    std::vector<TileEntry> geom((size_t)tiles_x * tiles_y);
+    for (int ty = 0; ty < tiles_y; ++ty) {
+      for (int tx = 0; tx < tiles_x; ++tx) {
+        const int oy0 = ty * TR, ox0 = tx * TC;
+        const int oy1 = (oy0 + TR < d.dst_height ? oy0 + TR : d.dst_height) - 1;
+        const int ox1 = (ox0 + TC < d.dst_width ? ox0 + TC : d.dst_width) - 1;
+        Rect L, C;
+        tile_rects(d, virtual_rect(d, oy0, oy1, ox0, ox1), &L, &C);
+        TileEntry& e = geom[(size_t)ty * tiles_x + tx];
+        memset(&e, 0, sizeof(e));
+        e.l_r0 = L.r0; e.l_rows = L.r1 - L.r0 + 1; e.l_first = L.c0;
+        e.c_r0 = C.r0; e.c_rows = C.r1 - C.r0 + 1; e.c_first = C.c0 * d.pixel_stride_uv;
+      }
+    }
+    cudaError_t e = cudaMalloc((void**)&p->geom_dev, geom.size() * sizeof(TileEntry));
+    if (e == cudaSuccess) e = cudaMemcpy(p->geom_dev, geom.data(), geom.size() * sizeof(TileEntry), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { if (p->geom_dev) cudaFree(p->geom_dev); delete p; return (int)e; }
+  }
   p->TR = TR; p->TC = TC;
   p->g16 = g16; p->g4 = g4;
   p->skip = skip;
   p->skip_c = skip_c;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
-    if (e != cudaSuccess) { delete p; return (int)e; }
+    if (e != cudaSuccess) { cudaFree(p->geom_dev); delete p; return (int)e; }
     tile_build_lut_kernel<<<1, 256>>>(p->lut_dev, d.mean, d.std_);
     count_launch();
     e = cudaDeviceSynchronize();
-    if (e != cudaSuccess) { cudaFree(p->lut_dev); delete p; return (int)e; }
+    if (e != cudaSuccess) { cudaFree(p->lut_dev); cudaFree(p->geom_dev); delete p; return (int)e; }
   }
   *out = p;
   return BANDCU_OK;
@@ -503,6 +533,7 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
 void tile_plan_destroy(TilePlan* p) {
   if (!p) return;
   if (p->lut_dev) (void)cudaFree(p->lut_dev);
+  if (p->geom_dev) (void)cudaFree(p->geom_dev);
   delete p;
 }
 
@@ -523,6 +554,7 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.tiles_x = (d.dst_width + P.TC - 1) / P.TC;
   P.tiles_y = (d.dst_height + P.TR - 1) / P.TR;
   P.lut = p->lut_dev;
+  P.geom = p->geom_dev;
   bool aligned4, aligned16 = (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0) && (d.src_width % 16 == 0) &&
                              ((((d.src_width + 1) / 2) * d.pixel_stride_uv) % 16 == 0);
   if (d.pixel_stride_uv == 2) {
