@@ -177,8 +177,7 @@ __device__ __forceinline__ void stage_plane(uint8_t* smem_dst, const uint8_t* __
 struct TChroma {
   uint32_t kr, kg, kb;
 };
-__device__ __forceinline__ TChroma t_chroma_pair(uint32_t uL, uint32_t vL, uint32_t uR, uint32_t vR) {
-  const uint32_t u2 = uL | (uR << 16), v2 = vL | (vR << 16);
+__device__ __forceinline__ TChroma t_chroma_terms(uint32_t u2, uint32_t v2) {
   TChroma c;
   c.kr = __vadd2(v2 * 102u, 0xC878C878u /* -14216 */);
   const uint32_t t = u2 * 25u + v2 * 52u;
@@ -256,18 +255,30 @@ __device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i
   t.kB = slot_pitch_c ? (2 * i + 1) * slot_pitch_c : P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
   return t;
 }
+// Chroma of the LEFT|RIGHT sample pair at byte offsets oL, oR. Planar: four byte loads. Interleaved (IL): the staged
+// plane holds (first, second) byte pairs at even offsets -- one 16-bit load per sample, and two PRMTs (selectors sel_u,
+// sel_v pick U and V for NV12 or NV21) build the packed lanes.
+template <bool IL>
+__device__ __forceinline__ TChroma t_chroma_at(const uint8_t* su, const uint8_t* sv, int oL, int oR, uint32_t sel_u,
+                                               uint32_t sel_v) {
+  if (IL) {
+    const uint32_t wL = *reinterpret_cast<const uint16_t*>(su + oL), wR = *reinterpret_cast<const uint16_t*>(su + oR);
+    return t_chroma_terms(__byte_perm(wL, wR, sel_u), __byte_perm(wL, wR, sel_v));
+  }
+  return t_chroma_terms(su[oL] | ((uint32_t)su[oR] << 16), sv[oL] | ((uint32_t)sv[oR] << 16));
+}
 // One output pixel from the staged planes: raw products, the 8-bit results sit in bits 23..30.
-__device__ __forceinline__ void tile_pixel(const uint8_t* sl, const uint8_t* su, const uint8_t* sv, const RowTerms& R,
-                                           const ColTerms& Cn, uint32_t& r, uint32_t& g, uint32_t& b) {
+template <bool IL>
+__device__ __forceinline__ void tile_pixel(const uint8_t* sl, const uint8_t* su, const uint8_t* sv, uint32_t sel_u,
+                                           uint32_t sel_v, const RowTerms& R, const ColTerms& Cn, uint32_t& r, uint32_t& g,
+                                           uint32_t& b) {
   uint32_t tr, tg, tb, br, bg, bb;
   {
-    const int oL = R.kA + Cn.kA, oR = R.kA + Cn.kB;
-    const TChroma ct = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
+    const TChroma ct = t_chroma_at<IL>(su, sv, R.kA + Cn.kA, R.kA + Cn.kB, sel_u, sel_v);
     t_luma_pair_to_rgb(sl[R.lA + Cn.lA], sl[R.lA + Cn.lB], ct, tr, tg, tb);
   }
   if (R.w1) {
-    const int oL = R.kB + Cn.kA, oR = R.kB + Cn.kB;
-    const TChroma cb = t_chroma_pair(su[oL], sv[oL], su[oR], sv[oR]);
+    const TChroma cb = t_chroma_at<IL>(su, sv, R.kB + Cn.kA, R.kB + Cn.kB, sel_u, sel_v);
     t_luma_pair_to_rgb(sl[R.lB + Cn.lA], sl[R.lB + Cn.lB], cb, br, bg, bb);
   } else {
     br = tr; bg = tg; bb = tb;
@@ -284,7 +295,7 @@ __device__ __forceinline__ void tile_pixel(const uint8_t* sl, const uint8_t* su,
 // warp stores 384 contiguous bytes per row.
 // The row and column terms of the tile (32 + 32 entries) are computed once by two warps while the cp.async copies
 // are in flight and read back as broadcasts.
-template <typename OT, int G, bool SWAP>
+template <typename OT, int G, bool SWAP, bool IL>
 __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __grid_constant__ TileParams P) {
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ float lut[256];
@@ -324,10 +335,11 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
     if (P.skip_c) stage_rows<G>(dst, plane, d.stride_uv, 2 * npos_c, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes, chroma_row_of);
     else stage_plane<G>(dst, plane, d.stride_uv, te.c_r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
   };
-  if (P.interleaved) {
+  // IL: su stays the base of the (first, second) byte pairs; byte 2 of a zero-extended 16-bit load is the zero lane filler
+  const uint32_t sel_u = P.v_first ? 0x2521u : 0x2420u, sel_v = P.v_first ? 0x2420u : 0x2521u;
+  if (IL) {
     stage_chroma(su, P.v_first ? f.pv : f.pu);
-    sv = su + (P.v_first ? 0 : 1);
-    su = su + (P.v_first ? 1 : 0);
+    sv = su;
   } else {
     sv = su + P.c_rows_max * P.c_pitch;
     stage_chroma(su, f.pu);
@@ -366,7 +378,7 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
       for (int ry = wid; oy0 + ry <= oy1; ry += 8) {
         const RowTerms R = rt[ry];
         uint32_t r, g, b;
-        tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+        tile_pixel<IL>(gl, gu, gv, sel_u, sel_v, R, Cn, r, g, b);
         ob[ry * 100] = (uint8_t)(r >> 23); ob[ry * 100 + 1] = (uint8_t)(g >> 23); ob[ry * 100 + 2] = (uint8_t)(b >> 23);
       }
     }
@@ -381,7 +393,7 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
       for (int j = 0; j < 4; ++j) {
         const ColTerms Cn = ct[min(cx0 + j, 31)];
         uint32_t r, g, b;
-        tile_pixel(gl, gu, gv, R, Cn, r, g, b);
+        tile_pixel<IL>(gl, gu, gv, sel_u, sel_v, R, Cn, r, g, b);
         px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
       }
 #pragma unroll
@@ -539,9 +551,13 @@ void tile_plan_destroy(TilePlan* p) {
 
 typedef void (*TileKernel)(const TileParams);
 template <typename OT>
-static TileKernel pick_tile_kernel(bool g16, bool swap) {
-  if (g16) return swap ? tile_yuv_bilinear_down_kernel<OT, 16, true> : tile_yuv_bilinear_down_kernel<OT, 16, false>;
-  return swap ? tile_yuv_bilinear_down_kernel<OT, 4, true> : tile_yuv_bilinear_down_kernel<OT, 4, false>;
+static TileKernel pick_tile_kernel(bool g16, bool swap, bool il) {
+  if (il) {
+    if (g16) return swap ? tile_yuv_bilinear_down_kernel<OT, 16, true, true> : tile_yuv_bilinear_down_kernel<OT, 16, false, true>;
+    return swap ? tile_yuv_bilinear_down_kernel<OT, 4, true, true> : tile_yuv_bilinear_down_kernel<OT, 4, false, true>;
+  }
+  if (g16) return swap ? tile_yuv_bilinear_down_kernel<OT, 16, true, false> : tile_yuv_bilinear_down_kernel<OT, 16, false, false>;
+  return swap ? tile_yuv_bilinear_down_kernel<OT, 4, true, false> : tile_yuv_bilinear_down_kernel<OT, 4, false, false>;
 }
 
 int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
@@ -635,7 +651,7 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
     else ok = (reinterpret_cast<uintptr_t>(batch.first.out) & need) == 0 && (n == 1 || (batch.out_stride & need) == 0);
     P.out_vec = (ok && (d.dst_row_stride & need) == 0) ? 1 : 0;
   }
-  TileKernel kern = d.normalize ? pick_tile_kernel<float>(aligned16, swap) : pick_tile_kernel<uint8_t>(aligned16, swap);
+  TileKernel kern = d.normalize ? pick_tile_kernel<float>(aligned16, swap, P.interleaved != 0) : pick_tile_kernel<uint8_t>(aligned16, swap, P.interleaved != 0);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   for (int done = 0; done < n;) {
