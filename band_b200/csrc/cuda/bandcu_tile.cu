@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   // the row-major reads are both conflict-free) and leave as row-major 16-byte (f32) / 4-byte (u8) pieces: a warp
   // writes 1.3 output rows of the tile per store instruction. (Storing from the quarter-turn compute layout -- each
   // lane its own output row -- cost 32 L1 wavefronts per store instruction, a third of the kernel's L1 data-pipe
-  // load: profiles/r01_ncu_full_tile_v6.txt.)
+  // load: profiles/r01_ncu_full_tile_v6_uncoalesced_stores.txt.)
   uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_terms + 2048);
   if (!SWAP) {
     // lane = output column inside the tile (TC == 32); warp w owns rows w, w+8, ...
