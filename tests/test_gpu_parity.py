@@ -81,7 +81,8 @@ def test_c4_nv21_1080p_mixed_targets(O, target):
 
 
 @pytest.mark.parametrize("s,d", [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (64, 128),
-                                 (64, 256), (64, 512), (64, 1024), (64, 2048), (640, 224), (225, 224)])
+                                 (64, 256), (64, 512), (64, 1024), (64, 2048), (640, 224), (225, 224),
+                                 (64, 352), (100, 1200), (480, 1072)])
 def test_c5_rgba_to_rgb_autoconvert(O, s, d):
     """C5 (i): default AutoConvert into a u8 RGB tensor = CSC(drop alpha) -> ResizeRgb, incl. the
     Down2 / DownEven box, point-sample and bilinear-up dispatch cases."""
@@ -95,7 +96,8 @@ def test_c5_rgba_to_rgb_autoconvert(O, s, d):
 
 
 @pytest.mark.parametrize("s,d", [(2048, 64), (2048, 128), (2048, 256), (2048, 512), (2048, 1024), (2048, 1536),
-                                 (2048, 768), (64, 128), (64, 256), (64, 100), (64, 2048), (640, 224)])
+                                 (2048, 768), (64, 128), (64, 256), (64, 100), (64, 2048), (640, 224),
+                                 (64, 1040), (300, 1504)])
 def test_c5_rgba_to_gray_resize(O, s, d):
     """C5 (ii): CSC(Gray) -> Resize through ScalePlane (x86 rounding blender, Down2/Down34/Down38/Up2 cases)."""
     ops = [_csc(O, O.FMT_GRAY), (O.OP_RESIZE, d, d)]
