@@ -172,6 +172,11 @@ static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hin
     if (e == BANDCU_OK) { trace_path("packed", plan, n); return BANDCU_OK; }
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: packed kernel launch");
   }
+  {
+    int e = launch_copy_rows(plan->d, b, hints, n, s);
+    if (e == BANDCU_OK) { trace_path("copy-rows", plan, n); return BANDCU_OK; }
+    if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: copy-rows kernel launch");
+  }
   int e = launch_generic(plan->d, b, n, s);
   if (e != 0) return fail(e, "plan_run: generic kernel launch");
   trace_path("generic", plan, n);

@@ -1,0 +1,272 @@
+// band_b200/csrc/cuda/bandcu_copy.cu
+//
+// Same-size conversions: a ColorSpaceConvert with no Resize behind it (optionally behind a Crop), the most common
+// single call into the reference's image operator (libyuv_image_operator.cc:1709-1727 -> NV12ToRAW / NV21ToRAW /
+// I420ToRAW / ..ToARGB-family :92-300, ARGBToRAW / RAWToJ400 / ARGBToJ400-style packed conversions, and the plain
+// luma copy of YUV -> gray). The pixel-per-thread kernel spends ~240 instructions and six byte-wide memory
+// instructions per output pixel on these (measured: 1080p NV21 -> RGB at 0.77 TB/s, 12 % of the HBM copy rate); here
+// a thread owns FOUR adjacent pixels of TWO rows (one chroma row), reads and writes 32-bit words only, converts pixel
+// pairs in packed 16-bit lanes (the identities of bandcu_fast.cu) and assembles the output words with PRMT.
+//
+// Arithmetic is unchanged (BT.601 6-bit fixed point YuvPixel; RGBToYJ); the parity tests compare with the oracle.
+#include <cstring>
+
+#include "bandcu_device.cuh"
+#include "bandcu_internal.h"
+
+namespace bandcu {
+
+struct CopyParams {
+  BatchArgs batch;
+  int W, H;                 // output (= virtual image) size
+  int stride0, stride_uv;
+  long long luma_off, chroma_off;  // crop origin folded into the plane pointers
+  long long dst_row_stride;
+  int out16;                // output rows are 16-byte aligned (RGBA: one 128-bit store per thread and row)
+};
+
+// ---- packed LEFT|RIGHT pixel pairs: both lanes share one chroma sample ----
+struct CChroma {
+  uint32_t kr, kg, kb;
+};
+__device__ __forceinline__ CChroma c_chroma_terms(uint32_t u, uint32_t v) {
+  const uint32_t u2 = u * 0x00010001u, v2 = v * 0x00010001u;
+  CChroma c;
+  c.kr = __vadd2(v2 * 102u, 0xC878C878u /* -14216 */);
+  const uint32_t t = u2 * 25u + v2 * 52u;
+  c.kg = __vadd2(~t, 0x21F921F9u /* 8696 + 1 */);
+  c.kb = u2 << 7;
+  return c;
+}
+__device__ __forceinline__ void c_luma_pair_to_rgb(uint32_t yL, uint32_t yR, const CChroma& c, uint32_t& R2, uint32_t& G2,
+                                                   uint32_t& B2) {
+  const uint32_t yy = __byte_perm(yL * 4882229u, yR * 4882229u, 0x7632);
+  const uint32_t r = __viaddmin_s16x2_relu(yy, c.kr, 0x3FFF3FFFu);
+  const uint32_t g = __viaddmin_s16x2_relu(yy, c.kg, 0x3FFF3FFFu);
+  uint32_t b = __vmaxu2(__viaddmin_u16x2(yy, c.kb, 0x84878487u), 0x44884488u);
+  b = __vadd2(b, 0xBB78BB78u);
+  R2 = (r >> 6) & 0x00FF00FFu;
+  G2 = (g >> 6) & 0x00FF00FFu;
+  B2 = (b >> 6) & 0x00FF00FFu;
+}
+
+// Four pixels of one row (luma word y4 = Y0 Y1 Y2 Y3) with the chroma of pairs A (px 0,1) and B (px 2,3) -> o[].
+template <int OUTCH>
+__device__ __forceinline__ void c_row4(uint32_t y4, const CChroma& ca, const CChroma& cb, uint32_t (&o)[4]) {
+  uint32_t ra, ga, ba, rb, gb, bb;
+  c_luma_pair_to_rgb(y4 & 0xFF, (y4 >> 8) & 0xFF, ca, ra, ga, ba);
+  c_luma_pair_to_rgb((y4 >> 16) & 0xFF, y4 >> 24, cb, rb, gb, bb);
+  const uint32_t rga = __byte_perm(ra, ga, 0x6240), rgb = __byte_perm(rb, gb, 0x6240);  // R0 G0 R1 G1
+  if (OUTCH == 3) {
+    o[0] = __byte_perm(rga, ba, 0x2410);                             // R0 G0 B0 R1
+    o[1] = __byte_perm(__byte_perm(rga, ba, 0x0063), rgb, 0x5410);   // G1 B1 R2 G2
+    o[2] = __byte_perm(rgb, bb, 0x6324);                             // B2 R3 G3 B3
+  } else {
+    const uint32_t bfa = ba | 0xFF00FF00u, bfb = bb | 0xFF00FF00u;   // B0 FF B1 FF
+    o[0] = __byte_perm(rga, bfa, 0x5410);
+    o[1] = __byte_perm(rga, bfa, 0x7632);
+    o[2] = __byte_perm(rgb, bfb, 0x5410);
+    o[3] = __byte_perm(rgb, bfb, 0x7632);
+  }
+}
+
+enum { kCopyUV = 0, kCopyVU = 1, kCopyPlanar = 2 };
+
+template <int CH, int OUTCH>
+__global__ void __launch_bounds__(256) yuv_copy_rows_kernel(const __grid_constant__ CopyParams P) {
+  const int x = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y = (blockIdx.y * 8 + threadIdx.y) * 2;
+  if (x >= P.W || y >= P.H) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  const uint8_t* yp = f.p0 + P.luma_off + (long long)y * P.stride0 + x;
+  const bool two = y + 1 < P.H;
+  const uint32_t y0 = __ldg(reinterpret_cast<const uint32_t*>(yp));
+  const uint32_t y1 = two ? __ldg(reinterpret_cast<const uint32_t*>(yp + P.stride0)) : y0;
+  const long long coff = P.chroma_off + (long long)(y >> 1) * P.stride_uv;
+  CChroma ca, cb;
+  if (CH == kCopyPlanar) {
+    const uint32_t uu = __ldg(reinterpret_cast<const uint16_t*>(f.pu + coff + (x >> 1)));
+    const uint32_t vv = __ldg(reinterpret_cast<const uint16_t*>(f.pv + coff + (x >> 1)));
+    ca = c_chroma_terms(uu & 0xFF, vv & 0xFF);
+    cb = c_chroma_terms(uu >> 8, vv >> 8);
+  } else {
+    const uint8_t* uv = (CH == kCopyVU ? f.pv : f.pu) + coff + x;  // (first, second) byte pairs
+    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(uv));
+    const uint32_t a0 = w & 0xFF, b0 = (w >> 8) & 0xFF, a1 = (w >> 16) & 0xFF, b1 = w >> 24;
+    ca = CH == kCopyVU ? c_chroma_terms(b0, a0) : c_chroma_terms(a0, b0);
+    cb = CH == kCopyVU ? c_chroma_terms(b1, a1) : c_chroma_terms(a1, b1);
+  }
+  uint8_t* op = f.out + (long long)y * P.dst_row_stride + (size_t)x * OUTCH;
+  uint32_t o[4];
+  c_row4<OUTCH>(y0, ca, cb, o);
+  if (OUTCH == 4 && P.out16) {
+    *reinterpret_cast<uint4*>(op) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < OUTCH; ++k) reinterpret_cast<uint32_t*>(op)[k] = o[k];
+  }
+  if (!two) return;
+  op += P.dst_row_stride;
+  c_row4<OUTCH>(y1, ca, cb, o);
+  if (OUTCH == 4 && P.out16) {
+    *reinterpret_cast<uint4*>(op) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < OUTCH; ++k) reinterpret_cast<uint32_t*>(op)[k] = o[k];
+  }
+}
+
+// Packed sources, four pixels per thread: RGBA -> RGB (drop alpha), RGBA -> gray, RGB -> gray (RGBToYJ), and the
+// luma plane of a 4:2:0 frame -> gray (a strided copy). SRCB / DSTB = bytes per pixel.
+enum { kPkRgbaToRgb = 0, kPkRgbaToGray = 1, kPkRgbToGray = 2, kPkLumaCopy = 3 };
+template <int MODE>
+__global__ void __launch_bounds__(256) packed_copy_rows_kernel(const __grid_constant__ CopyParams P) {
+  const int x = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y = blockIdx.y * 8 + threadIdx.y;
+  if (x >= P.W || y >= P.H) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  constexpr int SRCB = MODE == kPkRgbToGray ? 3 : MODE == kPkLumaCopy ? 1 : 4;
+  constexpr int DSTB = MODE == kPkRgbaToRgb ? 3 : 1;
+  const uint32_t* sp = reinterpret_cast<const uint32_t*>(f.p0 + P.luma_off + (long long)y * P.stride0 + (size_t)x * SRCB);
+  uint32_t* op = reinterpret_cast<uint32_t*>(f.out + (long long)y * P.dst_row_stride + (size_t)x * DSTB);
+  if (MODE == kPkLumaCopy) {
+    op[0] = __ldg(sp);
+  } else if (MODE == kPkRgbToGray) {
+    const uint32_t a = __ldg(sp), b = __ldg(sp + 1), c = __ldg(sp + 2);  // R0G0B0R1 G1B1R2G2 B2R3G3B3
+    const uint32_t g0 = rgb_to_yj(a & 0xFF, (a >> 8) & 0xFF, (a >> 16) & 0xFF);
+    const uint32_t g1 = rgb_to_yj(a >> 24, b & 0xFF, (b >> 8) & 0xFF);
+    const uint32_t g2 = rgb_to_yj((b >> 16) & 0xFF, b >> 24, c & 0xFF);
+    const uint32_t g3 = rgb_to_yj((c >> 8) & 0xFF, (c >> 16) & 0xFF, c >> 24);
+    op[0] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+  } else {
+    uint32_t p[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) p[k] = __ldg(sp + k);
+    if (MODE == kPkRgbaToGray) {
+      uint32_t g[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) g[k] = rgb_to_yj(p[k] & 0xFF, (p[k] >> 8) & 0xFF, (p[k] >> 16) & 0xFF);
+      op[0] = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+    } else {
+      op[0] = __byte_perm(p[0], p[1], 0x4210);  // R0 G0 B0 R1
+      op[1] = __byte_perm(p[1], p[2], 0x5421);  // G1 B1 R2 G2
+      op[2] = __byte_perm(p[2], p[3], 0x6542);  // B2 R3 G3 B3
+    }
+  }
+}
+
+static bool copy_is_translation(const BandCuAffine& m) {
+  return m.rr == 1 && m.rc == 0 && m.cr == 0 && m.cc == 1 && m.r0 >= 0 && m.c0 >= 0;
+}
+
+typedef void (*CopyKernel)(const CopyParams);
+
+// BANDCU_E_UNSUPPORTED: not a same-size conversion this file covers, or the batch is not word-aligned.
+int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream) {
+  static const bool off = getenv("BANDCU_DISABLE_COPY_ROWS") && getenv("BANDCU_DISABLE_COPY_ROWS")[0] == '1';
+  if (off) return BANDCU_E_UNSUPPORTED;
+  if (d.scale_mode != BANDCU_SCALE_COPY || d.normalize) return BANDCU_E_UNSUPPORTED;
+  if (d.dst_width != d.vw || d.dst_height != d.vh || (d.vw & 3)) return BANDCU_E_UNSUPPORTED;
+  if (!copy_is_translation(d.luma_map) || !copy_is_translation(d.pre_map) || !copy_is_translation(d.chroma_map))
+    return BANDCU_E_UNSUPPORTED;
+  CopyParams P;
+  memset(&P, 0, sizeof(P));
+  P.batch = batch;
+  P.W = d.vw; P.H = d.vh;
+  P.stride0 = d.stride0; P.stride_uv = d.stride_uv;
+  P.dst_row_stride = d.dst_row_stride;
+  CopyKernel kern = nullptr;
+  int src_bpp = 1, rows_per_thread = 1;
+  bool need_chroma = false;
+  if (d.src_kind == BANDCU_SRC_YUV420 && (d.cvt == BANDCU_CVT_YUV2RGB || d.cvt == BANDCU_CVT_YUV2RGBA)) {
+    if ((d.pre_map.r0 & 1) || (d.pre_map.c0 & 1)) return BANDCU_E_UNSUPPORTED;
+    // a pixel pair (2k, 2k+1) and a row pair must share their chroma sample: even luma origin inside the converted image
+    // (a crop BEFORE the conversion re-bases chroma at origin/2, so any origin keeps the pairing)
+    if (d.pixel_stride_uv != 1 && d.pixel_stride_uv != 2) return BANDCU_E_UNSUPPORTED;
+    need_chroma = true;
+    rows_per_thread = 2;
+  } else if (d.src_kind == BANDCU_SRC_YUV420 && d.cvt == BANDCU_CVT_YUV2GRAY) {
+    kern = packed_copy_rows_kernel<kPkLumaCopy>;
+  } else if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2RGB) {
+    kern = packed_copy_rows_kernel<kPkRgbaToRgb>; src_bpp = 4;
+  } else if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2GRAY) {
+    kern = packed_copy_rows_kernel<kPkRgbaToGray>; src_bpp = 4;
+  } else if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_RGB2GRAY) {
+    kern = packed_copy_rows_kernel<kPkRgbToGray>; src_bpp = 3;
+  } else {
+    return BANDCU_E_UNSUPPORTED;
+  }
+  P.luma_off = (long long)d.luma_map.r0 * d.stride0 + (long long)d.luma_map.c0 * src_bpp;
+  P.chroma_off = (long long)(d.chroma_map.r0 + d.pre_map.r0 / 2) * d.stride_uv +
+                 (long long)(d.chroma_map.c0 + d.pre_map.c0 / 2) * d.pixel_stride_uv;
+  // 32-bit accesses everywhere: plane pointers, strides, crop offsets and outputs must be word aligned
+  if ((d.stride0 & 3) || (P.luma_off & 3) || (d.dst_row_stride & 3)) return BANDCU_E_UNSUPPORTED;
+  bool in4, out4, out16;
+  if (batch.table) {
+    if (!hints.valid) return BANDCU_E_UNSUPPORTED;
+    in4 = hints.planes_aligned4;
+    out4 = out16 = hints.out_aligned16;
+  } else {
+    uintptr_t bits = reinterpret_cast<uintptr_t>(batch.first.p0) | (n == 1 ? 0 : (uintptr_t)batch.in_stride);
+    if (need_chroma) bits |= reinterpret_cast<uintptr_t>(batch.first.pu) | reinterpret_cast<uintptr_t>(batch.first.pv);
+    const uintptr_t obits = reinterpret_cast<uintptr_t>(batch.first.out) | (n == 1 ? 0 : (uintptr_t)batch.out_stride);
+    in4 = (bits & 3) == 0;
+    out4 = (obits & 3) == 0;
+    out16 = (obits & 15) == 0;
+  }
+  if (need_chroma) {
+    const bool planar = d.pixel_stride_uv == 1;
+    // planar: 16-bit chroma loads at byte offset x/2 (x % 4 == 0); interleaved: 32-bit loads at byte offset x
+    if ((d.stride_uv & (planar ? 1 : 3)) || (P.chroma_off & (planar ? 1 : 3))) return BANDCU_E_UNSUPPORTED;
+    int ch;
+    if (planar) {
+      ch = kCopyPlanar;
+    } else if (batch.table) {
+      if (!hints.semi_planar) return BANDCU_E_UNSUPPORTED;
+      ch = hints.vu ? kCopyVU : kCopyUV;
+    } else if (batch.first.pv == batch.first.pu + 1) {
+      ch = kCopyUV;
+    } else if (batch.first.pu == batch.first.pv + 1) {
+      ch = kCopyVU;
+    } else {
+      return BANDCU_E_UNSUPPORTED;
+    }
+    // interleaved: the pair base (the lower of pu / pv) must be word aligned; the other pointer is odd by construction
+    if (!planar && !batch.table) {
+      const uint8_t* base = ch == kCopyVU ? batch.first.pv : batch.first.pu;
+      in4 = ((reinterpret_cast<uintptr_t>(batch.first.p0) | reinterpret_cast<uintptr_t>(base) |
+              (n == 1 ? 0 : (uintptr_t)batch.in_stride)) & 3) == 0;
+    } else if (!planar) {
+      in4 = hints.aligned16;
+    }
+    const bool rgba = d.cvt == BANDCU_CVT_YUV2RGBA;
+    if (ch == kCopyUV) kern = rgba ? yuv_copy_rows_kernel<kCopyUV, 4> : yuv_copy_rows_kernel<kCopyUV, 3>;
+    else if (ch == kCopyVU) kern = rgba ? yuv_copy_rows_kernel<kCopyVU, 4> : yuv_copy_rows_kernel<kCopyVU, 3>;
+    else kern = rgba ? yuv_copy_rows_kernel<kCopyPlanar, 4> : yuv_copy_rows_kernel<kCopyPlanar, 3>;
+  }
+  if (!in4 || !out4) return BANDCU_E_UNSUPPORTED;
+  P.out16 = (out16 && (d.dst_row_stride & 15) == 0) ? 1 : 0;
+  const dim3 block(32, 8, 1);
+  const int rows = (d.vh + rows_per_thread - 1) / rows_per_thread;
+  dim3 grid((d.vw / 4 + 31) / 32, (rows + 7) / 8, 1);
+  for (int done = 0; done < n;) {
+    const int chunk = n - done > 65535 ? 65535 : n - done;
+    CopyParams Q = P;
+    if (Q.batch.table) {
+      Q.batch.table += done;
+    } else {
+      const long long o = (long long)done * Q.batch.in_stride;
+      Q.batch.first.p0 += o;
+      if (Q.batch.first.pu) Q.batch.first.pu += o;
+      if (Q.batch.first.pv) Q.batch.first.pv += o;
+      Q.batch.first.out += (long long)done * Q.batch.out_stride;
+    }
+    grid.z = chunk;
+    kern<<<grid, block, 0, stream>>>(Q);
+    count_launch();
+    done += chunk;
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace bandcu

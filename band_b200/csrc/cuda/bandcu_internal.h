@@ -50,4 +50,7 @@ int packed_plan_create(const BandCuPlanDesc& d, PackedPlan** out);
 void packed_plan_destroy(PackedPlan* p);
 int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n,
                   cudaStream_t stream);
+// Same-size conversions (ColorSpaceConvert without a Resize, optionally behind a Crop): four pixels per thread, 32-bit
+// accesses (bandcu_copy.cu). BANDCU_E_UNSUPPORTED: another chain, or a batch that is not word aligned.
+int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream);
 }  // namespace bandcu

@@ -242,6 +242,41 @@ def c5_cases(steps, cpu, pairs=None):
     return lines
 
 
+def image_case(name, ops, W, H, fmt, out_fmt, ow, oh, n, steps):
+    """Single-operator image -> image chains (the rows of SURVEY 8a that do not end in a tensor)."""
+    ib = ImageBatch(ops, n, W, H, fmt, out_fmt, ow, oh)
+    rng = np.random.default_rng(11)
+    uniq = rng.integers(0, 256, size=(2, ib.fb), dtype=np.uint8)
+    ib.fill(uniq)
+    ib.step(False)
+    ms, launches = time_steps(ib.step, ib.proc.synchronize, lambda: ib.proc.stream, steps)
+    alg = ib.fb + ib.ob
+    fps = n / (ms * 1e-3)
+    ib.close()
+    return {"case": name, "frames_per_s": fps, "ms_per_step": ms, "frames_per_step": n, "launches_per_step": launches,
+            "alg_bytes_per_frame": alg, "achieved_GBps": fps * alg / 1e9, "frac_of_measured_hbm": fps * alg / 1e9 / peak()}
+
+
+def g_cases(steps):
+    W, H, n = 1920, 1080, 256
+    csc = B.BAND_COLOR_SPACE_CONVERT
+    return [
+        image_case("g_1080p_nv21_to_rgb", [(csc, B.kBandRGB)], W, H, B.kBandNV21, B.kBandRGB, W, H, n, steps),
+        image_case("g_1080p_nv21_to_rgba", [(csc, B.kBandRGBA)], W, H, B.kBandNV21, B.kBandRGBA, W, H, n, steps),
+        image_case("g_1080p_yv12_to_rgb", [(csc, B.kBandRGB)], W, H, B.kBandYV12, B.kBandRGB, W, H, n, steps),
+        image_case("g_1080p_nv21_to_gray", [(csc, B.kBandGrayScale)], W, H, B.kBandNV21, B.kBandGrayScale, W, H, n, steps),
+        image_case("g_1080p_rgb_to_gray", [(csc, B.kBandGrayScale)], W, H, B.kBandRGB, B.kBandGrayScale, W, H, n, steps),
+        image_case("g_1080p_rgba_to_nv21", [(csc, B.kBandNV21)], W, H, B.kBandRGBA, B.kBandNV21, W, H, n, steps),
+        image_case("g_1080p_nv21_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandNV21, B.kBandNV21, H, W, n, steps),
+        image_case("g_1080p_rgb_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandRGB, B.kBandRGB, H, W, n, steps),
+        image_case("g_1080p_nv21_flip_h", [(B.BAND_FLIP, 1, 0)], W, H, B.kBandNV21, B.kBandNV21, W, H, n, steps),
+        image_case("g_1080p_nv21_crop_center_720p", [(B.BAND_CROP, 320, 180, 1599, 899)], W, H, B.kBandNV21, B.kBandNV21,
+                   1280, 720, n, steps),
+        image_case("g_1080p_nv21_resize_640x360", [(B.BAND_RESIZE, 640, 360)], W, H, B.kBandNV21, B.kBandNV21, 640, 360, n, steps),
+        image_case("g_1080p_rgb_resize_640x360", [(B.BAND_RESIZE, 640, 360)], W, H, B.kBandRGB, B.kBandRGB, 640, 360, n, steps),
+    ]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x")
@@ -287,6 +322,8 @@ def main():
                                pre_ops=[(B.BAND_ROTATE, 270)], pre_ops_o=[(O.OP_ROTATE, 270)]))
         out.append(tensor_case("x_1080p_nv21_rot180_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
                                pre_ops=[(B.BAND_ROTATE, 180)], pre_ops_o=[(O.OP_ROTATE, 180)]))
+    if "g" in want:  # single-operator image -> image chains
+        out += g_cases(a.steps)
     if "c5" in want:
         pairs = [tuple(int(v) for v in p.split(":")) for p in a.c5_pairs.split(",") if p] or None
         out += c5_cases(a.steps, a.cpu, pairs)
