@@ -760,18 +760,41 @@ absl::Status FusedPlan::RunSegments(int first, int last) {
         break;
       }
       case Segment::Kind::kYuvMap: {
-        for (int f = first; f < last; ++f) {
+        // frames whose planes all advance by one stride per frame (batches carved from one allocation, the scratch
+        // images) go out as one launch
+        for (int f = first; f < last;) {
           const SlotPointers s = Resolve(seg.src_slot, f), d = Resolve(seg.dst_slot, f);
+          long long ss = 0, ds = 0;
+          int g = f + 1;
+          for (; g < last; ++g) {
+            const SlotPointers sg = Resolve(seg.src_slot, g), dg = Resolve(seg.dst_slot, g);
+            if (g == f + 1) { ss = sg.y - s.y; ds = dg.u - d.u; }
+            const long long k = g - f;
+            if (sg.y - s.y != ss * k || sg.u - s.u != ss * k || sg.v - s.v != ss * k || dg.u - d.u != ds * k ||
+                dg.v - d.v != ds * k || (d.y ? dg.y - d.y != ds * k : dg.y != nullptr))
+              break;
+          }
           const BandCuYuvPtrs p = {s.y, s.u, s.v, d.y, d.u, d.v};
-          if (bandcu_yuv_map(&seg.yuv, &p, stream_) != BANDCU_OK) return CudaError("bandcu_yuv_map");
+          if (bandcu_yuv_map_strided(&seg.yuv, &p, ss, ds, g - f, stream_) != BANDCU_OK) return CudaError("bandcu_yuv_map");
+          f = g;
         }
         break;
       }
       case Segment::Kind::kRgbToYuv: {
-        for (int f = first; f < last; ++f) {
+        for (int f = first; f < last;) {
           const SlotPointers s = Resolve(seg.src_slot, f), d = Resolve(seg.dst_slot, f);
+          long long ss = 0, ds = 0;
+          int g = f + 1;
+          for (; g < last; ++g) {
+            const SlotPointers sg = Resolve(seg.src_slot, g), dg = Resolve(seg.dst_slot, g);
+            if (g == f + 1) { ss = sg.y - s.y; ds = dg.y - d.y; }
+            const long long k = g - f;
+            if (sg.y - s.y != ss * k || dg.y - d.y != ds * k || dg.u - d.u != ds * k || dg.v - d.v != ds * k) break;
+          }
           const BandCuRgbToYuvPtrs p = {s.y, d.y, d.u, d.v};
-          if (bandcu_rgb_to_yuv420(&seg.rgb2yuv, &p, stream_) != BANDCU_OK) return CudaError("bandcu_rgb_to_yuv420");
+          if (bandcu_rgb_to_yuv420_strided(&seg.rgb2yuv, &p, ss, ds, g - f, stream_) != BANDCU_OK)
+            return CudaError("bandcu_rgb_to_yuv420");
+          f = g;
         }
         break;
       }

@@ -298,8 +298,19 @@ int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void
   if (!desc || !ptrs || !ptrs->sy || !ptrs->su || !ptrs->sv || !ptrs->du || !ptrs->dv)
     return fail(BANDCU_E_INVALID, "yuv_map: null argument");
   if (desc->dst_width <= 0 || desc->dst_height <= 0) return fail(BANDCU_E_INVALID, "yuv_map: bad dims");
-  int e = launch_yuv_map(*desc, *ptrs, (cudaStream_t)stream);
+  int e = launch_yuv_map(*desc, *ptrs, 0, 0, 1, (cudaStream_t)stream);
   if (e != 0) return fail(e, "yuv_map: launch");
+  return BANDCU_OK;
+}
+
+int bandcu_yuv_map_strided(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* first, long long src_frame_stride,
+                           long long dst_frame_stride, int n, void* stream) {
+  if (!desc || !first || !first->sy || !first->su || !first->sv || !first->du || !first->dv || n < 0)
+    return fail(BANDCU_E_INVALID, "yuv_map_strided: bad argument");
+  if (desc->dst_width <= 0 || desc->dst_height <= 0) return fail(BANDCU_E_INVALID, "yuv_map_strided: bad dims");
+  if (n == 0) return BANDCU_OK;
+  int e = launch_yuv_map(*desc, *first, src_frame_stride, dst_frame_stride, n, (cudaStream_t)stream);
+  if (e != 0) return fail(e, "yuv_map_strided: launch");
   return BANDCU_OK;
 }
 
@@ -308,8 +319,20 @@ int bandcu_rgb_to_yuv420(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtr
     return fail(BANDCU_E_INVALID, "rgb_to_yuv420: null argument");
   if (desc->width <= 0 || desc->height <= 0 || (desc->src_channels != 3 && desc->src_channels != 4))
     return fail(BANDCU_E_INVALID, "rgb_to_yuv420: bad descriptor");
-  int e = launch_rgb_to_yuv(*desc, *ptrs, (cudaStream_t)stream);
+  int e = launch_rgb_to_yuv(*desc, *ptrs, 0, 0, 1, (cudaStream_t)stream);
   if (e != 0) return fail(e, "rgb_to_yuv420: launch");
+  return BANDCU_OK;
+}
+
+int bandcu_rgb_to_yuv420_strided(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtrs* first, long long src_frame_stride,
+                                 long long dst_frame_stride, int n, void* stream) {
+  if (!desc || !first || !first->src || !first->dy || !first->du || !first->dv || n < 0)
+    return fail(BANDCU_E_INVALID, "rgb_to_yuv420_strided: bad argument");
+  if (desc->width <= 0 || desc->height <= 0 || (desc->src_channels != 3 && desc->src_channels != 4))
+    return fail(BANDCU_E_INVALID, "rgb_to_yuv420_strided: bad descriptor");
+  if (n == 0) return BANDCU_OK;
+  int e = launch_rgb_to_yuv(*desc, *first, src_frame_stride, dst_frame_stride, n, (cudaStream_t)stream);
+  if (e != 0) return fail(e, "rgb_to_yuv420_strided: launch");
   return BANDCU_OK;
 }
 

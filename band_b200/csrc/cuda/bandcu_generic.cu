@@ -310,35 +310,50 @@ int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaS
 // ---------------------------------------------------------------------------
 struct YuvMapParams {
   BandCuYuvMapDesc d;
-  BandCuYuvPtrs p;
+  BandCuYuvPtrs p;                       // frame 0
+  long long src_step, dst_step;          // bytes between consecutive frames (every plane pointer advances by it)
 };
+// blockIdx.z = 2 * frame + plane group (0: luma, 1: chroma)
 __global__ void __launch_bounds__(256) yuv_map_kernel(const __grid_constant__ YuvMapParams P) {
   const BandCuYuvMapDesc& d = P.d;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int r = blockIdx.y * blockDim.y + threadIdx.y;
-  if (blockIdx.z == 0) {
+  const long long so_f = (long long)(blockIdx.z >> 1) * P.src_step, do_f = (long long)(blockIdx.z >> 1) * P.dst_step;
+  if ((blockIdx.z & 1) == 0) {
     if (c >= d.dst_width || r >= d.dst_height || !P.p.dy) return;
     const int sr = map_row(d.luma_map, r, c), sc = map_col(d.luma_map, r, c);
-    ((uint8_t*)P.p.dy)[(long long)r * d.dst_stride_y + c] = ((const uint8_t*)P.p.sy)[(long long)sr * d.src_stride_y + sc];
+    ((uint8_t*)P.p.dy)[do_f + (long long)r * d.dst_stride_y + c] =
+        ((const uint8_t*)P.p.sy)[so_f + (long long)sr * d.src_stride_y + sc];
   } else {
     const int cw = d.chroma_width_override > 0 ? d.chroma_width_override : (d.dst_width + 1) / 2;
     const int chh = (d.dst_height + 1) / 2;
     if (c >= cw || r >= chh) return;
     const int sr = map_row(d.chroma_map, r, c), sc = map_col(d.chroma_map, r, c);
-    const long long so = (long long)sr * d.src_stride_uv + (long long)sc * d.src_pixel_stride_uv;
-    const long long dof = (long long)r * d.dst_stride_uv + (long long)c * d.dst_pixel_stride_uv;
+    const long long so = so_f + (long long)sr * d.src_stride_uv + (long long)sc * d.src_pixel_stride_uv;
+    const long long dof = do_f + (long long)r * d.dst_stride_uv + (long long)c * d.dst_pixel_stride_uv;
     ((uint8_t*)P.p.du)[dof] = ((const uint8_t*)P.p.su)[so];
     ((uint8_t*)P.p.dv)[dof] = ((const uint8_t*)P.p.sv)[so];
   }
 }
-int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream_t stream) {
+int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, long long src_step, long long dst_step, int n,
+                   cudaStream_t stream) {
   YuvMapParams P;
   P.d = d;
-  P.p = p;
+  P.src_step = src_step;
+  P.dst_step = dst_step;
   dim3 block(32, 8, 1);
-  dim3 grid((d.dst_width + 31) / 32, (d.dst_height + 7) / 8, 2);
-  yuv_map_kernel<<<grid, block, 0, stream>>>(P);
-  count_launch();
+  for (int done = 0; done < n;) {  // gridDim.z <= 65535
+    const int chunk = n - done > 32767 ? 32767 : n - done;
+    P.p = p;
+    const long long so = (long long)done * src_step, dof = (long long)done * dst_step;
+    P.p.sy = (const uint8_t*)p.sy + so; P.p.su = (const uint8_t*)p.su + so; P.p.sv = (const uint8_t*)p.sv + so;
+    if (p.dy) P.p.dy = (uint8_t*)p.dy + dof;
+    P.p.du = (uint8_t*)p.du + dof; P.p.dv = (uint8_t*)p.dv + dof;
+    dim3 grid((d.dst_width + 31) / 32, (d.dst_height + 7) / 8, 2 * chunk);
+    yuv_map_kernel<<<grid, block, 0, stream>>>(P);
+    count_launch();
+    done += chunk;
+  }
   return (int)cudaGetLastError();
 }
 
@@ -352,7 +367,8 @@ int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream
 // ---------------------------------------------------------------------------
 struct RgbToYuvParams {
   BandCuRgbToYuvDesc d;
-  BandCuRgbToYuvPtrs p;
+  BandCuRgbToYuvPtrs p;                  // frame 0
+  long long src_step, dst_step;          // bytes between consecutive frames; blockIdx.z = frame
 };
 __global__ void __launch_bounds__(256) rgb_to_yuv420_kernel(const __grid_constant__ RgbToYuvParams P) {
   const BandCuRgbToYuvDesc& d = P.d;
@@ -360,8 +376,9 @@ __global__ void __launch_bounds__(256) rgb_to_yuv420_kernel(const __grid_constan
   const int cy = blockIdx.y * blockDim.y + threadIdx.y;
   const int cw = (d.width + 1) >> 1, chh = (d.height + 1) >> 1;
   if (cx >= cw || cy >= chh) return;
-  const uint8_t* src = (const uint8_t*)P.p.src;
-  uint8_t* dy = (uint8_t*)P.p.dy;
+  const long long do_f = (long long)blockIdx.z * P.dst_step;
+  const uint8_t* src = (const uint8_t*)P.p.src + (long long)blockIdx.z * P.src_step;
+  uint8_t* dy = (uint8_t*)P.p.dy + do_f;
   const int x0 = 2 * cx, y0 = 2 * cy;
   const int x1 = min(x0 + 1, d.width - 1), y1 = min(y0 + 1, d.height - 1);
   int sr = 0, sg = 0, sb = 0;
@@ -376,18 +393,27 @@ __global__ void __launch_bounds__(256) rgb_to_yuv420_kernel(const __grid_constan
     if (fresh) dy[(long long)r * d.dst_stride_y + c] = (uint8_t)((66 * R + 129 * G + 25 * B + 0x1080) >> 8);
   }
   const int ar = (sr + 1) >> 1, ag = (sg + 1) >> 1, ab = (sb + 1) >> 1;
-  const long long o = (long long)cy * d.dst_stride_uv + (long long)cx * d.dst_pixel_stride_uv;
+  const long long o = do_f + (long long)cy * d.dst_stride_uv + (long long)cx * d.dst_pixel_stride_uv;
   ((uint8_t*)P.p.du)[o] = (uint8_t)((56 * ab - 37 * ag - 19 * ar + 0x8080) >> 8);
   ((uint8_t*)P.p.dv)[o] = (uint8_t)((56 * ar - 47 * ag - 9 * ab + 0x8080) >> 8);
 }
-int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, cudaStream_t stream) {
+int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, long long src_step, long long dst_step,
+                      int n, cudaStream_t stream) {
   RgbToYuvParams P;
   P.d = d;
-  P.p = p;
+  P.src_step = src_step;
+  P.dst_step = dst_step;
   dim3 block(32, 8, 1);
-  dim3 grid(((d.width + 1) / 2 + 31) / 32, ((d.height + 1) / 2 + 7) / 8, 1);
-  rgb_to_yuv420_kernel<<<grid, block, 0, stream>>>(P);
-  count_launch();
+  for (int done = 0; done < n;) {
+    const int chunk = n - done > 65535 ? 65535 : n - done;
+    const long long so = (long long)done * src_step, dof = (long long)done * dst_step;
+    P.p.src = (const uint8_t*)p.src + so;
+    P.p.dy = (uint8_t*)p.dy + dof; P.p.du = (uint8_t*)p.du + dof; P.p.dv = (uint8_t*)p.dv + dof;
+    dim3 grid(((d.width + 1) / 2 + 31) / 32, ((d.height + 1) / 2 + 7) / 8, chunk);
+    rgb_to_yuv420_kernel<<<grid, block, 0, stream>>>(P);
+    count_launch();
+    done += chunk;
+  }
   return (int)cudaGetLastError();
 }
 

@@ -10,8 +10,10 @@ struct BatchArgs;
 
 void count_launch();
 int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream);
-int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, cudaStream_t stream);
-int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, cudaStream_t stream);
+int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, long long src_step, long long dst_step, int n,
+                   cudaStream_t stream);
+int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, long long src_step, long long dst_step,
+                      int n, cudaStream_t stream);
 int launch_normalize(const void* in, int in_dtype, void* out, int out_dtype, long long n, float mean, float sd,
                      cudaStream_t stream);
 

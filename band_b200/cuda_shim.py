@@ -93,6 +93,9 @@ def lib():
     L.bandcu_launch_count.restype = ll
     L.bandcu_yuv_map.argtypes = [C.POINTER(YuvMapDesc), C.POINTER(YuvPtrs), vp]
     L.bandcu_rgb_to_yuv420.argtypes = [C.POINTER(RgbToYuvDesc), C.POINTER(RgbToYuvPtrs), vp]
+    L.bandcu_yuv_map_strided.argtypes = [C.POINTER(YuvMapDesc), C.POINTER(YuvPtrs), C.c_longlong, C.c_longlong, C.c_int, vp]
+    L.bandcu_rgb_to_yuv420_strided.argtypes = [C.POINTER(RgbToYuvDesc), C.POINTER(RgbToYuvPtrs), C.c_longlong, C.c_longlong,
+                                               C.c_int, vp]
     L.bandcu_normalize.argtypes = [vp, ci, vp, ci, ll, C.c_float, C.c_float, vp]
     L.bandcu_device_count.argtypes = [C.POINTER(ci)]
     L.bandcu_set_device.argtypes = [ci]
@@ -127,7 +130,7 @@ def check(code, what=""):
 EXPORTED = [
     "bandcu_plan_create", "bandcu_plan_destroy", "bandcu_plan_is_fast", "bandcu_plan_set_host_output", "bandcu_plan_staging_kind", "bandcu_stream_begin_capture", "bandcu_stream_end_capture",
     "bandcu_graph_launch", "bandcu_graph_destroy", "bandcu_plan_run_strided", "bandcu_plan_run",
-    "bandcu_launch_count", "bandcu_yuv_map", "bandcu_rgb_to_yuv420", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
+    "bandcu_launch_count", "bandcu_yuv_map", "bandcu_yuv_map_strided", "bandcu_rgb_to_yuv420", "bandcu_rgb_to_yuv420_strided", "bandcu_normalize", "bandcu_device_count", "bandcu_set_device",
     "bandcu_malloc", "bandcu_free", "bandcu_host_alloc", "bandcu_host_free", "bandcu_memcpy_h2d", "bandcu_memcpy_d2h",
     "bandcu_memcpy_d2d", "bandcu_memset", "bandcu_stream_create", "bandcu_stream_destroy", "bandcu_stream_sync",
     "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",

@@ -175,6 +175,9 @@ typedef struct BandCuYuvPtrs {
   void *dy, *du, *dv;
 } BandCuYuvPtrs;
 BANDCU_API int bandcu_yuv_map(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* ptrs, void* stream);
+/* n frames whose plane pointers all advance by src_frame_stride / dst_frame_stride bytes per frame: one launch. */
+BANDCU_API int bandcu_yuv_map_strided(const BandCuYuvMapDesc* desc, const BandCuYuvPtrs* first, long long src_frame_stride,
+                                      long long dst_frame_stride, int n, void* stream);
 
 /* ---- RGB / RGBA -> 4:2:0 (ColorSpaceConvert to NV12/NV21/YV12/YV21: RAWToI420 :570, ABGRToNV12 :626,
  * ABGRToNV21 :643, ABGRToI420 :661; libyuv's default C rows RGBToY / RGB2xToU / RGB2xToV with the 2x2
@@ -191,6 +194,8 @@ typedef struct BandCuRgbToYuvPtrs {
   void *dy, *du, *dv;
 } BandCuRgbToYuvPtrs;
 BANDCU_API int bandcu_rgb_to_yuv420(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtrs* ptrs, void* stream);
+BANDCU_API int bandcu_rgb_to_yuv420_strided(const BandCuRgbToYuvDesc* desc, const BandCuRgbToYuvPtrs* first,
+                                            long long src_frame_stride, long long dst_frame_stride, int n, void* stream);
 
 /* ---- element-wise Normalize / DataTypeConvert on an arbitrary dtype pair
  * (common_operator.cc:24-65); n elements, contiguous. ----------------------- */
