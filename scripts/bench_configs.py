@@ -279,7 +279,7 @@ def g_cases(steps):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x")
+    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x,g")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--cpu", action="store_true")
     ap.add_argument("--device", type=int, default=0)
