@@ -352,6 +352,10 @@ __global__ void __launch_bounds__(256) yuv_map_kernel(const __grid_constant__ Yu
 // rectangle and stores the word. The staged pitch is odd, so the gather is conflict-free whether consecutive output
 // bytes walk a staged row (crop, flips) or a staged column (quarter-turns). E = bytes per element: 1 for luma and
 // planar chroma, 2 for interleaved chroma pairs (copied as pairs from the lower of the two pointers).
+template <int N>
+struct IntTag {
+  static constexpr int value = N;
+};
 struct PlaneMap {
   const uint8_t* src;
   uint8_t* dst;
@@ -382,8 +386,10 @@ __device__ __forceinline__ void plane_map_tile(const PlaneMap& pl, long long src
   const int pitch = sbytes | 1;
   const uint8_t* src = pl.src + src_off + (long long)sr0 * pl.src_stride + (long long)sc0 * E;
   const int lane = threadIdx.x, wid = threadIdx.y;
-  {  // all of a thread's loads are issued before the first shared-memory store (predicated, fully unrolled)
-    constexpr int NR = E == 1 ? 8 : 4, NB = E == 1 ? 2 : E == 2 ? 2 : E == 3 ? 3 : 4;
+  // all of a thread's loads are issued before its first shared-memory store (predicated, fully unrolled). One-byte
+  // elements stage 32 rows x 64 bytes (straight maps) or 64 rows x 32 bytes (quarter-turns): two shapes, 8 slots each.
+  auto stage_rect = [&](auto nr_tag, auto nb_tag) {
+    constexpr int NR = decltype(nr_tag)::value, NB = decltype(nb_tag)::value;
     uint8_t v[NR * NB];
 #pragma unroll
     for (int i = 0; i < NR; ++i) {
@@ -400,6 +406,12 @@ __device__ __forceinline__ void plane_map_tile(const PlaneMap& pl, long long src
       for (int j = 0; j < NB; ++j)
         if (r < srows && lane + 32 * j < sbytes) stage[r * pitch + lane + 32 * j] = v[i * NB + j];
     }
+  };
+  if (E == 1) {
+    if (pl.m.rr == 0) stage_rect(IntTag<8>(), IntTag<1>());
+    else stage_rect(IntTag<4>(), IntTag<2>());
+  } else {
+    stage_rect(IntTag<4>(), IntTag<(E == 2 ? 2 : E == 3 ? 3 : 4)>());
   }
   __syncthreads();
   // staged offset of output element (r, c): row term + column term (each mapped coordinate depends on one of them)
