@@ -72,47 +72,90 @@ __device__ __forceinline__ void c_row4(uint32_t y4, const CChroma& ca, const CCh
 
 enum { kCopyUV = 0, kCopyVU = 1, kCopyPlanar = 2 };
 
-template <int CH, int OUTCH>
+// The two chroma samples of a four-pixel group: interleaved word `w` = (first, second) x 2, or planar 16-bit halves.
+template <int CH>
+__device__ __forceinline__ void c_group_chroma(uint32_t w, uint32_t uu, uint32_t vv, CChroma& ca, CChroma& cb) {
+  if (CH == kCopyPlanar) {
+    ca = c_chroma_terms(uu & 0xFF, vv & 0xFF);
+    cb = c_chroma_terms((uu >> 8) & 0xFF, (vv >> 8) & 0xFF);
+  } else {
+    const uint32_t a0 = w & 0xFF, b0 = (w >> 8) & 0xFF, a1 = (w >> 16) & 0xFF, b1 = w >> 24;
+    ca = CH == kCopyVU ? c_chroma_terms(b0, a0) : c_chroma_terms(a0, b0);
+    cb = CH == kCopyVU ? c_chroma_terms(b1, a1) : c_chroma_terms(a1, b1);
+  }
+}
+template <int OUTCH>
+__device__ __forceinline__ void c_store4(uint8_t* op, const uint32_t (&o)[4], bool out16) {
+  if (OUTCH == 4 && out16) {
+    *reinterpret_cast<uint4*>(op) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < OUTCH; ++k) reinterpret_cast<uint32_t*>(op)[k] = o[k];
+  }
+}
+
+// NPX = pixels per thread and row: 4 (32-bit accesses) or 8 (64-bit loads, 64/128-bit stores; frames whose planes,
+// strides and outputs are 8-byte aligned -- 16 for RGBA outputs -- and whose width is a multiple of 8).
+template <int CH, int OUTCH, int NPX>
 __global__ void __launch_bounds__(256) yuv_copy_rows_kernel(const __grid_constant__ CopyParams P) {
-  const int x = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int x = (blockIdx.x * 32 + threadIdx.x) * NPX;
   const int y = (blockIdx.y * 8 + threadIdx.y) * 2;
   if (x >= P.W || y >= P.H) return;
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
   const uint8_t* yp = f.p0 + P.luma_off + (long long)y * P.stride0 + x;
   const bool two = y + 1 < P.H;
-  const uint32_t y0 = __ldg(reinterpret_cast<const uint32_t*>(yp));
-  const uint32_t y1 = two ? __ldg(reinterpret_cast<const uint32_t*>(yp + P.stride0)) : y0;
   const long long coff = P.chroma_off + (long long)(y >> 1) * P.stride_uv;
-  CChroma ca, cb;
-  if (CH == kCopyPlanar) {
-    const uint32_t uu = __ldg(reinterpret_cast<const uint16_t*>(f.pu + coff + (x >> 1)));
-    const uint32_t vv = __ldg(reinterpret_cast<const uint16_t*>(f.pv + coff + (x >> 1)));
-    ca = c_chroma_terms(uu & 0xFF, vv & 0xFF);
-    cb = c_chroma_terms(uu >> 8, vv >> 8);
-  } else {
-    const uint8_t* uv = (CH == kCopyVU ? f.pv : f.pu) + coff + x;  // (first, second) byte pairs
-    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(uv));
-    const uint32_t a0 = w & 0xFF, b0 = (w >> 8) & 0xFF, a1 = (w >> 16) & 0xFF, b1 = w >> 24;
-    ca = CH == kCopyVU ? c_chroma_terms(b0, a0) : c_chroma_terms(a0, b0);
-    cb = CH == kCopyVU ? c_chroma_terms(b1, a1) : c_chroma_terms(a1, b1);
-  }
   uint8_t* op = f.out + (long long)y * P.dst_row_stride + (size_t)x * OUTCH;
-  uint32_t o[4];
-  c_row4<OUTCH>(y0, ca, cb, o);
-  if (OUTCH == 4 && P.out16) {
-    *reinterpret_cast<uint4*>(op) = make_uint4(o[0], o[1], o[2], o[3]);
-  } else {
-#pragma unroll
-    for (int k = 0; k < OUTCH; ++k) reinterpret_cast<uint32_t*>(op)[k] = o[k];
+  if (NPX == 4) {
+    const uint32_t y0 = __ldg(reinterpret_cast<const uint32_t*>(yp));
+    const uint32_t y1 = two ? __ldg(reinterpret_cast<const uint32_t*>(yp + P.stride0)) : y0;
+    uint32_t w = 0, uu = 0, vv = 0;
+    if (CH == kCopyPlanar) {
+      uu = __ldg(reinterpret_cast<const uint16_t*>(f.pu + coff + (x >> 1)));
+      vv = __ldg(reinterpret_cast<const uint16_t*>(f.pv + coff + (x >> 1)));
+    } else {
+      w = __ldg(reinterpret_cast<const uint32_t*>((CH == kCopyVU ? f.pv : f.pu) + coff + x));  // (first, second) pairs
+    }
+    CChroma ca, cb;
+    c_group_chroma<CH>(w, uu, vv, ca, cb);
+    uint32_t o[4];
+    c_row4<OUTCH>(y0, ca, cb, o);
+    c_store4<OUTCH>(op, o, P.out16 != 0);
+    if (!two) return;
+    c_row4<OUTCH>(y1, ca, cb, o);
+    c_store4<OUTCH>(op + P.dst_row_stride, o, P.out16 != 0);
+    return;
   }
-  if (!two) return;
-  op += P.dst_row_stride;
-  c_row4<OUTCH>(y1, ca, cb, o);
-  if (OUTCH == 4 && P.out16) {
-    *reinterpret_cast<uint4*>(op) = make_uint4(o[0], o[1], o[2], o[3]);
+  // eight pixels: two four-pixel groups
+  const uint2 y0 = __ldg(reinterpret_cast<const uint2*>(yp));
+  const uint2 y1 = two ? __ldg(reinterpret_cast<const uint2*>(yp + P.stride0)) : y0;
+  uint2 w = make_uint2(0u, 0u);
+  uint32_t uu = 0, vv = 0;
+  if (CH == kCopyPlanar) {
+    uu = __ldg(reinterpret_cast<const uint32_t*>(f.pu + coff + (x >> 1)));
+    vv = __ldg(reinterpret_cast<const uint32_t*>(f.pv + coff + (x >> 1)));
   } else {
+    w = __ldg(reinterpret_cast<const uint2*>((CH == kCopyVU ? f.pv : f.pu) + coff + x));
+  }
+  CChroma c0a, c0b, c1a, c1b;
+  c_group_chroma<CH>(w.x, uu & 0xFFFFu, vv & 0xFFFFu, c0a, c0b);
+  c_group_chroma<CH>(w.y, uu >> 16, vv >> 16, c1a, c1b);
 #pragma unroll
-    for (int k = 0; k < OUTCH; ++k) reinterpret_cast<uint32_t*>(op)[k] = o[k];
+  for (int row = 0; row < 2; ++row) {
+    if (row == 1 && !two) break;
+    const uint2 yy = row == 0 ? y0 : y1;
+    uint32_t a[4], b[4];
+    c_row4<OUTCH>(yy.x, c0a, c0b, a);
+    c_row4<OUTCH>(yy.y, c1a, c1b, b);
+    uint8_t* o = op + (long long)row * P.dst_row_stride;
+    if (OUTCH == 4) {
+      reinterpret_cast<uint4*>(o)[0] = make_uint4(a[0], a[1], a[2], a[3]);
+      reinterpret_cast<uint4*>(o)[1] = make_uint4(b[0], b[1], b[2], b[3]);
+    } else {
+      reinterpret_cast<uint2*>(o)[0] = make_uint2(a[0], a[1]);
+      reinterpret_cast<uint2*>(o)[1] = make_uint2(a[2], b[0]);
+      reinterpret_cast<uint2*>(o)[2] = make_uint2(b[1], b[2]);
+    }
   }
 }
 
@@ -176,7 +219,7 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
   P.stride0 = d.stride0; P.stride_uv = d.stride_uv;
   P.dst_row_stride = d.dst_row_stride;
   CopyKernel kern = nullptr;
-  int src_bpp = 1, rows_per_thread = 1;
+  int src_bpp = 1, rows_per_thread = 1, px_per_thread = 4;
   bool need_chroma = false;
   if (d.src_kind == BANDCU_SRC_YUV420 && (d.cvt == BANDCU_CVT_YUV2RGB || d.cvt == BANDCU_CVT_YUV2RGBA)) {
     if ((d.pre_map.r0 & 1) || (d.pre_map.c0 & 1)) return BANDCU_E_UNSUPPORTED;
@@ -240,15 +283,36 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
       in4 = hints.aligned16;
     }
     const bool rgba = d.cvt == BANDCU_CVT_YUV2RGBA;
-    if (ch == kCopyUV) kern = rgba ? yuv_copy_rows_kernel<kCopyUV, 4> : yuv_copy_rows_kernel<kCopyUV, 3>;
-    else if (ch == kCopyVU) kern = rgba ? yuv_copy_rows_kernel<kCopyVU, 4> : yuv_copy_rows_kernel<kCopyVU, 3>;
-    else kern = rgba ? yuv_copy_rows_kernel<kCopyPlanar, 4> : yuv_copy_rows_kernel<kCopyPlanar, 3>;
+    // eight pixels per thread when everything is 8-byte granular (planar chroma: 4-byte loads at x/2; RGBA: 16-byte stores)
+    if ((d.vw & 7) == 0 && !batch.table && in4 && out4) {
+      uintptr_t ib = reinterpret_cast<uintptr_t>(batch.first.p0) | (uintptr_t)d.stride0 | (uintptr_t)P.luma_off |
+                     (n == 1 ? 0 : (uintptr_t)batch.in_stride);
+      if (planar) {
+        const uintptr_t cb = reinterpret_cast<uintptr_t>(batch.first.pu) | reinterpret_cast<uintptr_t>(batch.first.pv) |
+                             (uintptr_t)d.stride_uv | (uintptr_t)P.chroma_off;
+        if (cb & 3) ib |= 7;
+      } else {
+        ib |= reinterpret_cast<uintptr_t>(ch == kCopyVU ? batch.first.pv : batch.first.pu) | (uintptr_t)d.stride_uv |
+              (uintptr_t)P.chroma_off;
+      }
+      const uintptr_t ob = reinterpret_cast<uintptr_t>(batch.first.out) | (uintptr_t)d.dst_row_stride |
+                           (n == 1 ? 0 : (uintptr_t)batch.out_stride);
+      if ((ib & 7) == 0 && (ob & (rgba ? 15 : 7)) == 0) px_per_thread = 8;
+    }
+    const bool p8 = px_per_thread == 8;
+#define BANDCU_COPY_PICK(C) \
+    (rgba ? (p8 ? yuv_copy_rows_kernel<C, 4, 8> : yuv_copy_rows_kernel<C, 4, 4>) \
+          : (p8 ? yuv_copy_rows_kernel<C, 3, 8> : yuv_copy_rows_kernel<C, 3, 4>))
+    if (ch == kCopyUV) kern = BANDCU_COPY_PICK(kCopyUV);
+    else if (ch == kCopyVU) kern = BANDCU_COPY_PICK(kCopyVU);
+    else kern = BANDCU_COPY_PICK(kCopyPlanar);
+#undef BANDCU_COPY_PICK
   }
   if (!in4 || !out4) return BANDCU_E_UNSUPPORTED;
   P.out16 = (out16 && (d.dst_row_stride & 15) == 0) ? 1 : 0;
   const dim3 block(32, 8, 1);
   const int rows = (d.vh + rows_per_thread - 1) / rows_per_thread;
-  dim3 grid((d.vw / 4 + 31) / 32, (rows + 7) / 8, 1);
+  dim3 grid((d.vw / px_per_thread + 31) / 32, (rows + 7) / 8, 1);
   for (int done = 0; done < n;) {
     const int chunk = n - done > 65535 ? 65535 : n - done;
     CopyParams Q = P;
