@@ -162,39 +162,61 @@ __global__ void __launch_bounds__(256) yuv_copy_rows_kernel(const __grid_constan
 // Packed sources, four pixels per thread: RGBA -> RGB (drop alpha), RGBA -> gray, RGB -> gray (RGBToYJ), and the
 // luma plane of a 4:2:0 frame -> gray (a strided copy). SRCB / DSTB = bytes per pixel.
 enum { kPkRgbaToRgb = 0, kPkRgbaToGray = 1, kPkRgbToGray = 2, kPkLumaCopy = 3 };
+// One four-pixel group: SW source words -> DW output words.
 template <int MODE>
+__device__ __forceinline__ void pk_group(const uint32_t* p, uint32_t* o) {
+  if (MODE == kPkLumaCopy) {
+    o[0] = p[0];
+  } else if (MODE == kPkRgbToGray) {
+    const uint32_t a = p[0], b = p[1], c = p[2];  // R0G0B0R1 G1B1R2G2 B2R3G3B3
+    const uint32_t g0 = rgb_to_yj(a & 0xFF, (a >> 8) & 0xFF, (a >> 16) & 0xFF);
+    const uint32_t g1 = rgb_to_yj(a >> 24, b & 0xFF, (b >> 8) & 0xFF);
+    const uint32_t g2 = rgb_to_yj((b >> 16) & 0xFF, b >> 24, c & 0xFF);
+    const uint32_t g3 = rgb_to_yj((c >> 8) & 0xFF, (c >> 16) & 0xFF, c >> 24);
+    o[0] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+  } else if (MODE == kPkRgbaToGray) {
+    uint32_t g[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) g[k] = rgb_to_yj(p[k] & 0xFF, (p[k] >> 8) & 0xFF, (p[k] >> 16) & 0xFF);
+    o[0] = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+  } else {
+    o[0] = __byte_perm(p[0], p[1], 0x4210);  // R0 G0 B0 R1
+    o[1] = __byte_perm(p[1], p[2], 0x5421);  // G1 B1 R2 G2
+    o[2] = __byte_perm(p[2], p[3], 0x6542);  // B2 R3 G3 B3
+  }
+}
+// NPX = 4: 32-bit accesses. NPX = 16: four groups per thread, 128-bit loads and stores (16-byte granular frames).
+template <int MODE, int NPX>
 __global__ void __launch_bounds__(256) packed_copy_rows_kernel(const __grid_constant__ CopyParams P) {
-  const int x = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int x = (blockIdx.x * 32 + threadIdx.x) * NPX;
   const int y = blockIdx.y * 8 + threadIdx.y;
   if (x >= P.W || y >= P.H) return;
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
   constexpr int SRCB = MODE == kPkRgbToGray ? 3 : MODE == kPkLumaCopy ? 1 : 4;
   constexpr int DSTB = MODE == kPkRgbaToRgb ? 3 : 1;
-  const uint32_t* sp = reinterpret_cast<const uint32_t*>(f.p0 + P.luma_off + (long long)y * P.stride0 + (size_t)x * SRCB);
-  uint32_t* op = reinterpret_cast<uint32_t*>(f.out + (long long)y * P.dst_row_stride + (size_t)x * DSTB);
-  if (MODE == kPkLumaCopy) {
-    op[0] = __ldg(sp);
-  } else if (MODE == kPkRgbToGray) {
-    const uint32_t a = __ldg(sp), b = __ldg(sp + 1), c = __ldg(sp + 2);  // R0G0B0R1 G1B1R2G2 B2R3G3B3
-    const uint32_t g0 = rgb_to_yj(a & 0xFF, (a >> 8) & 0xFF, (a >> 16) & 0xFF);
-    const uint32_t g1 = rgb_to_yj(a >> 24, b & 0xFF, (b >> 8) & 0xFF);
-    const uint32_t g2 = rgb_to_yj((b >> 16) & 0xFF, b >> 24, c & 0xFF);
-    const uint32_t g3 = rgb_to_yj((c >> 8) & 0xFF, (c >> 16) & 0xFF, c >> 24);
-    op[0] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
-  } else {
-    uint32_t p[4];
+  constexpr int SW = SRCB, DW = DSTB, G = NPX / 4;  // words per four-pixel group in / out
+  const uint8_t* sp = f.p0 + P.luma_off + (long long)y * P.stride0 + (size_t)x * SRCB;
+  uint8_t* op = f.out + (long long)y * P.dst_row_stride + (size_t)x * DSTB;
+  uint32_t in[SW * G], out[DW * G];
+  if (G == 4) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) p[k] = __ldg(sp + k);
-    if (MODE == kPkRgbaToGray) {
-      uint32_t g[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) g[k] = rgb_to_yj(p[k] & 0xFF, (p[k] >> 8) & 0xFF, (p[k] >> 16) & 0xFF);
-      op[0] = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
-    } else {
-      op[0] = __byte_perm(p[0], p[1], 0x4210);  // R0 G0 B0 R1
-      op[1] = __byte_perm(p[1], p[2], 0x5421);  // G1 B1 R2 G2
-      op[2] = __byte_perm(p[2], p[3], 0x6542);  // B2 R3 G3 B3
+    for (int k = 0; k < SW; ++k) {
+      const uint4 q = __ldg(reinterpret_cast<const uint4*>(sp) + k);
+      in[4 * k] = q.x; in[4 * k + 1] = q.y; in[4 * k + 2] = q.z; in[4 * k + 3] = q.w;
     }
+  } else {
+#pragma unroll
+    for (int k = 0; k < SW; ++k) in[k] = __ldg(reinterpret_cast<const uint32_t*>(sp) + k);
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g) pk_group<MODE>(in + g * SW, out + g * DW);
+  if (G == 4) {
+#pragma unroll
+    for (int k = 0; k < DW; ++k)
+      reinterpret_cast<uint4*>(op)[k] = make_uint4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < DW; ++k) reinterpret_cast<uint32_t*>(op)[k] = out[k];
   }
 }
 
@@ -219,7 +241,7 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
   P.stride0 = d.stride0; P.stride_uv = d.stride_uv;
   P.dst_row_stride = d.dst_row_stride;
   CopyKernel kern = nullptr;
-  int src_bpp = 1, rows_per_thread = 1, px_per_thread = 4;
+  int src_bpp = 1, rows_per_thread = 1, px_per_thread = 4, pk_mode = -1;
   bool need_chroma = false;
   if (d.src_kind == BANDCU_SRC_YUV420 && (d.cvt == BANDCU_CVT_YUV2RGB || d.cvt == BANDCU_CVT_YUV2RGBA)) {
     if ((d.pre_map.r0 & 1) || (d.pre_map.c0 & 1)) return BANDCU_E_UNSUPPORTED;
@@ -229,13 +251,13 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
     need_chroma = true;
     rows_per_thread = 2;
   } else if (d.src_kind == BANDCU_SRC_YUV420 && d.cvt == BANDCU_CVT_YUV2GRAY) {
-    kern = packed_copy_rows_kernel<kPkLumaCopy>;
+    pk_mode = kPkLumaCopy;
   } else if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2RGB) {
-    kern = packed_copy_rows_kernel<kPkRgbaToRgb>; src_bpp = 4;
+    pk_mode = kPkRgbaToRgb; src_bpp = 4;
   } else if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2GRAY) {
-    kern = packed_copy_rows_kernel<kPkRgbaToGray>; src_bpp = 4;
+    pk_mode = kPkRgbaToGray; src_bpp = 4;
   } else if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_RGB2GRAY) {
-    kern = packed_copy_rows_kernel<kPkRgbToGray>; src_bpp = 3;
+    pk_mode = kPkRgbToGray; src_bpp = 3;
   } else {
     return BANDCU_E_UNSUPPORTED;
   }
@@ -307,6 +329,22 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
     else if (ch == kCopyVU) kern = BANDCU_COPY_PICK(kCopyVU);
     else kern = BANDCU_COPY_PICK(kCopyPlanar);
 #undef BANDCU_COPY_PICK
+  }
+  if (pk_mode >= 0) {
+    // sixteen pixels per thread when rows, planes and outputs are 16-byte granular
+    if ((d.vw & 15) == 0 && !batch.table) {
+      const uintptr_t bits = reinterpret_cast<uintptr_t>(batch.first.p0) | (uintptr_t)d.stride0 | (uintptr_t)P.luma_off |
+                             reinterpret_cast<uintptr_t>(batch.first.out) | (uintptr_t)d.dst_row_stride |
+                             (n == 1 ? 0 : ((uintptr_t)batch.in_stride | (uintptr_t)batch.out_stride));
+      if ((bits & 15) == 0) px_per_thread = 16;
+    }
+    const bool w16 = px_per_thread == 16;
+    switch (pk_mode) {
+      case kPkLumaCopy: kern = w16 ? packed_copy_rows_kernel<kPkLumaCopy, 16> : packed_copy_rows_kernel<kPkLumaCopy, 4>; break;
+      case kPkRgbaToRgb: kern = w16 ? packed_copy_rows_kernel<kPkRgbaToRgb, 16> : packed_copy_rows_kernel<kPkRgbaToRgb, 4>; break;
+      case kPkRgbaToGray: kern = w16 ? packed_copy_rows_kernel<kPkRgbaToGray, 16> : packed_copy_rows_kernel<kPkRgbaToGray, 4>; break;
+      default: kern = w16 ? packed_copy_rows_kernel<kPkRgbToGray, 16> : packed_copy_rows_kernel<kPkRgbToGray, 4>; break;
+    }
   }
   if (!in4 || !out4) return BANDCU_E_UNSUPPORTED;
   P.out16 = (out16 && (d.dst_row_stride & 15) == 0) ? 1 : 0;
