@@ -404,7 +404,13 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
           const uint32_t gq = hblend_pair_raw(vblend2(tg, bg, w0, w1), wp);
           const uint32_t b = hblend_pair_raw(vblend2(tb, bb, w0, w1), wp);
           if (sizeof(OT) == 1) {
-            o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(gq >> 23); o[2] = (uint8_t)(b >> 23);
+            if (P.lut) {  // Normalize into a one-byte type (int8 / uint8 model inputs): the table holds the byte
+              o[0] = (uint8_t)lds_u32(lut_lane + ((r >> 18) & 0x1FE0u));
+              o[1] = (uint8_t)lds_u32(lut_lane + ((gq >> 18) & 0x1FE0u));
+              o[2] = (uint8_t)lds_u32(lut_lane + ((b >> 18) & 0x1FE0u));
+            } else {
+              o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(gq >> 23); o[2] = (uint8_t)(b >> 23);
+            }
           } else {
             // table index v = raw >> 23; byte offset v * 4 * kLutCopies = (raw >> 18) & 0x1FE0
             float* of = reinterpret_cast<float*>(o);
@@ -438,6 +444,12 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
 }
 
 // Builds the Normalize table with the same device arithmetic as the generic kernel.
+// One-byte Normalize outputs: the 32-bit table entry holds the output byte (same element arithmetic, then the cast).
+template <typename T>
+__global__ void build_byte_lut_kernel(uint32_t* lut, float mean, float sd) {
+  const int i = threadIdx.x;
+  if (i < 256) lut[i] = (uint32_t)(uint8_t)normalize_elem<T>((float)i, mean, sd);
+}
 __global__ void build_lut_kernel(float* lut, float mean, float sd) {
   int i = threadIdx.x;
   if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
@@ -468,7 +480,7 @@ bool fast_plan_supported(const BandCuPlanDesc& d) {
   if (d.cvt != BANDCU_CVT_YUV2RGB || d.channels != 3) return false;
   if (d.flavor != BANDCU_FLAVOR_ARGB || d.scale_mode != BANDCU_SCALE_BILINEAR_DOWN) return false;
   if (!crop_only(d)) return false;  // identity maps included
-  if (d.normalize ? (d.out_dtype != BANDCU_DT_F32) : false) return false;
+  if (d.normalize && d.out_dtype != BANDCU_DT_F32 && d.out_dtype != BANDCU_DT_I8 && d.out_dtype != BANDCU_DT_U8) return false;
   if (d.vw < 2 || d.vw > 8192 || d.dst_width > 4096) return false;
   // 32-bit x stepping inside the kernel
   if ((long long)d.x0 + (long long)d.dst_width * d.dx > 0x7fffffffLL) return false;
@@ -485,7 +497,9 @@ int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out) {
   if (d.normalize) {
     e = cudaMalloc(&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
-    build_lut_kernel<<<1, 256>>>((float*)p->lut_dev, d.mean, d.std_);
+    if (d.out_dtype == BANDCU_DT_I8) build_byte_lut_kernel<int8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
+    else if (d.out_dtype == BANDCU_DT_U8) build_byte_lut_kernel<uint8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
+    else build_lut_kernel<<<1, 256>>>((float*)p->lut_dev, d.mean, d.std_);
     count_launch();
     e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { cudaFree(p->lut_dev); delete p; return (int)e; }
@@ -560,7 +574,8 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   while (P.R > 1 && (long long)n * ((d.dst_height + P.R - 1) / P.R) < 2LL * p->num_sms) P.R >>= 1;
   P.passes = (d.dst_width + 511) / 512;
   P.cols = (((d.dst_width + P.passes - 1) / P.passes) + 31) / 32 * 32;
-  const int esize = d.normalize ? 4 : 1;
+  const bool f32_out = d.normalize && d.out_dtype == BANDCU_DT_F32;
+  const int esize = f32_out ? 4 : 1;
   P.out_row_bytes = d.dst_width * 3 * esize;
   // bulk stores need 16-byte granularity everywhere (row length, row stride, every output pointer)
   bool out_aligned;
@@ -603,7 +618,7 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   const char* nb = getenv("BANDCU_FAST_NO_BULK");
   if (nb && nb[0] == '1') P.use_bulk = 0;
   // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
-  FastKernel kern = d.normalize ? pick_kernel<float>(ch, bulk_out) : pick_kernel<uint8_t>(ch, bulk_out);
+  FastKernel kern = f32_out ? pick_kernel<float>(ch, bulk_out) : pick_kernel<uint8_t>(ch, bulk_out);
   int per_sm = 1;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);

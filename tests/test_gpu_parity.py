@@ -298,3 +298,22 @@ def test_pinned_host_tensors_bulk_store(O, fmt_name, W, H, dw, dh, f32, dev_in):
         L.BandHostFree(host)
         if dev:
             L.BandDeviceFree(dev)
+
+
+@pytest.mark.parametrize("out_dt_name,mean,std", [("DT_I8", 128.0, 1.0), ("DT_U8", 0.0, 2.0), ("DT_I8", 127.5, 1.0)])
+@pytest.mark.parametrize("fmt_name,W,H,d", [("NV21", 1920, 1080, 224), ("NV12", 640, 480, 300), ("YV12", 1920, 1080, 224),
+                                            ("NV21", 642, 482, 224)])
+def test_quantized_model_inputs(O, out_dt_name, mean, std, fmt_name, W, H, d):
+    """CSC -> Resize -> Normalize into a ONE-BYTE tensor (int8 / uint8 quantized models: NormalizeFromTo<u8, i8>,
+    common_operator.cc:24-40, cast of the difference then the division): the row-staged kernel with a byte table;
+    the unaligned case runs its byte-copy producer. uint8 keeps mean at 0: the cast of a negative difference to an unsigned
+    type is undefined in the reference too."""
+    out_dt = getattr(O, out_dt_name)
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, d, d), (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)]
+    fr = rand_frames(O, 2, W, H, fmt, 4242 + d)
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, out_dt, (1, d, d, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, W, H, fmt, out_dt, (1, d, d, 3), device_resident=True)
+    assert st == 0
+    assert_same_bits(got, want, "quantized %s %s" % (out_dt_name, fmt_name))
