@@ -300,7 +300,8 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   extern __shared__ __align__(16) uint8_t smem[];
   __shared__ float lut[256];
   const BandCuPlanDesc& d = P.d;
-  if (sizeof(OT) == 4) lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
+  // f32 outputs: the Normalize table; one-byte Normalize outputs (int8 / uint8 models): 32-bit entries holding the byte
+  if (sizeof(OT) == 4 || P.lut) lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
   const int oy0 = blockIdx.y * P.TR, ox0 = blockIdx.x * P.TC;
   const int oy1 = min(oy0 + P.TR, d.dst_height) - 1, ox1 = min(ox0 + P.TC, d.dst_width) - 1;
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
@@ -407,8 +408,11 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
   if (P.out_vec && ncols == 32) {  // 24 aligned pieces per row (ox0 is a multiple of 32)
     for (int idx = threadIdx.x; idx < nrows * 24; idx += 256) {
       const int row = idx / 24, q = idx - row * 24;
-      const uint32_t w = os[row * 25 + q];
+      uint32_t w = os[row * 25 + q];
       uint8_t* o = obase + (long long)row * d.dst_row_stride;
+      if (sizeof(OT) == 1 && P.lut)
+        w = (__float_as_uint(lut[w & 0xFF]) & 0xFF) | ((__float_as_uint(lut[(w >> 8) & 0xFF]) & 0xFF) << 8) |
+            ((__float_as_uint(lut[(w >> 16) & 0xFF]) & 0xFF) << 16) | (__float_as_uint(lut[w >> 24]) << 24);
       if (sizeof(OT) == 1) reinterpret_cast<uint32_t*>(o)[q] = w;
       else reinterpret_cast<float4*>(o)[q] = make_float4(lut[w & 0xFF], lut[(w >> 8) & 0xFF], lut[(w >> 16) & 0xFF], lut[w >> 24]);
     }
@@ -419,12 +423,17 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
       if (c >= 3 * ncols) continue;
       const uint32_t v = ob[row * 100 + c];
       uint8_t* o = obase + (long long)row * d.dst_row_stride;
-      if (sizeof(OT) == 1) o[c] = (uint8_t)v;
+      if (sizeof(OT) == 1) o[c] = P.lut ? (uint8_t)__float_as_uint(lut[v]) : (uint8_t)v;
       else reinterpret_cast<float*>(o)[c] = lut[v];
     }
   }
 }
 
+template <typename T>
+__global__ void tile_build_byte_lut_kernel(uint32_t* lut, float mean, float sd) {
+  const int i = threadIdx.x;
+  if (i < 256) lut[i] = (uint32_t)(uint8_t)normalize_elem<T>((float)i, mean, sd);
+}
 __global__ void tile_build_lut_kernel(float* lut, float mean, float sd) {
   const int i = threadIdx.x;
   if (i < 256) lut[i] = normalize_elem<float>((float)i, mean, sd);
@@ -481,7 +490,9 @@ bool tile_plan_supported(const BandCuPlanDesc& d) {
   if (d.src_kind != BANDCU_SRC_YUV420 || d.cvt != BANDCU_CVT_YUV2RGB || d.channels != 3) return false;
   if (d.flavor != BANDCU_FLAVOR_ARGB || d.scale_mode != BANDCU_SCALE_BILINEAR_DOWN) return false;
   if (d.pixel_stride_uv != 1 && d.pixel_stride_uv != 2) return false;
-  if (d.normalize ? d.out_dtype != BANDCU_DT_F32 : d.out_dtype != BANDCU_DT_U8) return false;
+  if (d.normalize ? (d.out_dtype != BANDCU_DT_F32 && d.out_dtype != BANDCU_DT_I8 && d.out_dtype != BANDCU_DT_U8)
+                  : d.out_dtype != BANDCU_DT_U8)
+    return false;
   if (!is_permutation(d.luma_map) || !is_permutation(d.pre_map) || !is_permutation(d.chroma_map)) return false;
   // 32-bit word staging: rows must start word aligned and whole words must stay inside the plane rows
   if (d.src_width <= 0 || d.src_width % 4 != 0 || d.stride0 % 4 != 0 || d.stride_uv % 4 != 0) return false;
@@ -533,7 +544,9 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { cudaFree(p->geom_dev); delete p; return (int)e; }
-    tile_build_lut_kernel<<<1, 256>>>(p->lut_dev, d.mean, d.std_);
+    if (d.out_dtype == BANDCU_DT_I8) tile_build_byte_lut_kernel<int8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
+    else if (d.out_dtype == BANDCU_DT_U8) tile_build_byte_lut_kernel<uint8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
+    else tile_build_lut_kernel<<<1, 256>>>(p->lut_dev, d.mean, d.std_);
     count_launch();
     e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { cudaFree(p->lut_dev); cudaFree(p->geom_dev); delete p; return (int)e; }
@@ -565,6 +578,7 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   TileParams P;
   memset(&P, 0, sizeof(P));
   P.d = d;
+  const bool f32_out = d.normalize && d.out_dtype == BANDCU_DT_F32;
   P.batch = batch;
   P.TR = p->TR; P.TC = p->TC;
   P.tiles_x = (d.dst_width + P.TC - 1) / P.TC;
@@ -645,13 +659,13 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   P.off_terms = (int)g.stage_bytes;
   const size_t smem = g.stage_bytes + 2048 + 3200;  // + row / column term tables + the [32][25]-word output tile
   {
-    const int need = d.normalize ? 15 : 3;
+    const int need = f32_out ? 15 : 3;
     bool ok;
     if (batch.table) ok = hints.out_aligned16;
     else ok = (reinterpret_cast<uintptr_t>(batch.first.out) & need) == 0 && (n == 1 || (batch.out_stride & need) == 0);
     P.out_vec = (ok && (d.dst_row_stride & need) == 0) ? 1 : 0;
   }
-  TileKernel kern = d.normalize ? pick_tile_kernel<float>(aligned16, swap, P.interleaved != 0) : pick_tile_kernel<uint8_t>(aligned16, swap, P.interleaved != 0);
+  TileKernel kern = f32_out ? pick_tile_kernel<float>(aligned16, swap, P.interleaved != 0) : pick_tile_kernel<uint8_t>(aligned16, swap, P.interleaved != 0);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   for (int done = 0; done < n;) {

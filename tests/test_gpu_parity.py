@@ -317,3 +317,18 @@ def test_quantized_model_inputs(O, out_dt_name, mean, std, fmt_name, W, H, d):
     st, got = gpu_chain(ops, fr, W, H, fmt, out_dt, (1, d, d, 3), device_resident=True)
     assert st == 0
     assert_same_bits(got, want, "quantized %s %s" % (out_dt_name, fmt_name))
+
+
+@pytest.mark.parametrize("angle", [90, 180])
+@pytest.mark.parametrize("fmt_name", ["NV21", "YV12"])
+def test_quantized_model_inputs_rotated(O, angle, fmt_name):
+    """Rotate -> CSC -> Resize -> Normalize(128, 1) into int8: the tile-staged kernel with the byte table."""
+    W, H, d = 1280, 720, 224
+    fmt = getattr(O, "FMT_" + fmt_name)
+    ops = [(O.OP_ROTATE, angle), (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, d, d), (O.OP_NORMALIZE, 0, 0, 0, 0, 128.0, 1.0)]
+    fr = rand_frames(O, 2, W, H, fmt, 777 + angle)
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, O.DT_I8, (1, d, d, 3))
+    assert st == 0
+    st, got = gpu_chain(ops, fr, W, H, fmt, O.DT_I8, (1, d, d, 3), device_resident=True)
+    assert st == 0
+    assert_same_bits(got, want, "quantized rotated %s %d" % (fmt_name, angle))
