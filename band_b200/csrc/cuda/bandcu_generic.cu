@@ -455,6 +455,69 @@ __global__ void __launch_bounds__(256) plane_map_tile_kernel(const __grid_consta
   }
 }
 
+// Straight maps (crop, flips, half-turn) need no staging: 16 output bytes are 16 CONSECUTIVE source bytes, ascending or
+// descending. The staged kernel above keeps 8 - 16 bytes per thread in flight (~16 KB per SM: 1.2 TB/s by Little's
+// law, which is what it measured on flips and crops); here a thread owns one 16-byte column of FOUR rows and issues
+// its four loads (128-bit when the source chunk is aligned, 32-bit or byte loads otherwise) before the first store.
+// A horizontal flip reverses the chunk: words swapped, bytes (E = 1) or byte pairs (E = 2) reversed by PRMT.
+// blockIdx.z = 3 * frame + plane; grid.x covers 512-byte column groups, grid.y 32-row groups.
+__global__ void __launch_bounds__(256) plane_rows16_kernel(const __grid_constant__ PlaneMapParams P) {
+  const PlaneMap& pl = P.pl[blockIdx.z % 3];
+  if (!pl.src) return;
+  const int E = pl.esize;
+  const int row_bytes = pl.w * E;
+  const int b0 = (blockIdx.x * 32 + threadIdx.x) * 16;
+  const int r0 = (blockIdx.y * 8 + threadIdx.y) * 4;
+  if (b0 >= row_bytes || r0 >= pl.h) return;
+  const uint8_t* src = pl.src + (long long)(blockIdx.z / 3) * P.src_step;
+  uint8_t* dst = pl.dst + (long long)(blockIdx.z / 3) * P.dst_step;
+  const bool rev = pl.m.cc < 0;
+  const bool whole = b0 + 16 <= row_bytes;
+  if (whole) {
+    // lowest source byte of the chunk (row-relative): ascending from c0 * E + b0, or the mirror image of [b0, b0 + 16)
+    const int sb = !rev ? pl.m.c0 * E + b0 : (pl.m.c0 + 1) * E - b0 - 16;
+    const uint32_t perm = !rev ? 0x3210u : (E == 1 ? 0x0123u : E == 2 ? 0x1032u : 0x3210u);
+    uint4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = min(r0 + j, pl.h - 1);
+      const uint8_t* a = src + (long long)(pl.m.r0 + pl.m.rr * r) * pl.src_stride + sb;
+      const uintptr_t al = reinterpret_cast<uintptr_t>(a);
+      if ((al & 15) == 0) {
+        v[j] = __ldg(reinterpret_cast<const uint4*>(a));
+      } else if ((al & 3) == 0) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(a);
+        v[j] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+      } else {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          w[k] = (uint32_t)__ldg(a + 4 * k) | ((uint32_t)__ldg(a + 4 * k + 1) << 8) | ((uint32_t)__ldg(a + 4 * k + 2) << 16) |
+                 ((uint32_t)__ldg(a + 4 * k + 3) << 24);
+        v[j] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (r0 + j >= pl.h) break;
+      uint4 o = v[j];
+      if (rev) o = make_uint4(__byte_perm(v[j].w, 0u, perm), __byte_perm(v[j].z, 0u, perm), __byte_perm(v[j].y, 0u, perm),
+                              __byte_perm(v[j].x, 0u, perm));
+      *reinterpret_cast<uint4*>(dst + (long long)(r0 + j) * pl.dst_stride + b0) = o;
+    }
+    return;
+  }
+  for (int j = 0; j < 4 && r0 + j < pl.h; ++j) {  // the partial chunk at the end of a row: byte by byte
+    const int r = r0 + j;
+    const uint8_t* srow = src + (long long)(pl.m.r0 + pl.m.rr * r) * pl.src_stride;
+    uint8_t* o = dst + (long long)r * pl.dst_stride;
+    for (int b = b0; b < row_bytes; ++b) {
+      const int c = E == 1 ? b : E == 2 ? (b >> 1) : E == 4 ? (b >> 2) : (int)(((unsigned)b * 43691u) >> 17);
+      o[b] = __ldg(srow + (long long)(pl.m.c0 + pl.m.cc * c) * E + (b - c * E));
+    }
+  }
+}
+
 static bool plane_map_ok(const BandCuAffine& m) {
   const bool straight = (m.rr == 1 || m.rr == -1) && (m.cc == 1 || m.cc == -1) && m.rc == 0 && m.cr == 0;
   const bool swapped = m.rr == 0 && m.cc == 0 && (m.rc == 1 || m.rc == -1) && (m.cr == 1 || m.cr == -1);
@@ -503,6 +566,33 @@ static int launch_plane_map_tiles(const BandCuYuvMapDesc& d, const BandCuYuvPtrs
 }
 
 static int run_plane_maps(PlaneMapParams& P, int n, cudaStream_t stream) {
+  {  // every plane straight, destination rows 16-byte aligned, no 3-byte elements under a horizontal flip: no staging
+    bool rows16 = true;
+    int bx = 1, by = 1;
+    for (int k = 0; k < 3; ++k) {
+      const PlaneMap& pl = P.pl[k];
+      if (!pl.src) continue;
+      const uintptr_t bits = reinterpret_cast<uintptr_t>(pl.dst) | (uintptr_t)pl.dst_stride | (n == 1 ? 0 : (uintptr_t)P.dst_step);
+      if (pl.m.rr == 0 || (bits & 15) != 0 || (pl.esize == 3 && pl.m.cc < 0)) rows16 = false;
+      bx = max(bx, (pl.w * pl.esize + 511) / 512);
+      by = max(by, (pl.h + 31) / 32);
+    }
+    if (rows16) {
+      for (int done = 0; done < n;) {
+        const int chunk = n - done > 21845 ? 21845 : n - done;
+        PlaneMapParams Q = P;
+        for (int k = 0; k < 3; ++k) {
+          if (!Q.pl[k].src) continue;
+          Q.pl[k].src += (long long)done * P.src_step;
+          Q.pl[k].dst += (long long)done * P.dst_step;
+        }
+        plane_rows16_kernel<<<dim3(bx, by, 3 * chunk), dim3(32, 8, 1), 0, stream>>>(Q);
+        count_launch();
+        done += chunk;
+      }
+      return (int)cudaGetLastError();
+    }
+  }
   int gx = 1, gy = 1;
   for (int k = 0; k < 3; ++k) {
     if (!P.pl[k].src) continue;
