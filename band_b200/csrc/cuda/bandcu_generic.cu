@@ -372,6 +372,10 @@ struct PlaneMapParams {
 // Tile: 32 output rows x kPlaneTew(E) output elements (64, 32, 32, 32 elements = 64, 64, 96, 128 bytes). Staged either
 // way round the map turns it: at most 64 rows of at most 128 bytes.
 __host__ __device__ constexpr int plane_tew(int E) { return E == 1 ? 64 : 32; }
+// Quarter-turns of one- and two-byte elements use larger tiles (plane_turn_tile below): 64 output elements wide, 128 / 64 rows.
+__host__ __device__ inline bool plane_big_turn(const PlaneMap& pl) { return pl.m.rr == 0 && pl.esize <= 2; }
+__host__ __device__ inline int plane_tile_w(const PlaneMap& pl) { return plane_big_turn(pl) ? 64 : plane_tew(pl.esize); }
+__host__ __device__ inline int plane_tile_h(const PlaneMap& pl) { return plane_big_turn(pl) ? (pl.esize == 1 ? 128 : 64) : 32; }
 template <int E>
 __device__ __forceinline__ void plane_map_tile(const PlaneMap& pl, long long src_off, long long dst_off, uint8_t* stage) {
   constexpr int TEW = plane_tew(E), TR = 32, WPR = TEW * E / 4;  // words per output tile row
@@ -440,6 +444,101 @@ __device__ __forceinline__ void plane_map_tile(const PlaneMap& pl, long long src
         if (b0 + k < row_bytes) o[k] = (uint8_t)v[k];
     }
   }
+}
+// Quarter-turn of a plane of one- or two-byte elements. The staged rectangle is 64 source rows x 128 bytes (8 KB): a
+// thread keeps eight 32-bit loads in flight (byte loads in two batches when the rectangle is not word aligned) -- the
+// 32-row tiles above hold 8 bytes per thread in flight, ~16 KB per SM, which is the 1.2 TB/s they measure. Bytes go
+// into shared memory at an odd pitch, so the gather of an output word (four staged rows, one column) is
+// conflict-free; each thread keeps its word column, so the four column terms are computed once.
+template <int E>
+__device__ __forceinline__ void plane_turn_tile(const PlaneMap& pl, long long src_off, long long dst_off, uint8_t* stage) {
+  constexpr int TEW = 64, TR = E == 1 ? 128 : 64, WPR = TEW * E / 4, RSTEP = 256 / WPR;
+  const int c_lo = blockIdx.x * TEW, r_lo = blockIdx.y * TR;
+  if (c_lo >= pl.w || r_lo >= pl.h) return;
+  const int c_hi = min(c_lo + TEW, pl.w) - 1, r_hi = min(r_lo + TR, pl.h) - 1;
+  const int ra = map_row(pl.m, r_lo, c_lo), rb = map_row(pl.m, r_hi, c_hi);
+  const int ca = map_col(pl.m, r_lo, c_lo), cb = map_col(pl.m, r_hi, c_hi);
+  const int sr0 = min(ra, rb), sc0 = min(ca, cb);
+  const int srows = abs(ra - rb) + 1, sbytes = (abs(ca - cb) + 1) * E;  // <= 64 rows x 128 bytes
+  const int pitch = sbytes | 1;
+  const uint8_t* src = pl.src + src_off + (long long)sr0 * pl.src_stride + (long long)sc0 * E;
+  const int lane = threadIdx.x, wid = threadIdx.y;
+  if (((reinterpret_cast<uintptr_t>(src) | (uintptr_t)pl.src_stride | (uintptr_t)sbytes) & 3) == 0) {
+    const int wprs = sbytes >> 2;  // <= 32 words per staged row: lane = word
+    uint32_t v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = wid + 8 * i;
+      if (r < srows && lane < wprs) v[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)r * pl.src_stride) + lane);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = wid + 8 * i;
+      if (r < srows && lane < wprs) {
+        uint8_t* q = stage + r * pitch + 4 * lane;
+        q[0] = (uint8_t)v[i]; q[1] = (uint8_t)(v[i] >> 8); q[2] = (uint8_t)(v[i] >> 16); q[3] = (uint8_t)(v[i] >> 24);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint8_t v[16];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = wid + 8 * (4 * half + i);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (r < srows && lane + 32 * j < sbytes) v[4 * i + j] = __ldg(src + (long long)r * pl.src_stride + lane + 32 * j);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = wid + 8 * (4 * half + i);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (r < srows && lane + 32 * j < sbytes) stage[r * pitch + lane + 32 * j] = v[4 * i + j];
+      }
+    }
+  }
+  __syncthreads();
+  const int row_mul = pl.m.rr * pitch + pl.m.cr * E, col_mul = pl.m.rc * pitch + pl.m.cc * E;
+  const int base = (pl.m.r0 - sr0) * pitch + (pl.m.c0 - sc0) * E;
+  const int row_bytes = pl.w * E;
+  const int tid = wid * 32 + lane;
+  const int wq = tid & (WPR - 1), b0 = c_lo * E + wq * 4;
+  if (b0 >= row_bytes) return;
+  int cterm[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int b = min(b0 + k, row_bytes - 1);
+    const int c = E == 1 ? b : (b >> 1);
+    cterm[k] = base + col_mul * c + (b - c * E);
+  }
+  const bool whole = pl.vec && b0 + 4 <= row_bytes;
+  int r = r_lo + tid / WPR;
+  uint8_t* o = pl.dst + dst_off + (long long)r * pl.dst_stride + b0;
+  const long long ostep = (long long)RSTEP * pl.dst_stride;
+  for (; r <= r_hi; r += RSTEP, o += ostep) {
+    const int rterm = row_mul * r;
+    const uint32_t v0 = stage[rterm + cterm[0]], v1 = stage[rterm + cterm[1]], v2 = stage[rterm + cterm[2]],
+                   v3 = stage[rterm + cterm[3]];
+    if (whole) {
+      *reinterpret_cast<uint32_t*>(o) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+    } else {
+      o[0] = (uint8_t)v0;
+      if (b0 + 1 < row_bytes) o[1] = (uint8_t)v1;
+      if (b0 + 2 < row_bytes) o[2] = (uint8_t)v2;
+      if (b0 + 3 < row_bytes) o[3] = (uint8_t)v3;
+    }
+  }
+}
+// Every present plane is a quarter-turn of one- or two-byte elements (4:2:0 frames, gray, UV): blockIdx.z = 3 * frame + plane
+__global__ void __launch_bounds__(256) plane_turn_kernel(const __grid_constant__ PlaneMapParams P) {
+  __shared__ uint8_t stage[64 * 129 + 64];  // 64 rows x 129 bytes
+  const PlaneMap& pl = P.pl[blockIdx.z % 3];
+  if (!pl.src) return;
+  const long long so = (long long)(blockIdx.z / 3) * P.src_step, dof = (long long)(blockIdx.z / 3) * P.dst_step;
+  if (pl.esize == 1) plane_turn_tile<1>(pl, so, dof, stage);
+  else plane_turn_tile<2>(pl, so, dof, stage);
 }
 // blockIdx.z = 3 * frame + plane
 __global__ void __launch_bounds__(256) plane_map_tile_kernel(const __grid_constant__ PlaneMapParams P) {
@@ -593,6 +692,14 @@ static int run_plane_maps(PlaneMapParams& P, int n, cudaStream_t stream) {
       return (int)cudaGetLastError();
     }
   }
+  bool turn = true;  // every present plane a quarter-turn of 1- / 2-byte elements: the large-tile kernel
+  int tx = 1, ty = 1;
+  for (int k = 0; k < 3; ++k) {
+    if (!P.pl[k].src) continue;
+    if (!plane_big_turn(P.pl[k])) turn = false;
+    tx = max(tx, (P.pl[k].w + plane_tile_w(P.pl[k]) - 1) / plane_tile_w(P.pl[k]));
+    ty = max(ty, (P.pl[k].h + plane_tile_h(P.pl[k]) - 1) / plane_tile_h(P.pl[k]));
+  }
   int gx = 1, gy = 1;
   for (int k = 0; k < 3; ++k) {
     if (!P.pl[k].src) continue;
@@ -610,7 +717,8 @@ static int run_plane_maps(PlaneMapParams& P, int n, cudaStream_t stream) {
       Q.pl[k].src += (long long)done * src_step;
       Q.pl[k].dst += (long long)done * dst_step;
     }
-    plane_map_tile_kernel<<<dim3(gx, gy, 3 * chunk), block, 0, stream>>>(Q);
+    if (turn) plane_turn_kernel<<<dim3(tx, ty, 3 * chunk), block, 0, stream>>>(Q);
+    else plane_map_tile_kernel<<<dim3(gx, gy, 3 * chunk), block, 0, stream>>>(Q);
     count_launch();
     done += chunk;
   }
