@@ -44,6 +44,11 @@ EXPORTED = [
     "BandTensorRingBufferIsHandleValid", "BandTensorRingBufferGetSlot", "BandTensorRingBufferPutTensor",
     "BandTensorRingBufferGetTensor", "BandBufferSetOrientation", "BandImageProcessorRecordBatch",
     "BandRecordedBatchReplay", "BandRecordedBatchDelete",
+    "BandImageProcessorBuilderBuildSharded", "BandShardedImageProcessorDelete", "BandShardedImageProcessorGetNumShards",
+    "BandShardedImageProcessorGetDevice", "BandShardedImageProcessorGetSlice", "BandImageProcessorProcessBatchSharded",
+    "BandImageProcessorProcessBatchShardedAsync", "BandShardedImageProcessorSynchronize",
+    "BandShardedImageProcessorGetStream", "BandShardedImageProcessorIsFused",
+    "BandHostRegistrationCacheConfigure", "BandHostRegistrationCacheStats",
 ]
 
 
@@ -125,6 +130,24 @@ def lib():
     L.BandTensorRingBufferGetSlot.restype = vp
     L.BandTensorRingBufferPutTensor.argtypes = [vp, vp, ci, ci]
     L.BandTensorRingBufferGetTensor.argtypes = [vp, vp, ci, ci]
+    L.BandImageProcessorBuilderBuildSharded.argtypes = [vp, C.POINTER(ci), sz]
+    L.BandImageProcessorBuilderBuildSharded.restype = vp
+    L.BandShardedImageProcessorDelete.argtypes = [vp]
+    L.BandShardedImageProcessorGetNumShards.argtypes = [vp]
+    L.BandShardedImageProcessorGetNumShards.restype = sz
+    L.BandShardedImageProcessorGetDevice.argtypes = [vp, sz]
+    L.BandShardedImageProcessorGetSlice.argtypes = [vp, sz, sz, C.POINTER(sz), C.POINTER(sz)]
+    L.BandShardedImageProcessorGetSlice.restype = None
+    L.BandImageProcessorProcessBatchSharded.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
+    L.BandImageProcessorProcessBatchShardedAsync.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), sz]
+    L.BandShardedImageProcessorSynchronize.argtypes = [vp]
+    L.BandShardedImageProcessorGetStream.argtypes = [vp, sz]
+    L.BandShardedImageProcessorGetStream.restype = vp
+    L.BandShardedImageProcessorIsFused.argtypes = [vp, sz]
+    L.BandHostRegistrationCacheConfigure.argtypes = [ci, sz]
+    L.BandHostRegistrationCacheStats.argtypes = [C.POINTER(sz), C.POINTER(sz), C.POINTER(C.c_ulonglong),
+                                                 C.POINTER(C.c_ulonglong)]
+    L.BandHostRegistrationCacheStats.restype = None
     _lib = L
     return L
 
@@ -365,6 +388,85 @@ class ImageProcessor:
             self.close()
         except Exception:
             pass
+
+
+class ShardedImageProcessor:
+    """BandImageProcessorBuilderBuildSharded: one processor (plans, streams, host thread) per device; a batch is
+    cut into contiguous slices, one per shard, by ONE call. devices=None: every visible GPU."""
+
+    def __init__(self, ops, devices=None):
+        L = lib()
+        builder = L.BandImageProcessorBuilderCreate()
+        try:
+            for op in ops:
+                if add_operator(builder, op[0], *op[1:]) != kBandOk:
+                    raise BandError("BandAddOperator rejected %r" % (op,))
+            if devices is None:
+                self.handle = L.BandImageProcessorBuilderBuildSharded(builder, None, 0)
+            else:
+                arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+                self.handle = L.BandImageProcessorBuilderBuildSharded(builder, arr, len(devices))
+        finally:
+            L.BandImageProcessorBuilderDelete(builder)
+        if not self.handle:
+            raise BandError("BandImageProcessorBuilderBuildSharded failed: %s" % last_error())
+
+    @property
+    def num_shards(self):
+        return int(lib().BandShardedImageProcessorGetNumShards(self.handle))
+
+    def device_of(self, shard):
+        return int(lib().BandShardedImageProcessorGetDevice(self.handle, shard))
+
+    def slice_of(self, count, shard):
+        b, e = C.c_size_t(), C.c_size_t()
+        lib().BandShardedImageProcessorGetSlice(self.handle, count, shard, C.byref(b), C.byref(e))
+        return int(b.value), int(e.value)
+
+    def process_batch(self, buffers, tensors):
+        n = len(buffers)
+        ba = (C.c_void_p * n)(*[b.handle for b in buffers])
+        ta = (C.c_void_p * n)(*[t.handle for t in tensors])
+        return lib().BandImageProcessorProcessBatchSharded(self.handle, ba, ta, n)
+
+    def process_batch_handles(self, buffer_array, tensor_array, n):
+        return lib().BandImageProcessorProcessBatchSharded(self.handle, buffer_array, tensor_array, n)
+
+    def process_batch_async(self, buffer_array, tensor_array, n):
+        return lib().BandImageProcessorProcessBatchShardedAsync(self.handle, buffer_array, tensor_array, n)
+
+    def synchronize(self):
+        return lib().BandShardedImageProcessorSynchronize(self.handle)
+
+    def stream(self, shard):
+        return lib().BandShardedImageProcessorGetStream(self.handle, shard)
+
+    def is_fused(self, shard):
+        return bool(lib().BandShardedImageProcessorIsFused(self.handle, shard))
+
+    def close(self):
+        if self.handle:
+            lib().BandShardedImageProcessorDelete(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def host_registration_cache(enable, max_bytes=0):
+    """BandHostRegistrationCacheConfigure: processors built afterwards register pageable frames on first sight."""
+    return lib().BandHostRegistrationCacheConfigure(1 if enable else 0, int(max_bytes))
+
+
+def host_registration_stats():
+    b, e = C.c_size_t(), C.c_size_t()
+    h, r = C.c_ulonglong(), C.c_ulonglong()
+    lib().BandHostRegistrationCacheStats(C.byref(b), C.byref(e), C.byref(h), C.byref(r))
+    return {"registered_bytes": int(b.value), "entries": int(e.value), "hits": int(h.value),
+            "registrations": int(r.value)}
 
 
 def frame_bytes(width, height, fmt):

@@ -2,6 +2,8 @@
 // (/root/reference/band/buffer/buffer_processor.cc:22-64).
 #include "band/buffer/buffer_processor.h"
 
+#include <algorithm>
+
 #include "band/buffer/buffer.h"
 #include "band/buffer/fused_plan.h"
 #include "band/logger.h"
@@ -14,8 +16,16 @@ BufferProcessor::BufferProcessor(std::vector<IBufferOperator*> operations) : ope
   for (IBufferOperator* op : operations_) op->virtual_outputs_ = true;
 }
 
+RecordedBatch::~RecordedBatch() {
+  if (graph_exec) {
+    if (plan) (void)plan->Synchronize();  // a replay may still be running on the plan's stream
+    bandcu_graph_destroy(graph_exec);
+  }
+}
+
 BufferProcessor::~BufferProcessor() {
   plan_.reset();
+  plans_.clear();
   for (IBufferOperator* op : operations_) delete op;
 }
 
@@ -38,11 +48,16 @@ absl::Status BufferProcessor::Prepare(const Buffer& input, Buffer& output) {
   }
 
   const cuda::ImageLayout in = cuda::ImageLayout::Of(input);
-  if (plan_ && plan_->input_layout() == in &&
-      (!plan_->writes_output() || plan_->output_layout() == cuda::ImageLayout::Of(output)))
-    return absl::OkStatus();
+  const cuda::ImageLayout out = cuda::ImageLayout::Of(output);
+  for (size_t i = 0; i < plans_.size(); ++i) {
+    const std::shared_ptr<cuda::FusedPlan>& p = plans_[i];
+    if (p->input_layout() == in && (!p->writes_output() || p->output_layout() == out)) {
+      plan_ = p;
+      if (i != 0) std::rotate(plans_.begin(), plans_.begin() + i, plans_.begin() + i + 1);
+      return absl::OkStatus();
+    }
+  }
 
-  plan_.reset();
   cuda::ChainLowering lowering(input);
   next_input = &input;
   for (IBufferOperator* op : operations_) {
@@ -59,6 +74,11 @@ absl::Status BufferProcessor::Prepare(const Buffer& input, Buffer& output) {
     return plan.status();
   }
   plan_ = std::move(plan).value();
+  if (plans_.size() >= kPlanCacheSize) {
+    // the evicted plan may still have an asynchronous pass in flight: its destructor drains its streams
+    plans_.pop_back();
+  }
+  plans_.insert(plans_.begin(), plan_);
   return absl::OkStatus();
 }
 
@@ -91,8 +111,8 @@ absl::Status BufferProcessor::ProcessBatchAsync(const Buffer* const* inputs, Buf
   return status;
 }
 
-absl::Status BufferProcessor::RecordBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n,
-                                          void** graph_exec) {
+absl::StatusOr<std::unique_ptr<RecordedBatch>> BufferProcessor::RecordBatch(const Buffer* const* inputs,
+                                                                            Buffer* const* outputs, size_t n) {
   if (n == 0 || inputs == nullptr || outputs == nullptr || inputs[0] == nullptr || outputs[0] == nullptr)
     return absl::InvalidArgumentError("RecordBatch: null buffer list");
   for (size_t f = 0; f < n; ++f) {
@@ -102,23 +122,33 @@ absl::Status BufferProcessor::RecordBatch(const Buffer* const* inputs, Buffer* c
       return absl::InvalidArgumentError("RecordBatch: frames and outputs must be device-resident or pinned host memory");
   }
   RETURN_IF_ERROR(Prepare(*inputs[0], *outputs[0]));
-  absl::Status status = plan_->Record(inputs, outputs, static_cast<int>(n), graph_exec);
-  if (!status.ok()) BAND_LOG(LogSeverity::kError, "BufferProcessor::RecordBatch failed %s", status.ToString().c_str());
-  return status;
+  std::unique_ptr<RecordedBatch> recorded(new RecordedBatch());
+  recorded->plan = plan_;
+  absl::Status status = plan_->Record(inputs, outputs, static_cast<int>(n), &recorded->graph_exec);
+  if (!status.ok()) {
+    BAND_LOG(LogSeverity::kError, "BufferProcessor::RecordBatch failed %s", status.ToString().c_str());
+    return status;
+  }
+  return recorded;
 }
 
-absl::Status BufferProcessor::ReplayBatch(void* graph_exec, bool synchronize) {
-  if (!plan_ || graph_exec == nullptr) return absl::InvalidArgumentError("ReplayBatch: nothing recorded");
-  if (bandcu_graph_launch(graph_exec, plan_->ComputeStream()) != BANDCU_OK)
-    return absl::InternalError(bandcu_last_error_string());
-  if (synchronize && bandcu_stream_sync(plan_->ComputeStream()) != BANDCU_OK)
-    return absl::InternalError(bandcu_last_error_string());
+absl::Status BufferProcessor::ReplayBatch(RecordedBatch& recorded, bool synchronize) {
+  if (!recorded.plan || recorded.graph_exec == nullptr) return absl::InvalidArgumentError("ReplayBatch: nothing recorded");
+  void* stream = recorded.plan->ComputeStream();
+  if (bandcu_graph_launch(recorded.graph_exec, stream) != BANDCU_OK) return absl::InternalError(bandcu_last_error_string());
+  if (synchronize && bandcu_stream_sync(stream) != BANDCU_OK) return absl::InternalError(bandcu_last_error_string());
   return absl::OkStatus();
 }
 
-void BufferProcessor::ReleaseRecordedBatch(void* graph_exec) { bandcu_graph_destroy(graph_exec); }
-
-absl::Status BufferProcessor::Synchronize() { return plan_ ? plan_->Synchronize() : absl::OkStatus(); }
+absl::Status BufferProcessor::Synchronize() {
+  // every cached plan: asynchronous calls on alternating layouts leave work on more than one plan's streams
+  absl::Status first = absl::OkStatus();
+  for (const std::shared_ptr<cuda::FusedPlan>& p : plans_) {
+    absl::Status s = p->Synchronize();
+    if (first.ok() && !s.ok()) first = s;
+  }
+  return first;
+}
 void* BufferProcessor::GetComputeStream() const { return plan_ ? plan_->ComputeStream() : nullptr; }
 
 size_t BufferProcessor::GetNumLaunchSegments() const { return plan_ ? plan_->NumSegments() : 0; }

@@ -42,6 +42,16 @@ class IBufferProcessorBuilder {
   std::vector<std::unique_ptr<IBufferOperator>> operations_;
 };
 
+// Additive: one batch recorded into a CUDA graph (BufferProcessor::RecordBatch). The graph's kernels read plan-owned
+// device memory (Normalize table, scratch images, pointers resolved at record time), so the recording keeps its plan
+// alive -- the processor may since have compiled plans for other layouts, or be gone. The recorded frames and
+// outputs must stay where they are and outlive the recording.
+struct RecordedBatch {
+  ~RecordedBatch();
+  std::shared_ptr<cuda::FusedPlan> plan;
+  void* graph_exec = nullptr;
+};
+
 // Not re-entrant (like the reference: Process mutates operator state); use one
 // processor per thread and per GPU.
 class BufferProcessor {
@@ -54,11 +64,11 @@ class BufferProcessor {
   // Additive: enqueue only; results are complete after Synchronize(). The buffers must stay alive until then.
   virtual absl::Status ProcessBatchAsync(const Buffer* const* inputs, Buffer* const* outputs, size_t n);
   absl::Status Synchronize();
-  // Additive: record one batch into a CUDA graph (cuda::FusedPlan::Record); *graph_exec is replayed with ReplayBatch
-  // and released with ReleaseRecordedBatch. Frames and outputs must be device-resident (or pinned) and stay in place.
-  absl::Status RecordBatch(const Buffer* const* inputs, Buffer* const* outputs, size_t n, void** graph_exec);
-  absl::Status ReplayBatch(void* graph_exec, bool synchronize = true);
-  static void ReleaseRecordedBatch(void* graph_exec);
+  // Additive: record one batch into a CUDA graph (cuda::FusedPlan::Record), replayed with ReplayBatch. Frames and
+  // outputs must be device-resident (or pinned with the zero-copy conditions met) and stay in place.
+  absl::StatusOr<std::unique_ptr<RecordedBatch>> RecordBatch(const Buffer* const* inputs, Buffer* const* outputs,
+                                                             size_t n);
+  static absl::Status ReplayBatch(RecordedBatch& recorded, bool synchronize = true);
   // CUDA stream the fused launches go to (nullptr before the first Process*); for event timing.
   void* GetComputeStream() const;
   // Additive introspection for tests / benchmarks.
@@ -76,7 +86,11 @@ class BufferProcessor {
   absl::Status Prepare(const Buffer& input, Buffer& output);
 
   std::vector<IBufferOperator*> operations_;
-  std::unique_ptr<cuda::FusedPlan> plan_;
+  // compiled plans, most recently used first: a processor fed alternating layouts (two camera formats, a frame and a
+  // thumbnail) re-lowers nothing. plan_ is the one the current call runs.
+  static constexpr size_t kPlanCacheSize = 4;
+  std::vector<std::shared_ptr<cuda::FusedPlan>> plans_;
+  std::shared_ptr<cuda::FusedPlan> plan_;
 };
 }  // namespace band
 

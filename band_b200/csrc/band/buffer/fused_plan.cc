@@ -166,6 +166,12 @@ struct ChainLowering::View {
 // ---------------------------------------------------------------------------
 ChainLowering::ChainLowering(const Buffer& input) : plan_(new FusedPlan()), view_(new View()) {
   plan_->input_ = ImageLayout::Of(input);
+  // diagnostic switches are sampled here, once per plan: nothing on the launch path reads the environment
+  plan_->zero_copy_allowed_ = getenv("BAND_NO_ZERO_COPY") == nullptr;
+  if (const char* c = getenv("BAND_CHUNK_FRAMES"))
+    if (atoi(c) > 0) plan_->chunk_frames_ = atoi(c);
+  plan_->register_host_ = HostRegistry::Get().Enabled();
+  if (plan_->register_host_) HostRegistry::Get().AddUser();
   ResetView(kSlotInput, plan_->input_);
 }
 
@@ -559,6 +565,7 @@ absl::StatusOr<std::unique_ptr<FusedPlan>> ChainLowering::Finish(const Buffer* o
 namespace {
 
 constexpr size_t kAlign = 256;
+constexpr int kMaxPassFrames = 2048;  // frames per pass: bounds the staging areas
 size_t AlignUp(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 
 // Bytes a plane occupies from its first to its last addressed byte.
@@ -576,8 +583,9 @@ size_t PlaneExtent(const ImageLayout& l, int k) {
   return static_cast<size_t>(l.height - 1) * stride + row;
 }
 
-// Host byte ranges of one frame, overlapping / neighbouring planes merged (an
-// NV12 frame from CreateFromRaw is one range; Android Image.Planes may be three).
+// Host byte ranges of one frame; planes that overlap or touch are merged (an NV12 frame from CreateFromRaw is
+// one range; Android Image.Planes may be three). Planes that merely sit NEAR each other stay separate: the bytes
+// between them belong to the caller (and may be unmapped).
 struct HostRanges {
   int count = 0;
   const unsigned char* lo[3] = {nullptr, nullptr, nullptr};
@@ -604,7 +612,7 @@ HostRanges RangesOf(const Buffer& b, const ImageLayout& l) {
     if (r.count > 0) {
       const int c = r.count - 1;
       const unsigned char* cur_hi = r.lo[c] + r.bytes[c];
-      if (lo <= cur_hi + 4096) {  // overlaps or nearly touches: one copy
+      if (lo <= cur_hi) {  // overlaps or is exactly adjacent: one copy
         if (hi > cur_hi) r.bytes[c] = static_cast<size_t>(hi - r.lo[c]);
         r.range_of_plane[k] = c;
         continue;
@@ -614,6 +622,59 @@ HostRanges RangesOf(const Buffer& b, const ImageLayout& l) {
     r.bytes[r.count] = static_cast<size_t>(hi - lo);
     r.range_of_plane[k] = r.count;
     ++r.count;
+  }
+  return r;
+}
+
+// The bytes of a frame an operator chain may WRITE: per plane `rows` rows of `row_bytes` bytes, `stride` apart.
+// libyuv writes `width` bytes per row and nothing else (row padding, gaps between planes and the bytes between the
+// samples of a pixel-strided plane stay the caller's), so downloads into host images copy exactly these rectangles.
+struct PlaneRects {
+  int count = 0;
+  const unsigned char* lo[3] = {nullptr, nullptr, nullptr};
+  size_t row_bytes[3] = {0, 0, 0}, stride[3] = {0, 0, 0}, rows[3] = {0, 0, 0};
+  bool exact = true;  // false: a plane whose written bytes are not whole row segments (split pixel-stride-2 chroma)
+  // every rectangle is unpadded and they sit back to back: the frame is one contiguous block of written bytes
+  bool Dense() const {
+    if (!exact) return false;
+    for (int i = 0; i < count; ++i) {
+      if (rows[i] > 1 && stride[i] != row_bytes[i]) return false;
+      if (i > 0 && lo[i] != lo[i - 1] + rows[i - 1] * row_bytes[i - 1]) return false;
+    }
+    return true;
+  }
+};
+
+PlaneRects RectsOf(const Buffer& b, const ImageLayout& l) {
+  PlaneRects r;
+  auto add = [&](const unsigned char* lo, size_t row_bytes, size_t stride, size_t rows) {
+    r.lo[r.count] = lo; r.row_bytes[r.count] = row_bytes; r.stride[r.count] = stride; r.rows[r.count] = rows;
+    ++r.count;
+  };
+  if (Buffer::IsYUV(l.format) && l.num_planes == 3) {
+    const size_t cw = (static_cast<size_t>(l.width) + 1) / 2, ch = (static_cast<size_t>(l.height) + 1) / 2;
+    add(b[0].data, l.width, l.row_stride[0], l.height);
+    if (l.pixel_stride[1] == 1 && l.pixel_stride[2] == 1) {
+      const int first = b[1].data <= b[2].data ? 1 : 2;
+      add(b[first].data, cw, l.row_stride[first], ch);
+      add(b[3 - first].data, cw, l.row_stride[3 - first], ch);
+    } else if (l.pixel_stride[1] == 2 && l.pixel_stride[2] == 2 && l.row_stride[1] == l.row_stride[2] &&
+               (b[1].data + 1 == b[2].data || b[2].data + 1 == b[1].data)) {
+      add(std::min(b[1].data, b[2].data), 2 * cw, l.row_stride[1], ch);  // interleaved pairs
+    } else {
+      r.exact = false;
+    }
+    return r;
+  }
+  const size_t ch = Channels(l.format), esz = GetDataTypeBytes(l.dtype);
+  if (l.format == BufferFormat::kRaw) {
+    add(b[0].data, l.row_stride[0], l.row_stride[0], 1);
+  } else if (l.dtype != DataType::kUInt8) {  // contiguous tensor (strides ignored like the reference)
+    const size_t total = static_cast<size_t>(l.width) * l.height * ch * esz;
+    add(b[0].data, total, total, 1);
+  } else {
+    const size_t row = static_cast<size_t>(l.width) * ch;
+    add(b[0].data, row, l.row_stride[0] >= row ? l.row_stride[0] : row, l.height);
   }
   return r;
 }
@@ -640,6 +701,9 @@ SlotPointers StagedPointers(const Buffer& b, const ImageLayout& l, const HostRan
 }  // namespace
 
 FusedPlan::~FusedPlan() {
+  if (stream_) (void)Synchronize();
+  ReleaseHeldHost();
+  if (register_host_) HostRegistry::Get().RemoveUser();
   for (Segment& s : segments_) {
     if (s.plan) bandcu_plan_destroy(s.plan);
     for (BandCuPlan* p : s.plane_plan)
@@ -664,7 +728,28 @@ absl::Status FusedPlan::Synchronize() {
   if (bandcu_stream_sync(stream_) != BANDCU_OK) return CudaError("stream sync");
   if (bandcu_stream_sync(copy_out_) != BANDCU_OK) return CudaError("stream sync");
   in_flight_ = false;
+  ReleaseHeldHost();
   return absl::OkStatus();
+}
+
+bool FusedPlan::HostFrameIsMapped(const Buffer& frame) {
+  if (frame.IsPinnedHost()) return true;
+  if (!register_host_) return false;
+  const HostRanges r = RangesOf(frame, input_);
+  const size_t first = held_host_.size();
+  for (int i = 0; i < r.count; ++i) {
+    if (!HostRegistry::Get().Acquire(r.lo[i], r.bytes[i], &held_host_)) {
+      std::vector<HostRegistry::Entry*> undo(held_host_.begin() + first, held_host_.end());
+      held_host_.resize(first);
+      HostRegistry::Get().Release(&undo);
+      return false;
+    }
+  }
+  return true;
+}
+
+void FusedPlan::ReleaseHeldHost() {
+  if (!held_host_.empty()) HostRegistry::Get().Release(&held_host_);
 }
 
 absl::Status FusedPlan::Record(const Buffer* const* inputs, Buffer* const* outputs, int n, void** graph_exec) {
@@ -673,6 +758,11 @@ absl::Status FusedPlan::Record(const Buffer* const* inputs, Buffer* const* outpu
   // one ordinary pass first: it creates the streams, sizes every plan-owned allocation and proves the batch valid,
   // so that the recorded pass consists of kernel launches only
   RETURN_IF_ERROR(Run(inputs, outputs, n, /*synchronize=*/true));
+  if (last_pass_staged_)
+    return absl::InvalidArgumentError(
+        "RecordBatch: this batch moves through staging copies (pageable or unaligned host memory, or a chain that is not "
+        "one row-staged launch over pinned frames); record device-resident frames and tensors instead");
+  if (n > kMaxPassFrames) return absl::InvalidArgumentError("RecordBatch: more frames than one pass holds");
   if (bandcu_stream_begin_capture(stream_) != BANDCU_OK) return CudaError("bandcu_stream_begin_capture");
   absl::Status st = Run(inputs, outputs, n, /*synchronize=*/false);
   void* exec = nullptr;
@@ -855,8 +945,6 @@ bool UniformStep(const std::vector<HostRanges>& r, size_t* step) {
   *step = static_cast<size_t>(d);
   return true;
 }
-constexpr int kChunkFrames = 32;   // frames per upload/compute/download pipeline stage
-constexpr int kMaxPassFrames = 2048;
 }  // namespace
 
 absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host,
@@ -864,18 +952,19 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   // Zero-copy input: a chain that lowers to the single staged launch reads every needed source row exactly
   // once, through the TMA engine. When the frames sit in PINNED host memory (mapped into the device address
   // space under UVA) the kernel pulls those rows straight over PCIe: rows the resize never samples never
-  // cross the bus and there is no staging copy at all. Pageable frames are staged through HBM as before.
+  // cross the bus and there is no staging copy at all. Pageable frames are staged through HBM as before
+  // (or registered on first sight when the plan's registration cache is on, see HostRegistry).
   const bool reads_in_place = segments_.size() == 1 && segments_[0].kind == Segment::Kind::kPixel && segments_[0].plan &&
                               bandcu_plan_staging_kind(segments_[0].plan) == 1;  // the row-staged kernel only: the tile-staged
   // kernel's ~150-byte row fragments are poor PCIe reads (measured on C3: 2.4 K frames/s in place vs 3.8 K staged)
-  bool zero_copy = in_host && !writes_input_ && reads_in_place && getenv("BAND_NO_ZERO_COPY") == nullptr;
+  bool zero_copy = in_host && !writes_input_ && reads_in_place && zero_copy_allowed_;
   for (int f = 0; zero_copy && f < m; ++f)
-    if (!inputs[f]->IsPinnedHost()) zero_copy = false;
+    if (!HostFrameIsMapped(*inputs[f])) zero_copy = false;
   const bool in_staged = in_host && !zero_copy;
   // Zero-copy output: the staged kernel assembles rows in shared memory and pushes them into PINNED host tensors
   // with bulk stores, so results cross PCIe while the next source rows are being pulled (both directions of the
   // link busy at once) and neither a staging buffer nor a D2H copy exists. Needs 16-byte granularity.
-  bool zc_out = out_host && writes_output_ && IsSingleFastLaunch() && getenv("BAND_NO_ZERO_COPY") == nullptr &&
+  bool zc_out = out_host && writes_output_ && IsSingleFastLaunch() && zero_copy_allowed_ &&
                 output_.num_planes == 1 && output_.row_stride[0] % 16 == 0 &&
                 (static_cast<size_t>(segments_[0].pixel.dst_width) * segments_[0].pixel.channels *
                  GetDataTypeBytes(output_.dtype)) % 16 == 0;
@@ -887,8 +976,10 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
     return CudaError("bandcu_plan_set_host_output");
   if (zc_out) out_host = false;  // from here on the tensors are addressed like device memory
   std::vector<HostRanges> in_r, out_r;
+  std::vector<PlaneRects> out_rect;
   size_t in_step = 0, out_step = 0;
   bool in_uniform = false, out_uniform = false;
+  bool out_preload = false;  // some output's written bytes are not whole row segments: keep the caller's bytes around them
   if (in_staged) {
     in_r.reserve(m);
     for (int f = 0; f < m; ++f) in_r.push_back(RangesOf(*inputs[f], input_));
@@ -897,11 +988,20 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
       for (const HostRanges& r : in_r) in_step = std::max(in_step, r.Total());
     }
   }
-  if (out_host && writes_output_) {
+  const bool out_staged = out_host && writes_output_;
+  if (out_staged) {
     out_r.reserve(m);
-    for (int f = 0; f < m; ++f) out_r.push_back(RangesOf(*outputs[f], output_));
-    out_uniform = UniformStep(out_r, &out_step);
+    out_rect.reserve(m);
+    bool dense = true;
+    for (int f = 0; f < m; ++f) {
+      out_r.push_back(RangesOf(*outputs[f], output_));
+      out_rect.push_back(RectsOf(*outputs[f], output_));
+      if (!out_rect.back().Dense()) dense = false;
+      if (!out_rect.back().exact) out_preload = true;
+    }
+    out_uniform = dense && UniformStep(out_r, &out_step);
     if (!out_uniform) {
+      out_step = 0;
       for (const HostRanges& r : out_r) out_step = std::max(out_step, r.Total());
     }
   }
@@ -915,18 +1015,29 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
       out_ptrs_[f] = out_host ? StagedPointers(*outputs[f], output_, out_r[f], out_stage_ + out_step * f)
                               : BufferPointers(*outputs[f]);
   }
-  const bool download = (out_host && writes_output_) || (in_staged && writes_input_);
+  // device address, inside frame f's output staging area, of the host output byte `p`
+  auto staged_out = [&](int f, const unsigned char* p) -> unsigned char* {
+    size_t off = 0;
+    const HostRanges& r = out_r[f];
+    for (int i = 0; i < r.count; ++i) {
+      if (p >= r.lo[i] && p < r.lo[i] + r.bytes[i]) return out_stage_ + out_step * f + off + (p - r.lo[i]);
+      off += AlignUp(r.bytes[i]);
+    }
+    return nullptr;
+  };
+  const bool download = out_staged || (in_staged && writes_input_);
   const bool staged = in_staged || download;
-  int chunk = staged ? kChunkFrames : m;
-  if (const char* c = getenv("BAND_CHUNK_FRAMES")) { if (staged && atoi(c) > 0) chunk = atoi(c); }
+  last_pass_staged_ = staged;
+  const int chunk = staged ? chunk_frames_ : m;
   size_t ev = 0;
   if (staged && in_flight_) {
     // an earlier asynchronous pass may still use the staging areas: its kernels read in_stage_, its
-    // downloads read out_stage_
+    // downloads read out_stage_ (and in_stage_ when an in-place stage wrote the staged input back)
     if (!fence_a_ && bandcu_event_create_sync(&fence_a_) != BANDCU_OK) return CudaError("fence event");
     if (!fence_b_ && bandcu_event_create_sync(&fence_b_) != BANDCU_OK) return CudaError("fence event");
     if (bandcu_event_record(fence_a_, stream_) != BANDCU_OK || bandcu_stream_wait_event(copy_in_, fence_a_) != BANDCU_OK ||
-        bandcu_event_record(fence_b_, copy_out_) != BANDCU_OK || bandcu_stream_wait_event(stream_, fence_b_) != BANDCU_OK)
+        bandcu_event_record(fence_b_, copy_out_) != BANDCU_OK || bandcu_stream_wait_event(stream_, fence_b_) != BANDCU_OK ||
+        bandcu_stream_wait_event(copy_in_, fence_b_) != BANDCU_OK)
       return CudaError("fence");
   }
   for (int a = 0; a < m; a += chunk) {
@@ -946,6 +1057,18 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
           }
         }
       }
+    }
+    if (out_preload) {  // the staging image starts as a copy of the caller's bytes, so a whole-range download restores them
+      for (int f = a; f < b; ++f) {
+        size_t off = 0;
+        for (int i = 0; i < out_r[f].count; ++i) {
+          if (bandcu_memcpy_h2d(out_stage_ + out_step * f + off, out_r[f].lo[i], out_r[f].bytes[i], copy_in_) != BANDCU_OK)
+            return CudaError("upload");
+          off += AlignUp(out_r[f].bytes[i]);
+        }
+      }
+    }
+    if (in_staged || out_preload) {
       void* e = Event(ev++);
       if (!e || bandcu_event_record(e, copy_in_) != BANDCU_OK || bandcu_stream_wait_event(stream_, e) != BANDCU_OK)
         return CudaError("upload event");
@@ -955,7 +1078,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
       void* e = Event(ev++);
       if (!e || bandcu_event_record(e, stream_) != BANDCU_OK || bandcu_stream_wait_event(copy_out_, e) != BANDCU_OK)
         return CudaError("compute event");
-      if (out_host && writes_output_) {
+      if (out_staged) {
         if (out_uniform) {
           const size_t bytes = out_step * (b - a - 1) + out_r[a].bytes[0];
           if (bandcu_memcpy_d2h(const_cast<unsigned char*>(out_r[a].lo[0]), out_stage_ + out_step * a, bytes,
@@ -963,12 +1086,24 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
             return CudaError("download");
         } else {
           for (int f = a; f < b; ++f) {
-            size_t off = 0;
-            for (int i = 0; i < out_r[f].count; ++i) {
-              if (bandcu_memcpy_d2h(const_cast<unsigned char*>(out_r[f].lo[i]), out_stage_ + out_step * f + off,
-                                    out_r[f].bytes[i], copy_out_) != BANDCU_OK)
+            const PlaneRects& pr = out_rect[f];
+            if (pr.Dense() || !pr.exact) {  // whole ranges: nothing but written (or preloaded) bytes inside
+              size_t off = 0;
+              for (int i = 0; i < out_r[f].count; ++i) {
+                if (bandcu_memcpy_d2h(const_cast<unsigned char*>(out_r[f].lo[i]), out_stage_ + out_step * f + off,
+                                      out_r[f].bytes[i], copy_out_) != BANDCU_OK)
+                  return CudaError("download");
+                off += AlignUp(out_r[f].bytes[i]);
+              }
+              continue;
+            }
+            // padded rows / planes with gaps: exactly the row segments the chain writes, pitch to pitch
+            for (int i = 0; i < pr.count; ++i) {
+              unsigned char* src = staged_out(f, pr.lo[i]);
+              if (!src) return absl::InternalError("output plane outside its staging range");
+              if (bandcu_memcpy2d_d2h(const_cast<unsigned char*>(pr.lo[i]), pr.stride[i], src, pr.stride[i],
+                                      pr.row_bytes[i], pr.rows[i], copy_out_) != BANDCU_OK)
                 return CudaError("download");
-              off += AlignUp(out_r[f].bytes[i]);
             }
           }
         }
@@ -991,6 +1126,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   if (bandcu_stream_sync(stream_) != BANDCU_OK) return CudaError("stream sync");
   if (download && bandcu_stream_sync(copy_out_) != BANDCU_OK) return CudaError("stream sync");
   in_flight_ = false;
+  ReleaseHeldHost();
   return absl::OkStatus();
 }
 
@@ -1020,13 +1156,20 @@ absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs,
 }
 
 absl::Status RunSingleOperator(IBufferOperator& op, const Buffer& input) {
-  ChainLowering lowering(input);
-  RETURN_IF_ERROR(lowering.LowerNested(op, input));
-  absl::StatusOr<std::unique_ptr<FusedPlan>> plan = lowering.Finish(op.GetOutput());
-  if (!plan.ok()) return plan.status();
-  const Buffer* in = &input;
   Buffer* out = op.GetOutput();
-  return plan.value()->Run(&in, &out, 1);
+  std::shared_ptr<FusedPlan>& cached = op.single_plan_;
+  const bool reusable = cached && cached->input_layout() == ImageLayout::Of(input) &&
+                        (!cached->writes_output() || (out && cached->output_layout() == ImageLayout::Of(*out)));
+  if (!reusable) {
+    cached.reset();
+    ChainLowering lowering(input);
+    RETURN_IF_ERROR(lowering.LowerNested(op, input));
+    absl::StatusOr<std::unique_ptr<FusedPlan>> plan = lowering.Finish(out);
+    if (!plan.ok()) return plan.status();
+    cached = std::move(plan).value();
+  }
+  const Buffer* in = &input;
+  return cached->Run(&in, &out, 1);
 }
 
 absl::Status SetDevice(int device) {

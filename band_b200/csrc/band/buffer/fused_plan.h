@@ -21,6 +21,7 @@
 #include "absl/status/status.h"
 #include "absl/status/statusor.h"
 #include "band/buffer/buffer.h"
+#include "band/buffer/host_registry.h"
 #include "band/buffer/scale_dispatch.h"
 #include "bandcu.h"
 
@@ -84,7 +85,9 @@ class FusedPlan {
   absl::Status Synchronize();
   // Records one Run() over DEVICE-resident (or pinned, zero-copy) frames into a CUDA graph and returns the executable
   // graph (bandcu_graph_launch / bandcu_graph_destroy). Replaying it costs one graph launch: no validation, no pointer
-  // resolution, no per-segment launch calls. The frames and outputs must stay where they are while the graph is used.
+  // resolution, no per-segment launch calls. The frames and outputs must stay where they are while the graph is used,
+  // and the graph reads plan-owned device memory (Normalize table, scratch images): whoever keeps the graph keeps a
+  // shared_ptr to this plan (band::RecordedBatch). A batch that would be staged through copies is refused.
   absl::Status Record(const Buffer* const* inputs, Buffer* const* outputs, int n, void** graph_exec);
   // The stream the kernels are launched on (created on first use); for CUDA-event timing by harnesses.
   void* ComputeStream();
@@ -103,6 +106,9 @@ class FusedPlan {
   absl::Status RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host, bool out_host,
                        bool synchronize);
   absl::Status RunSegments(int first, int last);
+  // the frame's planes are device-readable in place: pinned memory, or registered through the HostRegistry now
+  bool HostFrameIsMapped(const Buffer& frame);
+  void ReleaseHeldHost();
   SlotPointers Resolve(int slot, int frame) const;
   void* Event(size_t index);
 
@@ -131,6 +137,12 @@ class FusedPlan {
   void* fence_a_ = nullptr;  // orders a new pass's uploads after the previous pass's kernels
   void* fence_b_ = nullptr;  // orders a new pass's kernels after the previous pass's downloads
   bool in_flight_ = false;   // an unsynchronised pass may still be running
+  bool last_pass_staged_ = false;  // the last RunPass moved frames or results through staging copies
+  // environment switches, read ONCE when the plan is created (never on the launch path)
+  bool zero_copy_allowed_ = true;  // BAND_NO_ZERO_COPY
+  int chunk_frames_ = 32;          // BAND_CHUNK_FRAMES: frames per upload/compute/download pipeline stage
+  bool register_host_ = false;     // HostRegistry was on when the plan was created
+  std::vector<HostRegistry::Entry*> held_host_;  // registered ranges the passes in flight read
 };
 
 // Walks an operator chain and emits segments. Operators call the stage
@@ -169,7 +181,8 @@ class ChainLowering {
   bool terminal_noop_ = false;
 };
 
-// IBufferOperator::ProcessImpl for every operator: compile + run a one-stage chain.
+// IBufferOperator::ProcessImpl for every operator: compile + run a one-stage chain. The compiled plan stays with the
+// operator instance and is reused while the input and output layouts repeat.
 absl::Status RunSingleOperator(IBufferOperator& op, const Buffer& input);
 
 // Additive process-wide knobs of the GPU backing (the reference has no device notion).

@@ -11,6 +11,7 @@ IBufferOperator::IBufferOperator(const IBufferOperator&) {}
 IBufferOperator::IBufferOperator(IBufferOperator&&) {}
 IBufferOperator& IBufferOperator::operator=(const IBufferOperator&) {
   owned_output_.reset();
+  single_plan_.reset();
   output_ = nullptr;
   output_assigned_ = false;
   return *this;

@@ -14,8 +14,11 @@
 #include "band/buffer/buffer.h"
 
 namespace band {
+class IBufferOperator;
 namespace cuda {
 class ChainLowering;
+class FusedPlan;
+absl::Status RunSingleOperator(IBufferOperator& op, const Buffer& input);
 }
 
 class IBufferOperator {
@@ -50,6 +53,7 @@ class IBufferOperator {
   friend class ImageProcessorBuilder;
   friend class BufferProcessor;
   friend class cuda::ChainLowering;
+  friend absl::Status cuda::RunSingleOperator(IBufferOperator& op, const Buffer& input);
 
   virtual absl::Status ProcessImpl(const Buffer& input);
   virtual IBufferOperator* Clone() const = 0;
@@ -71,6 +75,8 @@ class IBufferOperator {
   bool virtual_outputs_ = false;
   Buffer* output_ = nullptr;              // assigned (not owned) or == owned_output_.get()
   std::unique_ptr<Buffer> owned_output_;  // created by CreateOutput
+  // stand-alone Process(): the compiled one-operator plan, kept while the layouts repeat (never copied with the operator)
+  std::shared_ptr<cuda::FusedPlan> single_plan_;
 };
 }  // namespace band
 

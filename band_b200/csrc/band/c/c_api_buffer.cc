@@ -48,6 +48,8 @@ thread_local std::string g_last_error;
 
 }  // namespace
 
+void BandSetLastError(const char* message) { g_last_error = message ? message : ""; }
+
 extern "C" {
 
 BandBuffer* BandBufferCreate() { return new BandBuffer(); }
@@ -223,8 +225,8 @@ BandStatus BandImageProcessorProcessBatchAsync(BandImageProcessor* image_process
 }
 
 struct BandRecordedBatch {
-  band::BufferProcessor* processor = nullptr;  // not owned
-  void* graph_exec = nullptr;
+  // graph + the plan whose device memory the graph reads (kept alive here, whatever the processor does afterwards)
+  std::unique_ptr<band::RecordedBatch> impl;
 };
 
 BandRecordedBatch* BandImageProcessorRecordBatch(BandImageProcessor* image_processor, BandBuffer* const* buffers,
@@ -244,15 +246,14 @@ BandRecordedBatch* BandImageProcessorRecordBatch(BandImageProcessor* image_proce
     out[i] = target_tensors[i]->View();
     if (!out[i]) return nullptr;
   }
-  void* exec = nullptr;
-  absl::Status status = image_processor->impl->RecordBatch(in.data(), out.data(), count, &exec);
-  if (!status.ok()) {
-    g_last_error = status.ToString();
+  absl::StatusOr<std::unique_ptr<band::RecordedBatch>> recorded =
+      image_processor->impl->RecordBatch(in.data(), out.data(), count);
+  if (!recorded.ok()) {
+    g_last_error = recorded.status().ToString();
     return nullptr;
   }
   BandRecordedBatch* r = new BandRecordedBatch();
-  r->processor = image_processor->impl.get();
-  r->graph_exec = exec;
+  r->impl = std::move(recorded).value();
   return r;
 }
 
@@ -261,15 +262,13 @@ BandStatus BandRecordedBatchReplay(BandRecordedBatch* recorded, int synchronize)
     BAND_LOG(LogSeverity::kError, "BandRecordedBatch is null");
     return kBandErr;
   }
-  absl::Status status = recorded->processor->ReplayBatch(recorded->graph_exec, synchronize != 0);
+  absl::Status status = band::BufferProcessor::ReplayBatch(*recorded->impl, synchronize != 0);
   if (!status.ok()) g_last_error = status.ToString();
   return status.ok() ? kBandOk : kBandErr;
 }
 
 void BandRecordedBatchDelete(BandRecordedBatch* recorded) {
-  if (!recorded) return;
-  band::BufferProcessor::ReleaseRecordedBatch(recorded->graph_exec);
-  delete recorded;
+  delete recorded;  // drains a replay still in flight, then frees the graph and (if last owner) the plan
 }
 
 BandStatus BandImageProcessorProcessBuffers(BandImageProcessor* image_processor, BandBuffer* const* inputs,

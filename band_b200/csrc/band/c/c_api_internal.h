@@ -38,4 +38,7 @@ struct BandImageProcessor {
   std::unique_ptr<band::BufferProcessor> impl;
 };
 
+// text BandGetLastError() returns on the calling thread (c_api_buffer.cc)
+void BandSetLastError(const char* message);
+
 #endif  // BAND_C_C_API_INTERNAL_H_

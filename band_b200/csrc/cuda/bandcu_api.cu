@@ -258,7 +258,12 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
     BatchArgs b;
     memset(&b, 0, sizeof(b));
     b.table = plan->table_dev;
-    return run_batch(plan, b, hints, n, s);
+    int e = run_batch(plan, b, hints, n, s);
+    if (e != BANDCU_OK) return e;
+    // this launch reads the table too: a later rewrite must wait for it, not only for the launch that uploaded it
+    CU_TRY(cudaEventRecord(plan->table_free, s), "plan_run: event record");
+    plan->table_pending = true;
+    return BANDCU_OK;
   }
   if (plan->table_pending) {  // previous launch may still read the table
     CU_TRY(cudaEventSynchronize(plan->table_free), "plan_run: wait for pointer table");
@@ -384,6 +389,30 @@ int bandcu_memcpy_d2h(void* dst, const void* src, size_t bytes, void* stream) {
 int bandcu_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream) {
   CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream), "memcpy d2d");
   return BANDCU_OK;
+}
+int bandcu_memcpy2d_d2h(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width, size_t height,
+                        void* stream) {
+  if (width == 0 || height == 0) return BANDCU_OK;
+  CU_TRY(cudaMemcpy2DAsync(dst, dst_pitch, src, src_pitch, width, height, cudaMemcpyDeviceToHost, (cudaStream_t)stream),
+         "memcpy2d d2h");
+  return BANDCU_OK;
+}
+int bandcu_host_register(void* ptr, size_t bytes) {
+  if (!ptr || !bytes) return fail(BANDCU_E_INVALID, "host_register: null range");
+  CU_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped), "cudaHostRegister");
+  return BANDCU_OK;
+}
+int bandcu_host_unregister(void* ptr) {
+  if (ptr) CU_TRY(cudaHostUnregister(ptr), "cudaHostUnregister");
+  return BANDCU_OK;
+}
+int bandcu_registered_host_pointers_usable(void) {
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrCanUseHostPointerForRegisteredMem, dev) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return v ? 1 : 0;
 }
 int bandcu_memset(void* dst, int value, size_t bytes, void* stream) {
   CU_TRY(cudaMemsetAsync(dst, value, bytes, (cudaStream_t)stream), "memset");

@@ -70,6 +70,7 @@ struct FastPlan {
   int num_sms;
   int R, S;
   int bulk_store;  // results leave through shared memory + cp.async.bulk stores (outputs in pinned host memory)
+  int no_bulk;     // BANDCU_FAST_NO_BULK=1 when the plan was created: stage with producer-warp byte copies
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -506,6 +507,7 @@ int fast_plan_create(const BandCuPlanDesc& d, FastPlan** out) {
   }
   p->R = env_int("BANDCU_FAST_ROWS", 1, kMaxRows, 0);  // 0: chosen per launch from the source row length
   p->S = env_int("BANDCU_FAST_STAGES", 2, kMaxStages, 2);
+  p->no_bulk = env_int("BANDCU_FAST_NO_BULK", 0, 1, 0);  // read here, once: nothing on the launch path touches the environment
   *out = p;
   return BANDCU_OK;
 }
@@ -615,8 +617,7 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
               ((reinterpret_cast<uintptr_t>(uv0) & 15) == 0) && (n == 1 || batch.in_stride % 16 == 0);
   }
   P.use_bulk = aligned ? 1 : 0;
-  const char* nb = getenv("BANDCU_FAST_NO_BULK");
-  if (nb && nb[0] == '1') P.use_bulk = 0;
+  if (p->no_bulk) P.use_bulk = 0;
   // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
   FastKernel kern = f32_out ? pick_kernel<float>(ch, bulk_out) : pick_kernel<uint8_t>(ch, bulk_out);
   int per_sm = 1;

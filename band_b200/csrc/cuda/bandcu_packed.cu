@@ -319,6 +319,7 @@ __global__ void __launch_bounds__(128) packed_up_rows_x16_kernel(const __grid_co
 
 struct PackedPlan {
   float* lut_dev;
+  int up_rows_mode;  // BANDCU_PACKED_UP_ROWS when the plan was created: -1 default, 0 off, 2 word-interleaved form
 };
 
 __global__ void packed_build_lut_kernel(float* lut, float mean, float sd) {
@@ -350,6 +351,8 @@ bool packed_plan_supported(const BandCuPlanDesc& d) {
 int packed_plan_create(const BandCuPlanDesc& d, PackedPlan** out) {
   PackedPlan* p = new PackedPlan();
   p->lut_dev = nullptr;
+  const char* ur = getenv("BANDCU_PACKED_UP_ROWS");  // read here, once per plan (never on the launch path)
+  p->up_rows_mode = (ur && ur[0] >= '0' && ur[0] <= '9') ? ur[0] - '0' : -1;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
@@ -418,8 +421,7 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
   dim3 grid((d.dst_width + 127) / 128, (d.dst_height + 7) / 8, 1);
   // row-streaming up-scaler: needs word (u8) / 16-byte (f32) aligned output rows
   int up_rows = 0;
-  const char* ur = getenv("BANDCU_PACKED_UP_ROWS");
-  if (d.scale_mode == BANDCU_SCALE_BILINEAR_UP && !(ur && ur[0] == '0')) {
+  if (d.scale_mode == BANDCU_SCALE_BILINEAR_UP && p->up_rows_mode != 0) {
     bool out4;
     if (batch.table) out4 = hints.out_aligned16;
     else out4 = (reinterpret_cast<uintptr_t>(batch.first.out) & 3) == 0 && (n == 1 || batch.out_stride % 4 == 0);
@@ -429,7 +431,7 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
       const int nwt = d.channels == 3 ? 3 : 4;
       up_rows = row_words <= 64 ? 1 : 2;
       // u8 rows of at least 1 KB that start 16-byte aligned: four consecutive words per lane, 128-bit stores
-      if (!d.normalize && P.vec_ok && row_words >= 256 && !(ur && ur[0] == '2')) up_rows = 3;
+      if (!d.normalize && P.vec_ok && row_words >= 256 && p->up_rows_mode != 2) up_rows = 3;
       const int per_warp = up_rows == 3 ? 128 : 32 * (up_rows == 1 ? 1 : nwt);
       // rows per thread: long enough to amortise the column filter of a source row pair (~4 source rows), short
       // enough to leave >= ~8 threads per lane of the machine

@@ -38,6 +38,7 @@ class PlanDesc(C.Structure):
         ("channels", C.c_int), ("out_dtype", C.c_int), ("normalize", C.c_int),
         ("mean", C.c_float), ("std_", C.c_float),
         ("dst_row_stride", C.c_longlong),
+        ("src_width", C.c_int), ("src_height", C.c_int),
     ]
 
 
@@ -106,6 +107,9 @@ def lib():
     for name in ("bandcu_memcpy_h2d", "bandcu_memcpy_d2h", "bandcu_memcpy_d2d"):
         getattr(L, name).argtypes = [vp, vp, C.c_size_t, vp]
     L.bandcu_memset.argtypes = [vp, ci, C.c_size_t, vp]
+    L.bandcu_memcpy2d_d2h.argtypes = [vp, C.c_size_t, vp, C.c_size_t, C.c_size_t, C.c_size_t, vp]
+    L.bandcu_host_register.argtypes = [vp, C.c_size_t]
+    L.bandcu_host_unregister.argtypes = [vp]
     L.bandcu_stream_create.argtypes = [C.POINTER(vp)]
     L.bandcu_stream_destroy.argtypes = [vp]
     L.bandcu_stream_sync.argtypes = [vp]
@@ -135,4 +139,5 @@ EXPORTED = [
     "bandcu_memcpy_d2d", "bandcu_memset", "bandcu_stream_create", "bandcu_stream_destroy", "bandcu_stream_sync",
     "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",
     "bandcu_pointer_is_device", "bandcu_pointer_kind", "bandcu_last_error_string",
+    "bandcu_memcpy2d_d2h", "bandcu_host_register", "bandcu_host_unregister", "bandcu_registered_host_pointers_usable",
 ]

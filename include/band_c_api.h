@@ -210,6 +210,47 @@ BAND_CAPI_EXPORT extern BandStatus BandTensorRingBufferPutTensor(BandTensorRingB
                                                                  int tensor_index, int handle);
 BAND_CAPI_EXPORT extern BandStatus BandTensorRingBufferGetTensor(BandTensorRingBuffer* ring, BandTensor* dst,
                                                                  int tensor_index, int handle);
+/* ---- ADDITIVE: one batch across the GPUs of the box through ONE call ----
+ * The reference processes one frame per call on the caller's thread (c_api_buffer.cc:198-214) and leaves batching as
+ * a TODO (band/buffer/buffer_processor.h:54-58). Frames are independent, so a batch shards with no exchange step:
+ * frame i of `count` goes to shard i / ceil(count / shards) (contiguous slices); every shard is an ordinary image
+ * processor with its own plans and streams on its own device, driven by its own host thread. No collective.
+ *   devices == NULL: one shard per visible GPU. Host frames / tensors (pinned or pageable) work on any shard;
+ *   DEVICE-resident ones must live on the device of the shard that owns their slice (GetSlice / GetDevice). */
+typedef struct BandShardedImageProcessor BandShardedImageProcessor;
+BAND_CAPI_EXPORT extern BandShardedImageProcessor* BandImageProcessorBuilderBuildSharded(
+    BandImageProcessorBuilder* builder, const int* devices, size_t num_devices);
+BAND_CAPI_EXPORT extern void BandShardedImageProcessorDelete(BandShardedImageProcessor* sharded);
+BAND_CAPI_EXPORT extern size_t BandShardedImageProcessorGetNumShards(BandShardedImageProcessor* sharded);
+BAND_CAPI_EXPORT extern int BandShardedImageProcessorGetDevice(BandShardedImageProcessor* sharded, size_t shard);
+BAND_CAPI_EXPORT extern void BandShardedImageProcessorGetSlice(BandShardedImageProcessor* sharded, size_t count,
+                                                               size_t shard, size_t* begin, size_t* end);
+/* Returns when every tensor is complete. */
+BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatchSharded(BandShardedImageProcessor* sharded,
+                                                                         BandBuffer* const* buffers,
+                                                                         BandTensor* const* target_tensors,
+                                                                         size_t count);
+/* Enqueue only; several batches may be queued (e.g. one per target shape). Complete after ...Synchronize. */
+BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatchShardedAsync(BandShardedImageProcessor* sharded,
+                                                                              BandBuffer* const* buffers,
+                                                                              BandTensor* const* target_tensors,
+                                                                              size_t count);
+BAND_CAPI_EXPORT extern BandStatus BandShardedImageProcessorSynchronize(BandShardedImageProcessor* sharded);
+BAND_CAPI_EXPORT extern void* BandShardedImageProcessorGetStream(BandShardedImageProcessor* sharded, size_t shard);
+BAND_CAPI_EXPORT extern int BandShardedImageProcessorIsFused(BandShardedImageProcessor* sharded, size_t shard);
+
+/* ---- ADDITIVE: registration cache for caller-owned (pageable) host frames ----
+ * BandBufferSetFromRawData receives whatever memory the application has (c_api_buffer.cc:40-53). With the cache on,
+ * a frame's address range is page-locked and mapped on first sight (cudaHostRegister) and found again on every later
+ * call, so a camera ring of malloc'ed buffers reaches the same in-place PCIe read path as BandHostAlloc memory.
+ * Bounded by `max_bytes` (0 keeps the current budget, default 4 GiB) with least-recently-used eviction; everything is
+ * unregistered when the last processor created while the cache was on is deleted. Processors created BEFORE the
+ * call keep their setting. Also switched on by BAND_REGISTER_HOST=1 (budget BAND_REGISTER_HOST_MB). The registered
+ * memory must stay mapped while registered: use it for long-lived frame buffers, not for transient allocations. */
+BAND_CAPI_EXPORT extern BandStatus BandHostRegistrationCacheConfigure(int enable, size_t max_bytes);
+BAND_CAPI_EXPORT extern void BandHostRegistrationCacheStats(size_t* registered_bytes, size_t* entries,
+                                                            unsigned long long* hits,
+                                                            unsigned long long* registrations);
 /* Kernel launches issued so far by this process (for harness accounting). */
 BAND_CAPI_EXPORT extern long long BandCudaLaunchCount();
 BAND_CAPI_EXPORT extern const char* BandGetLastError();

@@ -212,6 +212,17 @@ BANDCU_API int bandcu_host_free(void* ptr);
 BANDCU_API int bandcu_memcpy_h2d(void* dst, const void* src, size_t bytes, void* stream);
 BANDCU_API int bandcu_memcpy_d2h(void* dst, const void* src, size_t bytes, void* stream);
 BANDCU_API int bandcu_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
+/* `height` rows of `width` bytes, device pitch -> host pitch: downloads into padded host images write only the bytes
+ * libyuv would write (row padding stays the caller's). */
+BANDCU_API int bandcu_memcpy2d_d2h(void* dst, size_t dst_pitch, const void* src, size_t src_pitch, size_t width,
+                                   size_t height, void* stream);
+/* Page-lock and map caller-owned host memory (cudaHostRegister, portable across devices) so kernels can read it in
+ * place; `ptr` and `bytes` must be multiples of the 4 KB page. */
+BANDCU_API int bandcu_host_register(void* ptr, size_t bytes);
+BANDCU_API int bandcu_host_unregister(void* ptr);
+/* 1 when kernels on the current device may dereference a registered host pointer as it is (UVA, no separate device
+ * alias: cudaDevAttrCanUseHostPointerForRegisteredMem), 0 when not, <0 on error. */
+BANDCU_API int bandcu_registered_host_pointers_usable(void);
 BANDCU_API int bandcu_memset(void* dst, int value, size_t bytes, void* stream);
 BANDCU_API int bandcu_stream_create(void** stream);
 BANDCU_API int bandcu_stream_destroy(void* stream);
