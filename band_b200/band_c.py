@@ -48,7 +48,7 @@ EXPORTED = [
     "BandShardedImageProcessorGetDevice", "BandShardedImageProcessorGetSlice", "BandImageProcessorProcessBatchSharded",
     "BandImageProcessorProcessBatchShardedAsync", "BandShardedImageProcessorSynchronize",
     "BandShardedImageProcessorGetStream", "BandShardedImageProcessorIsFused",
-    "BandHostRegistrationCacheConfigure", "BandHostRegistrationCacheStats",
+    "BandHostRegistrationCacheConfigure", "BandHostRegistrationCacheStats", "BandShardSlice",
 ]
 
 
@@ -144,6 +144,8 @@ def lib():
     L.BandShardedImageProcessorGetStream.argtypes = [vp, sz]
     L.BandShardedImageProcessorGetStream.restype = vp
     L.BandShardedImageProcessorIsFused.argtypes = [vp, sz]
+    L.BandShardSlice.argtypes = [sz, sz, sz, C.POINTER(sz), C.POINTER(sz)]
+    L.BandShardSlice.restype = None
     L.BandHostRegistrationCacheConfigure.argtypes = [ci, sz]
     L.BandHostRegistrationCacheStats.argtypes = [C.POINTER(sz), C.POINTER(sz), C.POINTER(C.c_ulonglong),
                                                  C.POINTER(C.c_ulonglong)]
@@ -454,6 +456,13 @@ class ShardedImageProcessor:
             self.close()
         except Exception:
             pass
+
+
+def shard_slice(count, shards, shard):
+    """BandShardSlice: the contiguous-slice rule of the sharded processor."""
+    b, e = C.c_size_t(), C.c_size_t()
+    lib().BandShardSlice(count, shards, shard, C.byref(b), C.byref(e))
+    return int(b.value), int(e.value)
 
 
 def host_registration_cache(enable, max_bytes=0):

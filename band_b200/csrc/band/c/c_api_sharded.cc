@@ -87,6 +87,13 @@ void BandShardedImageProcessorGetSlice(BandShardedImageProcessor* sharded, size_
   if (end) *end = e;
 }
 
+void BandShardSlice(size_t count, size_t shards, size_t shard, size_t* begin, size_t* end) {
+  size_t b = 0, e = 0;
+  if (shards > 0 && shard < shards) band::ShardedBufferProcessor::SliceOf(count, shards, shard, &b, &e);
+  if (begin) *begin = b;
+  if (end) *end = e;
+}
+
 BandStatus BandImageProcessorProcessBatchSharded(BandShardedImageProcessor* sharded, BandBuffer* const* buffers,
                                                  BandTensor* const* target_tensors, size_t count) {
   return ShardedBatch(sharded, buffers, target_tensors, count, false);

@@ -131,3 +131,78 @@ class ResidentBatch:
             self.close()
         except Exception:
             pass
+
+
+class ShardedResidentBatch:
+    """n frames of one layout spread over the shards of a BandShardedImageProcessor: every shard's contiguous slice
+    (BandShardedImageProcessorGetSlice) is allocated on that shard's device together with its tensors, so ONE
+    BandImageProcessorProcessBatchSharded[Async] call drives all devices with no peer traffic."""
+
+    def __init__(self, ops, n, width, height, fmt, out_dtype, out_dims, devices, unique_frames, resident=True):
+        L = B.lib()
+        self.n, self.width, self.height = int(n), int(width), int(height)
+        self.fmt = FORMAT[fmt] if isinstance(fmt, str) else int(fmt)
+        self.frame_bytes = B.frame_bytes(self.width, self.height, self.fmt)
+        self.out_dims, self.out_dtype = tuple(out_dims), np.dtype(out_dtype)
+        self.out_bytes = int(np.prod(self.out_dims)) * self.out_dtype.itemsize
+        self.resident = bool(resident)
+        self.proc = B.ShardedImageProcessor(ops, devices)
+        self.frame_pitch = (self.frame_bytes + 255) // 256 * 256
+        self.buffers, self.tensors, self._allocs = [None] * self.n, [None] * self.n, []
+        uniq = np.ascontiguousarray(unique_frames, dtype=np.uint8)
+        for k in range(self.proc.num_shards):
+            b, e = self.proc.slice_of(self.n, k)
+            if e <= b:
+                continue
+            set_device(self.proc.device_of(k))
+            if self.resident:
+                base = L.BandDeviceAlloc(self.frame_pitch * (e - b))
+                if not base:
+                    raise B.BandError("BandDeviceAlloc failed: %s" % B.last_error())
+                self._allocs.append(("dev", base))
+            else:  # pinned host frames: read in place over PCIe by the shard's kernel
+                base = L.BandHostAlloc(self.frame_pitch * (e - b))
+                if not base:
+                    raise B.BandError("BandHostAlloc failed")
+                self._allocs.append(("host", base))
+            for i in range(b, e):
+                p = base + (i - b) * self.frame_pitch
+                src = uniq[i % uniq.shape[0]]
+                if self.resident:
+                    if L.BandCopyToDevice(p, src.ctypes.data, self.frame_bytes) != B.kBandOk:
+                        raise B.BandError("upload failed: " + B.last_error())
+                else:
+                    C.memmove(p, src.ctypes.data, self.frame_bytes)
+                self.buffers[i] = B.Buffer().set_raw(p, self.width, self.height, self.fmt, device=self.resident)
+                self.tensors[i] = B.Tensor(self.out_dtype, self.out_dims, device=self.resident)
+        self._ba = (C.c_void_p * self.n)(*[b.handle for b in self.buffers])
+        self._ta = (C.c_void_p * self.n)(*[t.handle for t in self.tensors])
+
+    def step(self):
+        if self.proc.process_batch_handles(self._ba, self._ta, self.n) != B.kBandOk:
+            raise B.BandError("BandImageProcessorProcessBatchSharded failed: %s" % B.last_error())
+
+    def step_async(self):
+        if self.proc.process_batch_async(self._ba, self._ta, self.n) != B.kBandOk:
+            raise B.BandError("BandImageProcessorProcessBatchShardedAsync failed: %s" % B.last_error())
+
+    def synchronize(self):
+        if self.proc.synchronize() != B.kBandOk:
+            raise B.BandError("BandShardedImageProcessorSynchronize failed: %s" % B.last_error())
+
+    def download(self, indices):
+        return np.stack([self.tensors[i].numpy() for i in indices])
+
+    def close(self):
+        for b in getattr(self, "buffers", []):
+            if b:
+                b.close()
+        for t in getattr(self, "tensors", []):
+            if t:
+                t.close()
+        if getattr(self, "proc", None):
+            self.proc.close()
+            self.proc = None
+        for kind, p in getattr(self, "_allocs", []):
+            (B.lib().BandDeviceFree if kind == "dev" else B.lib().BandHostFree)(p)
+        self._allocs = []

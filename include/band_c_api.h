@@ -225,6 +225,8 @@ BAND_CAPI_EXPORT extern size_t BandShardedImageProcessorGetNumShards(BandSharded
 BAND_CAPI_EXPORT extern int BandShardedImageProcessorGetDevice(BandShardedImageProcessor* sharded, size_t shard);
 BAND_CAPI_EXPORT extern void BandShardedImageProcessorGetSlice(BandShardedImageProcessor* sharded, size_t count,
                                                                size_t shard, size_t* begin, size_t* end);
+/* The slicing rule on its own (no processor, no device): [begin, end) of `shard` among `shards` for `count` frames. */
+BAND_CAPI_EXPORT extern void BandShardSlice(size_t count, size_t shards, size_t shard, size_t* begin, size_t* end);
 /* Returns when every tensor is complete. */
 BAND_CAPI_EXPORT extern BandStatus BandImageProcessorProcessBatchSharded(BandShardedImageProcessor* sharded,
                                                                          BandBuffer* const* buffers,
