@@ -132,15 +132,35 @@ def test_recorded_batch_survives_plan_changes_and_processor_deletion(O):
     tens = [B.Tensor(np.float32, (1, dh, dw, 3), device=True) for _ in range(2)]
     proc = B.ImageProcessor(to_capi_ops(ops))
     recs = [proc.record_batch([bufs[i]], [tens[i]]) for i in range(2)]
-    # other layouts through the same processor: more than the plan cache holds
-    for k, (w2, h2) in enumerate([(320, 240), (322, 242), (648, 488), (1280, 720), (96, 64)]):
-        other = rand_frames(O, 1, w2, h2, O.FMT_NV21, seed=20 + k)
-        st2, want2 = oracle_chain(O, ops, other, w2, h2, O.FMT_NV21, O.DT_F32, (1, dh, dw, 3))
+    # other layouts through the same processor, more than the plan cache holds. Same dimensions throughout: like the
+    # reference, a processor whose first operator caches its intermediate is bound to the first frame size
+    # (ColorSpaceConvert validates formats only and the conversion then rejects the stale dimensions,
+    # libyuv_image_operator.cc:1709-1727) -- what changes between cameras here is the 4:2:0 layout and the strides.
+    others = [("NV12", 0), ("YV12", 0), ("YV21", 0), ("NV12", 64), ("YV12", 32)]
+    for k, (fmt_name, pad) in enumerate(others):
+        fmt = getattr(O, "FMT_" + fmt_name)
+        other = rand_frames(O, 1, W, H, fmt, seed=20 + k)
+        st2, want2 = oracle_chain(O, ops, other, W, H, fmt, O.DT_F32, (1, dh, dw, 3))
         assert st2 == 0
         t2 = B.Tensor(np.float32, (1, dh, dw, 3), device=False)
-        b2 = B.Buffer.from_numpy(other[0], w2, h2, B.kBandNV21)
+        if pad == 0:
+            b2 = B.Buffer.from_numpy(other[0], W, H, B.FORMATS[fmt_name])
+        else:  # the same pixels with padded rows (BandBufferSetFromYUVData): another plan key
+            Y, U, V = _planes_of(other[0], W, H, fmt_name)
+            cw = (W + 1) // 2
+            yb = np.zeros((H, W + pad), np.uint8); yb[:, :W] = Y
+            if fmt_name in ("NV12", "NV21"):
+                cb = np.zeros((U.shape[0], 2 * cw + pad), np.uint8)
+                cb[:, 0:2 * cw:2], cb[:, 1:2 * cw:2] = (U, V) if fmt_name == "NV12" else (V, U)
+                up, vp = (cb.ctypes.data, cb.ctypes.data + 1) if fmt_name == "NV12" else (cb.ctypes.data + 1, cb.ctypes.data)
+                keep, cs, ps = (yb, cb), 2 * cw + pad, 2
+            else:
+                ub = np.zeros((U.shape[0], cw + pad), np.uint8); ub[:, :cw] = U
+                vb = np.zeros((U.shape[0], cw + pad), np.uint8); vb[:, :cw] = V
+                up, vp, keep, cs, ps = ub.ctypes.data, vb.ctypes.data, (yb, ub, vb), cw + pad, 1
+            b2 = B.Buffer().set_yuv(yb.ctypes.data, up, vp, W, H, W + pad, cs, ps, B.FORMATS[fmt_name], keep=keep)
         assert proc.process(b2, t2) == B.kBandOk, B.last_error()
-        assert_same_bits(t2.numpy(), want2[0], "other layout %dx%d" % (w2, h2))
+        assert_same_bits(t2.numpy(), want2[0], "other layout %s pad %d" % (fmt_name, pad))
         b2.close(); t2.close()
     for i in range(2):
         assert L.BandCopyToDevice(tens[i].data_ptr, np.zeros(tens[i].nbytes, np.uint8).ctypes.data, tens[i].nbytes) == B.kBandOk
@@ -193,11 +213,13 @@ def test_alternating_layouts_reuse_their_plans(O):
     ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
     proc = B.ImageProcessor(to_capi_ops(ops))
     cases = []
-    for k, (w, h) in enumerate([(640, 480), (1280, 720)]):
-        f = rand_frames(O, 1, w, h, O.FMT_NV12, seed=40 + k)
-        st, want = oracle_chain(O, ops, f, w, h, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+    w, h = 640, 480  # one frame size (see the note on reference semantics above), two 4:2:0 layouts
+    for k, fmt_name in enumerate(["NV12", "YV12"]):
+        fmt = getattr(O, "FMT_" + fmt_name)
+        f = rand_frames(O, 1, w, h, fmt, seed=40 + k)
+        st, want = oracle_chain(O, ops, f, w, h, fmt, O.DT_F32, (1, 224, 224, 3))
         assert st == 0
-        cases.append((B.Buffer.from_numpy(f[0], w, h, B.kBandNV12), want[0]))
+        cases.append((B.Buffer.from_numpy(f[0], w, h, B.FORMATS[fmt_name]), want[0]))
     t = B.Tensor(np.float32, (1, 224, 224, 3), device=False)
     per_call = []
     for rnd in range(3):
