@@ -733,19 +733,25 @@ absl::Status FusedPlan::Synchronize() {
 }
 
 bool FusedPlan::HostFrameIsMapped(const Buffer& frame) {
-  if (frame.IsPinnedHost()) return true;
-  if (!register_host_) return false;
+  if (!register_host_) return frame.IsPinnedHost();
+  // Ranges this cache registered are HELD for the duration of the pass (the runtime reports them as pinned too, but an
+  // unheld range could be evicted by another processor's registration while this pass's kernel still reads it).
   const HostRanges r = RangesOf(frame, input_);
-  const size_t first = held_host_.size();
-  for (int i = 0; i < r.count; ++i) {
-    if (!HostRegistry::Get().Acquire(r.lo[i], r.bytes[i], &held_host_)) {
-      std::vector<HostRegistry::Entry*> undo(held_host_.begin() + first, held_host_.end());
-      held_host_.resize(first);
-      HostRegistry::Get().Release(&undo);
-      return false;
+  auto acquire_all = [&](bool existing_only) {
+    const size_t first = held_host_.size();
+    for (int i = 0; i < r.count; ++i) {
+      if (!HostRegistry::Get().Acquire(r.lo[i], r.bytes[i], &held_host_, existing_only)) {
+        std::vector<HostRegistry::Entry*> undo(held_host_.begin() + first, held_host_.end());
+        held_host_.resize(first);
+        HostRegistry::Get().Release(&undo);
+        return false;
+      }
     }
-  }
-  return true;
+    return true;
+  };
+  if (acquire_all(/*existing_only=*/true)) return true;
+  if (frame.IsPinnedHost()) return true;  // page-locked by the caller (BandHostAlloc, cudaHostRegister of their own)
+  return acquire_all(/*existing_only=*/false);
 }
 
 void FusedPlan::ReleaseHeldHost() {

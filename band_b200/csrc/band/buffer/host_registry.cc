@@ -62,7 +62,7 @@ void HostRegistry::ClearIdle() {
   }
 }
 
-bool HostRegistry::Acquire(const void* p, size_t bytes, std::vector<Entry*>* held) {
+bool HostRegistry::Acquire(const void* p, size_t bytes, std::vector<Entry*>* held, bool existing_only) {
   if (!p || bytes == 0 || !held) return false;
   std::lock_guard<std::mutex> l(mu_);
   if (enabled_ != 1) return false;
@@ -94,6 +94,7 @@ bool HostRegistry::Acquire(const void* p, size_t bytes, std::vector<Entry*>* hel
       cur = cover->hi;
       continue;
     }
+    if (existing_only) return undo();
     // gap [cur, next entry or b): pin it first, so eviction below can never pick what this call already holds
     const uintptr_t gap_hi = (it != entries_.end() && it->first < b) ? it->first : b;
     const size_t gap = gap_hi - cur;

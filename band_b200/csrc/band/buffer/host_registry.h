@@ -36,7 +36,8 @@ class HostRegistry {
   // Makes [p, p + bytes) readable by kernels in place. On success the covering entries are appended to `held` and stay
   // registered until Release(held). false: not enabled, the platform cannot use registered host pointers directly, the
   // budget is exhausted by ranges in use, or cudaHostRegister refused -- the caller stages the frame instead.
-  bool Acquire(const void* p, size_t bytes, std::vector<Entry*>* held);
+  // existing_only: succeed only when the whole range is already registered here (a pure lookup, nothing is pinned).
+  bool Acquire(const void* p, size_t bytes, std::vector<Entry*>* held, bool existing_only = false);
   void Release(std::vector<Entry*>* held);
 
   // processors that were created while the cache was on; the last one out unregisters everything

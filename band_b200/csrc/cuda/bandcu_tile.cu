@@ -19,6 +19,7 @@
 // integers per plane: address = A + B*r + C*c.
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 #include "bandcu_device.cuh"
@@ -29,15 +30,39 @@ namespace bandcu {
 // Source rectangles of one output tile (the same for every frame of a plan): computed once on the host at plan creation
 // instead of by every CTA (three affine bounding boxes: ~170 of the ~1060 instructions a warp spent per tile).
 struct __align__(16) TileEntry {
-  int l_r0, l_rows, l_first;  // luma: first source row, rows, first source byte of a row
-  int c_r0, c_rows, c_first;  // chroma plane(s): the same, in plane bytes
+  int l_r0;          // luma: first source row of the rectangle
+  int l_rows_gpr;    // rows | granules per staged row << 16 (never past the end of the plane row)
+  int l_col0;        // first staged byte of a row, rounded down to the staging granule
+  int AL;            // tile constant of the staged-luma address form (see TileParams)
+  int c_r0, c_rows_gpr, c_col0;  // chroma plane(s): the same, in plane bytes
+  int AC;
+};
+
+// Everything an output ROW / COLUMN contributes to a sample address and to the blend. The same for every frame and
+// every tile row (column), so the host computes them once per plan -- [dst_height] and [dst_width] entries -- and the
+// kernel reads its entry with one 128-bit and one 64-bit load (L2-resident: 24 KB for a 512x512 output). The first
+// version rebuilt 32 + 32 entries per CTA behind a block barrier: ~60 instructions on 64 threads and a dependency
+// between the staging copies and the arithmetic.
+struct __align__(32) RowTerms {
+  int lA, lB;       // luma offsets of virtual rows rA, rB
+  int kA, kB;       // chroma offsets
+  uint32_t w0, w1;  // InterpolateRow weights
   int pad[2];
+};
+struct __align__(32) ColTerms {
+  int lA, lB, kA, kB;
+  uint32_t wp;      // packed 7-bit column weights, pre-shifted by one: the blended byte lands in bits 24..31
+  int pad[3];
 };
 
 struct TileParams {
   BandCuPlanDesc d;
   BatchArgs batch;
   const TileEntry* geom;  // [tiles_y][tiles_x]
+  const RowTerms* rt;     // [dst_height]
+  const ColTerms* ct;     // [dst_width]
+  const int* lrow;        // skip:   [2 * positions] source luma row of every staged slot
+  const int* crow;        // skip_c: [2 * positions] source chroma row of every staged slot
   int TR, TC;          // output rows / columns per tile
   int tiles_x, tiles_y;
   int interleaved;     // 1: semi-planar chroma (one staged plane, U/V one byte apart)
@@ -63,7 +88,8 @@ struct TileParams {
   int skip_c;
   int c_row_0, c_row_mul;
   int l_lpr_shift, c_lpr_shift;  // log2(threads serving one staged row) for the luma / chroma planes
-  int off_terms;       // offset of the per-tile term tables in dynamic shared memory
+  int off_u, off_v;    // offsets of the staged chroma plane(s) in dynamic shared memory
+  int off_out;         // offset of the [32][25]-word output tile
 };
 
 
@@ -119,61 +145,61 @@ __host__ __device__ __forceinline__ int staged_pitch(int first_byte, int last_by
 // G == 16: cp.async (LDGSTS) 16-byte copies, no register staging -- a thread's copies are all in flight at once.
 // G == 4 : 32-bit loads through registers (any word-aligned layout).
 // 2^lpr_shift threads serve one staged row (the next power of two >= granules per row, a launch constant), so the
-// loop has no division: (source, destination) advance by a fixed number of rows per pass.
-// Per-sample luma staging (skip mode): staged row `slot` comes from source row row_of(slot).
-template <int G, typename RowOf>
-__device__ __forceinline__ void stage_rows(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride, int nslots,
-                                           int first_byte, int pitch, int lpr_shift, int row_bytes, RowOf row_of) {
-  const int gpr = min(pitch / G, (row_bytes - (first_byte / G) * G + G - 1) / G);
+// loops have no division: (source, destination) advance by a fixed number of rows per pass. Destinations are 32-bit
+// shared-space addresses throughout.
+template <int G>
+__device__ __forceinline__ void copy_granules(uint32_t dst, const uint8_t* src, int g0, int gpr, int lpr) {
+  for (int g = g0, o = 0; g < gpr; g += lpr, o += lpr * G) {  // one trip unless a row has more granules than lpr
+    if (G == 16) {
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(src + o) : "memory");
+    } else {
+      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + o));
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(dst + o), "r"(v) : "memory");
+    }
+  }
+}
+// Per-sample staging (skip mode): staged row `slot` comes from source row rows[slot] -- a host-built table
+// (TileParams::lrow / crow), so a slot costs one 32-bit load instead of the 64-bit fixed-point stepping.
+template <int G>
+__device__ __forceinline__ void stage_slots(uint32_t smem_dst, const uint8_t* __restrict__ plane, int stride, int nslots,
+                                            int col0_bytes, int gpr, int pitch, int lpr_shift,
+                                            const int* __restrict__ rows) {
   const int lpr = 1 << lpr_shift;
   const int rows_per_pass = (int)blockDim.x >> lpr_shift;
   const int g0 = (int)threadIdx.x & (lpr - 1);
   if (g0 >= gpr) return;
-  const uint8_t* col0 = plane + (first_byte / G) * G + g0 * G;
-  const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(smem_dst) + (uint32_t)(g0 * G);
-  for (int r = (int)threadIdx.x >> lpr_shift; r < nslots; r += rows_per_pass) {
-    const uint8_t* src = col0 + (long long)row_of(r) * stride;
-    const uint32_t dst = dst0 + (uint32_t)(r * pitch);
-    for (int g = g0, o = 0; g < gpr; g += lpr, o += lpr * G) {
-      if (G == 16) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(src + o) : "memory");
-      } else {
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + o));
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(dst + o), "r"(v) : "memory");
-      }
-    }
-  }
+  const uint8_t* col0 = plane + col0_bytes + g0 * G;
+  const uint32_t dst0 = smem_dst + (uint32_t)(g0 * G);
+  for (int r = (int)threadIdx.x >> lpr_shift; r < nslots; r += rows_per_pass)
+    copy_granules<G>(dst0 + (uint32_t)(r * pitch), col0 + (long long)__ldg(rows + r) * stride, g0, gpr, lpr);
 }
 
 template <int G>
-__device__ __forceinline__ void stage_plane(uint8_t* smem_dst, const uint8_t* __restrict__ plane, int stride,
-                                            int row0, int nrows, int first_byte, int pitch, int lpr_shift,
-                                            int row_bytes) {
-  // granules per staged row: the launch-wide pitch, but never past the end of the plane row (the pitch is the worst
-  // case over all tiles and odd; a tile at the right edge must not read into memory behind the last row)
-  const int gpr = min(pitch / G, (row_bytes - (first_byte / G) * G + G - 1) / G);
+__device__ __forceinline__ void stage_plane(uint32_t smem_dst, const uint8_t* __restrict__ plane, int stride,
+                                            int row0, int nrows, int col0_bytes, int gpr, int pitch, int lpr_shift) {
   const int lpr = 1 << lpr_shift;
   const int rows_per_pass = (int)blockDim.x >> lpr_shift;
   int r = (int)threadIdx.x >> lpr_shift;
   const int g0 = (int)threadIdx.x & (lpr - 1);
   if (g0 >= gpr) return;
-  const uint8_t* src = plane + (long long)(row0 + r) * stride + (first_byte / G) * G + g0 * G;
-  uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst) + (uint32_t)(r * pitch + g0 * G);
+  const uint8_t* src = plane + (long long)(row0 + r) * stride + col0_bytes + g0 * G;
+  uint32_t dst = smem_dst + (uint32_t)(r * pitch + g0 * G);
   const long long src_step = (long long)rows_per_pass * stride;
   const uint32_t dst_step = (uint32_t)(rows_per_pass * pitch);
-  for (; r < nrows; r += rows_per_pass, src += src_step, dst += dst_step) {
-    for (int g = g0, o = 0; g < gpr; g += lpr, o += lpr * G) {  // one trip unless a row has more than 32 granules
-      if (G == 16) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(src + o) : "memory");
-      } else {
-        const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src + o));
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(dst + o), "r"(v) : "memory");
-      }
-    }
-  }
+  for (; r < nrows; r += rows_per_pass, src += src_step, dst += dst_step) copy_granules<G>(dst, src, g0, gpr, lpr);
 }
 
-// ---- packed LEFT|RIGHT pixel-pair arithmetic (same identities as bandcu_fast.cu; values instead of addresses) ----
+// ---- packed LEFT|RIGHT pixel-pair arithmetic (same identities as bandcu_fast.cu) ----
+__device__ __forceinline__ uint32_t t_lds_u8(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t t_lds_u16(uint32_t a) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+  return v;
+}
 struct TChroma {
   uint32_t kr, kg, kb;
 };
@@ -197,224 +223,208 @@ __device__ __forceinline__ void t_luma_pair_to_rgb(uint32_t yL, uint32_t yR, con
   B2 = (b >> 6) & 0x00FF00FFu;
 }
 __device__ __forceinline__ uint32_t t_vblend2(uint32_t top, uint32_t bot, uint32_t w0, uint32_t w1) {
-  // bytes 1 and 3 of the sums are the two results: one PRMT instead of shift + mask
+  // bytes 1 and 3 of the sums are the two results: one PRMT instead of shift + mask. w1 == 0 returns `top` exactly
+  // ((256 t + 128) >> 8), whatever `bot` holds: no branch on the fraction.
   return __byte_perm(top * w0 + bot * w1 + 0x00800080u, 0u, 0x4341);
 }
 
-struct __align__(16) RowTerms {   // everything an output ROW contributes (32 bytes)
-  int lA, lB;       // luma offsets of virtual rows rA, rB
-  int kA, kB;       // chroma offsets
-  uint32_t w0, w1;  // InterpolateRow weights
-  int pad[2];
-};
-struct __align__(16) ColTerms {   // everything an output COLUMN contributes (32 bytes)
-  int lA, lB, kA, kB;
-  uint32_t wp;      // packed 7-bit column weights
-  int pad[3];
-};
 // Clamped virtual rows (columns) sampled by output row oy (column ox): fetch_px's clamps.
-__device__ __forceinline__ void virt_rows(const BandCuPlanDesc& d, int oy, int* rA, int* rB) {
+__host__ __device__ __forceinline__ void virt_rows(const BandCuPlanDesc& d, int oy, int* rA, int* rB) {
   long long y = (long long)d.y0 + (long long)oy * d.dy;
   if (y > d.max_y) y = d.max_y;
   const int yi = (int)(y >> 16);
   *rA = min(max(yi, 0), d.vh - 1);
   *rB = min(max(yi + 1, 0), d.vh - 1);
 }
-__device__ __forceinline__ void virt_cols(const BandCuPlanDesc& d, int ox, int* cA, int* cB) {
+__host__ __device__ __forceinline__ void virt_cols(const BandCuPlanDesc& d, int ox, int* cA, int* cB) {
   const int xi = (int)(((long long)d.x0 + (long long)ox * d.dx) >> 16);
   *cA = min(max(xi, 0), d.vw - 1);
   *cB = min(max(xi + 1, 0), d.vw - 1);
 }
-// `slot_pitch` != 0: this axis selects the staged luma row (skip mode): offsets are slot * pitch for tile position i.
-__device__ __forceinline__ RowTerms row_terms(const TileParams& P, int oy, int i, int slot_pitch, int slot_pitch_c) {
+// Host side (plan tables). `slot_pitch` != 0: this axis selects the staged luma row (skip mode): offsets are
+// slot * pitch for tile position i = index % 32.
+static RowTerms row_terms(const TileParams& P, int oy, int i, int slot_pitch, int slot_pitch_c) {
   const BandCuPlanDesc& d = P.d;
   long long y = (long long)d.y0 + (long long)oy * d.dy;
   if (y > d.max_y) y = d.max_y;
-  const int yi = (int)(y >> 16);
   RowTerms t;
+  memset(&t, 0, sizeof(t));
   t.w1 = d.linear ? 0u : (uint32_t)((y >> 8) & 255);
   t.w0 = 256u - t.w1;
-  const int rA = min(max(yi, 0), d.vh - 1), rB = min(max(yi + 1, 0), d.vh - 1);
+  int rA, rB;
+  virt_rows(d, oy, &rA, &rB);
   t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lr_mul * rA;
   t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lr_mul * rB;
   t.kA = slot_pitch_c ? (2 * i) * slot_pitch_c : P.cr_mul * ((P.cr_0 + P.cr_s * rA) >> 1);
   t.kB = slot_pitch_c ? (2 * i + 1) * slot_pitch_c : P.cr_mul * ((P.cr_0 + P.cr_s * rB) >> 1);
   return t;
 }
-__device__ __forceinline__ ColTerms col_terms(const TileParams& P, int ox, int i, int slot_pitch, int slot_pitch_c) {
+static ColTerms col_terms(const TileParams& P, int ox, int i, int slot_pitch, int slot_pitch_c) {
   const BandCuPlanDesc& d = P.d;
   const long long x = (long long)d.x0 + (long long)ox * d.dx;
-  const int xi = (int)(x >> 16);
   const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
   ColTerms t;
-  t.wp = xf | ((0x7fu ^ xf) << 16);
-  const int cA = min(max(xi, 0), d.vw - 1), cB = min(max(xi + 1, 0), d.vw - 1);
+  memset(&t, 0, sizeof(t));
+  // ScaleARGBFilterCols_C on a packed pair: (L | R << 16) * (xf | (0x7f ^ xf) << 16) carries L*(0x7f^xf) + R*xf in its
+  // upper half (bits 23..30 hold the 8-bit result); shifted left once more the result is the top byte.
+  t.wp = (xf << 1) | ((0x7fu ^ xf) << 17);
+  int cA, cB;
+  virt_cols(d, ox, &cA, &cB);
   t.lA = slot_pitch ? (2 * i) * slot_pitch : P.lc_mul * cA;
   t.lB = slot_pitch ? (2 * i + 1) * slot_pitch : P.lc_mul * cB;
   t.kA = slot_pitch_c ? (2 * i) * slot_pitch_c : P.cc_mul * ((P.cc_0 + P.cc_s * cA) >> 1);
   t.kB = slot_pitch_c ? (2 * i + 1) * slot_pitch_c : P.cc_mul * ((P.cc_0 + P.cc_s * cB) >> 1);
   return t;
 }
-// Chroma of the LEFT|RIGHT sample pair at byte offsets oL, oR. Planar: four byte loads. Interleaved (IL): the staged
-// plane holds (first, second) byte pairs at even offsets -- one 16-bit load per sample, and two PRMTs (selectors sel_u,
-// sel_v pick U and V for NV12 or NV21) build the packed lanes.
+// Chroma of the LEFT|RIGHT sample pair at shared addresses aL, aR of the U plane (planar: V sits vd bytes further;
+// interleaved (IL): the staged plane holds (first, second) byte pairs at even offsets -- one 16-bit load per sample,
+// and two PRMTs with selectors sel_u, sel_v pick U and V for NV12 or NV21).
 template <bool IL>
-__device__ __forceinline__ TChroma t_chroma_at(const uint8_t* su, const uint8_t* sv, int oL, int oR, uint32_t sel_u,
-                                               uint32_t sel_v) {
+__device__ __forceinline__ TChroma t_chroma_at(uint32_t aL, uint32_t aR, uint32_t vd, uint32_t sel_u, uint32_t sel_v) {
   if (IL) {
-    const uint32_t wL = *reinterpret_cast<const uint16_t*>(su + oL), wR = *reinterpret_cast<const uint16_t*>(su + oR);
+    const uint32_t wL = t_lds_u16(aL), wR = t_lds_u16(aR);
     return t_chroma_terms(__byte_perm(wL, wR, sel_u), __byte_perm(wL, wR, sel_v));
   }
-  return t_chroma_terms(su[oL] | ((uint32_t)su[oR] << 16), sv[oL] | ((uint32_t)sv[oR] << 16));
+  return t_chroma_terms(t_lds_u8(aL) | (t_lds_u8(aR) << 16), t_lds_u8(aL + vd) | (t_lds_u8(aR + vd) << 16));
 }
-// One output pixel from the staged planes: raw products, the 8-bit results sit in bits 23..30.
+// LEFT and RIGHT samples fall into the same chroma cell (xi even: half of all columns): one sample feeds both lanes.
 template <bool IL>
-__device__ __forceinline__ void tile_pixel(const uint8_t* sl, const uint8_t* su, const uint8_t* sv, uint32_t sel_u,
-                                           uint32_t sel_v, const RowTerms& R, const ColTerms& Cn, uint32_t& r, uint32_t& g,
+__device__ __forceinline__ TChroma t_chroma_at_one(uint32_t a, uint32_t vd, uint32_t sel_u, uint32_t sel_v) {
+  if (IL) {
+    const uint32_t w = t_lds_u16(a);
+    return t_chroma_terms(__byte_perm(w, w, sel_u), __byte_perm(w, w, sel_v));
+  }
+  return t_chroma_terms(t_lds_u8(a) * 0x10001u, t_lds_u8(a + vd) * 0x10001u);
+}
+// One output pixel from the staged planes: the four luma and four chroma sample addresses (Top/Bottom x Left/Right). Raw
+// products: the 8-bit results are the top bytes. one_col / one_row: the two columns / rows share their chroma sample;
+// callers pass them only where the flag is warp-uniform (a property of the output column under a quarter-turn, of the
+// output row otherwise), so the branch never diverges.
+template <bool IL>
+__device__ __forceinline__ void tile_pixel(uint32_t lTL, uint32_t lTR, uint32_t lBL, uint32_t lBR, uint32_t kTL, uint32_t kTR,
+                                           uint32_t kBL, uint32_t kBR, bool one_col, bool one_row, uint32_t vd, uint32_t sel_u,
+                                           uint32_t sel_v, uint32_t w0, uint32_t w1, uint32_t wp, uint32_t& r, uint32_t& g,
                                            uint32_t& b) {
   uint32_t tr, tg, tb, br, bg, bb;
-  {
-    const TChroma ct = t_chroma_at<IL>(su, sv, R.kA + Cn.kA, R.kA + Cn.kB, sel_u, sel_v);
-    t_luma_pair_to_rgb(sl[R.lA + Cn.lA], sl[R.lA + Cn.lB], ct, tr, tg, tb);
-  }
-  if (R.w1) {
-    const TChroma cb = t_chroma_at<IL>(su, sv, R.kB + Cn.kA, R.kB + Cn.kB, sel_u, sel_v);
-    t_luma_pair_to_rgb(sl[R.lB + Cn.lA], sl[R.lB + Cn.lB], cb, br, bg, bb);
-  } else {
-    br = tr; bg = tg; bb = tb;
-  }
-  r = t_vblend2(tr, br, R.w0, R.w1) * Cn.wp;
-  g = t_vblend2(tg, bg, R.w0, R.w1) * Cn.wp;
-  b = t_vblend2(tb, bb, R.w0, R.w1) * Cn.wp;
+  const TChroma ct = one_col ? t_chroma_at_one<IL>(kTL, vd, sel_u, sel_v) : t_chroma_at<IL>(kTL, kTR, vd, sel_u, sel_v);
+  t_luma_pair_to_rgb(t_lds_u8(lTL), t_lds_u8(lTR), ct, tr, tg, tb);
+  TChroma cb = ct;
+  if (!one_row) cb = one_col ? t_chroma_at_one<IL>(kBL, vd, sel_u, sel_v) : t_chroma_at<IL>(kBL, kBR, vd, sel_u, sel_v);
+  t_luma_pair_to_rgb(t_lds_u8(lBL), t_lds_u8(lBR), cb, br, bg, bb);
+  r = t_vblend2(tr, br, w0, w1) * wp;
+  g = t_vblend2(tg, bg, w0, w1) * wp;
+  b = t_vblend2(tb, bb, w0, w1) * wp;
 }
 
 // SWAP: the luma map exchanges the axes (quarter-turns). Lanes then run along the output COLUMN so that a warp's
 // shared-memory reads walk consecutive source bytes (lanes along the output row would stride by whole staged rows:
-// 4-way bank conflicts measured, L1 at 84 %); each thread produces FOUR adjacent pixels of its output row and stores
-// them as 48 contiguous bytes (three 128-bit stores for f32). Without SWAP lanes run along the output row and a
-// warp stores 384 contiguous bytes per row.
-// The row and column terms of the tile (32 + 32 entries) are computed once by two warps while the cp.async copies
-// are in flight and read back as broadcasts.
+// 4-way bank conflicts measured, L1 at 84 %); each thread produces FOUR adjacent pixels of its output row.
+// Without SWAP lanes run along the output row. Either way the tile's 8-bit results go through a [32][25]-word shared
+// array and leave row-major (see below).
 template <typename OT, int G, bool SWAP, bool IL>
 __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __grid_constant__ TileParams P) {
   extern __shared__ __align__(16) uint8_t smem[];
-  __shared__ float lut[256];
+  __shared__ uint32_t lut[256];
   const BandCuPlanDesc& d = P.d;
   // f32 outputs: the Normalize table; one-byte Normalize outputs (int8 / uint8 models): 32-bit entries holding the byte
-  if (sizeof(OT) == 4 || P.lut) lut[threadIdx.x] = P.lut[threadIdx.x];  // blockDim.x == 256
-  const int oy0 = blockIdx.y * P.TR, ox0 = blockIdx.x * P.TC;
-  const int oy1 = min(oy0 + P.TR, d.dst_height) - 1, ox1 = min(ox0 + P.TC, d.dst_width) - 1;
+  if (sizeof(OT) == 4 || P.lut) lut[threadIdx.x] = __ldg(reinterpret_cast<const uint32_t*>(P.lut) + threadIdx.x);  // blockDim.x == 256
+  const int oy0 = blockIdx.y * 32, ox0 = blockIdx.x * 32;  // TR == TC == 32
+  const int nrows = min(32, d.dst_height - oy0), ncols = min(32, d.dst_width - ox0);
   const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
 
   const TileEntry te = P.geom[blockIdx.y * P.tiles_x + blockIdx.x];
-  const int ps = d.pixel_stride_uv;
-  const int l_first = te.l_first, c_first = te.c_first;
-  const int l_rows = te.l_rows, c_rows = te.c_rows;
-  const int c_row_bytes = ((d.src_width + 1) >> 1) * ps;  // bytes of one chroma plane row
-  uint8_t* sl = smem;
-  uint8_t* su = sl + P.l_rows_max * P.l_pitch;
-  uint8_t* sv;
-  if (P.skip) {
-    const int npos = SWAP ? (ox1 - ox0 + 1) : (oy1 - oy0 + 1);
-    stage_rows<G>(sl, f.p0, d.stride0, 2 * npos, l_first, P.l_pitch, P.l_lpr_shift, d.src_width, [&](int slot) {
-      int a, b;
-      if (SWAP) virt_cols(d, ox0 + (slot >> 1), &a, &b);
-      else virt_rows(d, oy0 + (slot >> 1), &a, &b);
-      return P.l_row_0 + P.l_row_mul * ((slot & 1) ? b : a);
-    });
-  } else {
-    stage_plane<G>(sl, f.p0, d.stride0, te.l_r0, l_rows, l_first, P.l_pitch, P.l_lpr_shift, d.src_width);
-  }
-  const int npos_c = SWAP ? (ox1 - ox0 + 1) : (oy1 - oy0 + 1);
-  auto chroma_row_of = [&](int slot) {
-    int a, b, q;
-    if (SWAP) { virt_cols(d, ox0 + (slot >> 1), &a, &b); q = (P.cc_0 + P.cc_s * ((slot & 1) ? b : a)) >> 1; }
-    else { virt_rows(d, oy0 + (slot >> 1), &a, &b); q = (P.cr_0 + P.cr_s * ((slot & 1) ? b : a)) >> 1; }
-    return P.c_row_0 + P.c_row_mul * q;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
+  const uint32_t sl = sbase, su = sbase + (uint32_t)P.off_u;
+  const int npos = SWAP ? ncols : nrows, pos0 = SWAP ? ox0 : oy0;
+  if (P.skip) stage_slots<G>(sl, f.p0, d.stride0, 2 * npos, te.l_col0, te.l_rows_gpr >> 16, P.l_pitch, P.l_lpr_shift, P.lrow + 2 * pos0);
+  else stage_plane<G>(sl, f.p0, d.stride0, te.l_r0, te.l_rows_gpr & 0xFFFF, te.l_col0, te.l_rows_gpr >> 16, P.l_pitch, P.l_lpr_shift);
+  auto stage_chroma = [&](uint32_t dst, const uint8_t* plane) {
+    if (P.skip_c) stage_slots<G>(dst, plane, d.stride_uv, 2 * npos, te.c_col0, te.c_rows_gpr >> 16, P.c_pitch, P.c_lpr_shift, P.crow + 2 * pos0);
+    else stage_plane<G>(dst, plane, d.stride_uv, te.c_r0, te.c_rows_gpr & 0xFFFF, te.c_col0, te.c_rows_gpr >> 16, P.c_pitch, P.c_lpr_shift);
   };
-  auto stage_chroma = [&](uint8_t* dst, const uint8_t* plane) {
-    if (P.skip_c) stage_rows<G>(dst, plane, d.stride_uv, 2 * npos_c, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes, chroma_row_of);
-    else stage_plane<G>(dst, plane, d.stride_uv, te.c_r0, c_rows, c_first, P.c_pitch, P.c_lpr_shift, c_row_bytes);
-  };
-  // IL: su stays the base of the (first, second) byte pairs; byte 2 of a zero-extended 16-bit load is the zero lane filler
+  // IL: su is the base of the (first, second) byte pairs; byte 2 of a zero-extended 16-bit load is the zero lane filler
   const uint32_t sel_u = P.v_first ? 0x2521u : 0x2420u, sel_v = P.v_first ? 0x2420u : 0x2521u;
   if (IL) {
     stage_chroma(su, P.v_first ? f.pv : f.pu);
-    sv = su;
   } else {
-    sv = su + P.c_rows_max * P.c_pitch;
     stage_chroma(su, f.pu);
-    stage_chroma(sv, f.pv);
+    stage_chroma(sbase + (uint32_t)P.off_v, f.pv);
   }
   if (G == 16) asm volatile("cp.async.commit_group;" ::: "memory");
 
+  // the tile's 32 row and 32 column terms move from the plan's tables into shared memory while the copies fly (two
+  // warps, two 16-byte loads each); the arithmetic then reads them as broadcasts
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // 8 warps
-  RowTerms* rt = reinterpret_cast<RowTerms*>(smem + P.off_terms);        // [32], 32 bytes each
-  ColTerms* ct = reinterpret_cast<ColTerms*>(smem + P.off_terms + 1024);  // [32], 32 bytes each
-  if (wid == 0) rt[lane] = row_terms(P, min(oy0 + lane, oy1), min(lane, oy1 - oy0), (P.skip && !SWAP) ? P.l_pitch : 0,
-                                 (P.skip_c && !SWAP) ? P.c_pitch : 0);
-  else if (wid == 1) ct[lane] = col_terms(P, min(ox0 + lane, ox1), min(lane, ox1 - ox0), (P.skip && SWAP) ? P.l_pitch : 0,
-                                      (P.skip_c && SWAP) ? P.c_pitch : 0);
+  uint4* terms = reinterpret_cast<uint4*>(smem + P.off_out + 3200);  // [32] RowTerms then [32] ColTerms, 32 bytes each
+  if (wid < 2) {
+    const uint4* src = wid == 0 ? reinterpret_cast<const uint4*>(P.rt + min(oy0 + lane, d.dst_height - 1))
+                                : reinterpret_cast<const uint4*>(P.ct + min(ox0 + lane, d.dst_width - 1));
+    const uint4 a = __ldg(src), b2 = __ldg(src + 1);
+    terms[wid * 64 + lane * 2] = a;
+    terms[wid * 64 + lane * 2 + 1] = b2;
+  }
+  const RowTerms* rt = reinterpret_cast<const RowTerms*>(terms);
+  const ColTerms* ct = reinterpret_cast<const ColTerms*>(terms + 64);
+  const uint32_t vd = (uint32_t)(P.off_v - P.off_u);
+  const uint32_t gl = sl + (uint32_t)te.AL, gu = su + (uint32_t)te.AC;
+  uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_out);
   if (G == 16) asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
-
-  // tile-dependent constants of the two affine address forms
-  const int AL = (P.skip ? 0 : (d.luma_map.r0 - te.l_r0) * P.l_pitch) + d.luma_map.c0 - (l_first / G) * G;
-  const int AC = (P.skip_c ? 0 : (d.chroma_map.r0 - te.c_r0) * P.c_pitch) + d.chroma_map.c0 * ps - (c_first / G) * G;
-  const uint8_t* gl = sl + AL;
-  const uint8_t* gu = su + AC;
-  const uint8_t* gv = sv + AC;
-
-  // The 8-bit results of the tile go through a [32][25]-word shared array (odd pitch: the compute layout's writes and
+  if (!SWAP) {
+    // lane = output column inside the tile; warp w owns rows w, w+8, ...
+    if (lane < ncols) {
+      const ColTerms Cn = ct[lane];
+      const uint32_t lL = gl + (uint32_t)Cn.lA, lR = gl + (uint32_t)Cn.lB, kL = gu + (uint32_t)Cn.kA, kR = gu + (uint32_t)Cn.kB;
+      uint8_t* ob = reinterpret_cast<uint8_t*>(os) + lane * 3;
+      for (int ry = wid; ry < nrows; ry += 8) {
+        const RowTerms R = rt[ry];  // warp-uniform: broadcast
+        uint32_t r, g, b;
+        tile_pixel<IL>(lL + R.lA, lR + R.lA, lL + R.lB, lR + R.lB, kL + R.kA, kR + R.kA, kL + R.kB, kR + R.kB, false, R.kA == R.kB,
+                       vd, sel_u, sel_v, R.w0, R.w1, Cn.wp, r, g, b);
+        ob[ry * 100] = (uint8_t)(r >> 24); ob[ry * 100 + 1] = (uint8_t)(g >> 24); ob[ry * 100 + 2] = (uint8_t)(b >> 24);
+      }
+    }
+  } else {
+    // lane = output row inside the tile; warp w owns columns 4w .. 4w+3
+    const int cx0 = wid * 4;
+    if (lane < nrows && cx0 < ncols) {
+      const RowTerms R = rt[lane];
+      const uint32_t lT = gl + (uint32_t)R.lA, lB = gl + (uint32_t)R.lB, kT = gu + (uint32_t)R.kA, kB = gu + (uint32_t)R.kB;
+      uint32_t px[12];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const ColTerms Cn = ct[cx0 + j];  // warp-uniform: broadcast (entries past the image repeat the last column)
+        tile_pixel<IL>(lT + Cn.lA, lT + Cn.lB, lB + Cn.lA, lB + Cn.lB, kT + Cn.kA, kT + Cn.kB, kB + Cn.kA, kB + Cn.kB,
+                       Cn.kA == Cn.kB, false, vd, sel_u, sel_v, R.w0, R.w1, Cn.wp, px[3 * j], px[3 * j + 1], px[3 * j + 2]);
+      }
+      // top bytes of twelve raw products -> three words (three PRMTs per word)
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        const uint32_t lo = __byte_perm(px[4 * q], px[4 * q + 1], 0x0073), hi = __byte_perm(px[4 * q + 2], px[4 * q + 3], 0x0073);
+        os[lane * 25 + wid * 3 + q] = __byte_perm(lo, hi, 0x5410);
+      }
+    }
+  }
+  __syncthreads();
+  // The 8-bit results of the tile went through a [32][25]-word shared array (odd pitch: the compute layout's writes and
   // the row-major reads are both conflict-free) and leave as row-major 16-byte (f32) / 4-byte (u8) pieces: a warp
   // writes 1.3 output rows of the tile per store instruction. (Storing from the quarter-turn compute layout -- each
   // lane its own output row -- cost 32 L1 wavefronts per store instruction, a third of the kernel's L1 data-pipe
   // load: profiles/r01_ncu_full_tile_v6_uncoalesced_stores.txt.)
-  uint32_t* os = reinterpret_cast<uint32_t*>(smem + P.off_terms + 2048);
-  if (!SWAP) {
-    // lane = output column inside the tile (TC == 32); warp w owns rows w, w+8, ...
-    if (ox0 + lane <= ox1) {
-      const ColTerms Cn = ct[lane];
-      uint8_t* ob = reinterpret_cast<uint8_t*>(os) + lane * 3;
-      for (int ry = wid; oy0 + ry <= oy1; ry += 8) {
-        const RowTerms R = rt[ry];
-        uint32_t r, g, b;
-        tile_pixel<IL>(gl, gu, gv, sel_u, sel_v, R, Cn, r, g, b);
-        ob[ry * 100] = (uint8_t)(r >> 23); ob[ry * 100 + 1] = (uint8_t)(g >> 23); ob[ry * 100 + 2] = (uint8_t)(b >> 23);
-      }
-    }
-  } else {
-    // lane = output row inside the tile (TR == 32); warp w owns columns 4w .. 4w+3
-    const int oy = oy0 + lane;
-    const int cx0 = wid * 4;
-    if (oy <= oy1 && ox0 + cx0 <= ox1) {
-      const RowTerms R = rt[lane];
-      uint32_t px[12];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const ColTerms Cn = ct[min(cx0 + j, 31)];
-        uint32_t r, g, b;
-        tile_pixel<IL>(gl, gu, gv, sel_u, sel_v, R, Cn, r, g, b);
-        px[3 * j] = (r >> 23) & 0xFF; px[3 * j + 1] = (g >> 23) & 0xFF; px[3 * j + 2] = (b >> 23) & 0xFF;
-      }
-#pragma unroll
-      for (int q = 0; q < 3; ++q)
-        os[lane * 25 + wid * 3 + q] = px[4 * q] | (px[4 * q + 1] << 8) | (px[4 * q + 2] << 16) | (px[4 * q + 3] << 24);
-    }
-  }
-  __syncthreads();
-  const int nrows = oy1 - oy0 + 1, ncols = ox1 - ox0 + 1;
   uint8_t* obase = f.out + (long long)oy0 * d.dst_row_stride + (size_t)ox0 * (3 * sizeof(OT));
   if (P.out_vec && ncols == 32) {  // 24 aligned pieces per row (ox0 is a multiple of 32)
-    for (int idx = threadIdx.x; idx < nrows * 24; idx += 256) {
-      const int row = idx / 24, q = idx - row * 24;
-      uint32_t w = os[row * 25 + q];
-      uint8_t* o = obase + (long long)row * d.dst_row_stride;
+    // piece (row, q) of thread t: t = 24 row + q once, then every pass adds 256 = 10 rows + 16 pieces
+    int row = (int)threadIdx.x / 24, q = (int)threadIdx.x - row * 24;
+    const uint32_t stride = (uint32_t)d.dst_row_stride;
+    for (; row < nrows; row += 10, q += 16) {
+      if (q >= 24) { q -= 24; ++row; if (row >= nrows) break; }
+      uint32_t wv = os[row * 25 + q];
+      uint8_t* o = obase + row * stride;
       if (sizeof(OT) == 1 && P.lut)
-        w = (__float_as_uint(lut[w & 0xFF]) & 0xFF) | ((__float_as_uint(lut[(w >> 8) & 0xFF]) & 0xFF) << 8) |
-            ((__float_as_uint(lut[(w >> 16) & 0xFF]) & 0xFF) << 16) | (__float_as_uint(lut[w >> 24]) << 24);
-      if (sizeof(OT) == 1) reinterpret_cast<uint32_t*>(o)[q] = w;
-      else reinterpret_cast<float4*>(o)[q] = make_float4(lut[w & 0xFF], lut[(w >> 8) & 0xFF], lut[(w >> 16) & 0xFF], lut[w >> 24]);
+        wv = (lut[wv & 0xFF] & 0xFF) | ((lut[(wv >> 8) & 0xFF] & 0xFF) << 8) | ((lut[(wv >> 16) & 0xFF] & 0xFF) << 16) |
+             (lut[wv >> 24] << 24);
+      if (sizeof(OT) == 1) reinterpret_cast<uint32_t*>(o)[q] = wv;
+      else reinterpret_cast<uint4*>(o)[q] = make_uint4(lut[wv & 0xFF], lut[(wv >> 8) & 0xFF], lut[(wv >> 16) & 0xFF], lut[wv >> 24]);
     }
   } else {  // right-edge tiles, unaligned outputs: element by element, still row-major
     const uint8_t* ob = reinterpret_cast<const uint8_t*>(os);
@@ -423,8 +433,8 @@ __global__ void __launch_bounds__(256) tile_yuv_bilinear_down_kernel(const __gri
       if (c >= 3 * ncols) continue;
       const uint32_t v = ob[row * 100 + c];
       uint8_t* o = obase + (long long)row * d.dst_row_stride;
-      if (sizeof(OT) == 1) o[c] = P.lut ? (uint8_t)__float_as_uint(lut[v]) : (uint8_t)v;
-      else reinterpret_cast<float*>(o)[c] = lut[v];
+      if (sizeof(OT) == 1) o[c] = P.lut ? (uint8_t)lut[v] : (uint8_t)v;
+      else reinterpret_cast<uint32_t*>(o)[c] = lut[v];
     }
   }
 }
@@ -470,11 +480,21 @@ static TileGeom tile_geometry(const BandCuPlanDesc& d, int TR, int TC, bool inte
   return g;
 }
 
+// Everything a launch needs that depends on the staging granule G (16 when the batch is 16-byte granular, else 4): the
+// worst-case geometry, and the device tables built from it once per plan.
+struct TileTables {
+  TileGeom g;
+  TileEntry* geom_dev = nullptr;
+  RowTerms* rt_dev = nullptr;
+  ColTerms* ct_dev = nullptr;
+  int* lrow_dev = nullptr;
+  int* crow_dev = nullptr;
+};
+
 struct TilePlan {
   float* lut_dev;
-  TileEntry* geom_dev;
   int TR, TC;
-  TileGeom g16, g4;
+  TileTables t16, t4;
   bool skip, skip_c;
 };
 
@@ -500,9 +520,140 @@ bool tile_plan_supported(const BandCuPlanDesc& d) {
   return true;
 }
 
-int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
+// The launch parameters that follow from the plan and the geometry alone (no batch pointers): separable address forms
+// (signed permutations: each mapped coordinate depends on one virtual coordinate), staging split, shared-memory map.
+static void fill_geometry_params(TileParams& P, const BandCuPlanDesc& d, const TileGeom& g, int G, bool skip, bool skip_c) {
+  P.d = d;
+  P.TR = 32; P.TC = 32;
+  P.tiles_x = (d.dst_width + 31) / 32;
+  P.tiles_y = (d.dst_height + 31) / 32;
+  P.interleaved = d.pixel_stride_uv == 2 ? 1 : 0;
+  P.l_pitch = g.l_pitch; P.c_pitch = g.c_pitch;
+  P.l_rows_max = g.l_rows; P.c_rows_max = g.c_rows;
+  const int ps = d.pixel_stride_uv;
+  P.skip = skip ? 1 : 0;
+  P.skip_c = skip_c ? 1 : 0;
+  P.c_row_0 = d.chroma_map.r0;
+  P.c_row_mul = d.chroma_map.rr != 0 ? d.chroma_map.rr : d.chroma_map.rc;
+  P.l_row_0 = d.luma_map.r0;
+  P.l_row_mul = d.luma_map.rr != 0 ? d.luma_map.rr : d.luma_map.rc;
+  P.lr_mul = d.luma_map.rr * g.l_pitch + d.luma_map.cr;
+  P.lc_mul = d.luma_map.rc * g.l_pitch + d.luma_map.cc;
+  const int BC = d.chroma_map.rr * g.c_pitch + d.chroma_map.cr * ps;  // per chroma-index row
+  const int CC = d.chroma_map.rc * g.c_pitch + d.chroma_map.cc * ps;  // per chroma-index column
+  if (d.pre_map.rr != 0) {  // conversion-image row <- virtual row
+    P.cr_0 = d.pre_map.r0; P.cr_s = d.pre_map.rr; P.cr_mul = BC;
+    P.cc_0 = d.pre_map.c0; P.cc_s = d.pre_map.cc; P.cc_mul = CC;
+  } else {                  // conversion-image row <- virtual column
+    P.cr_0 = d.pre_map.c0; P.cr_s = d.pre_map.cr; P.cr_mul = CC;
+    P.cc_0 = d.pre_map.r0; P.cc_s = d.pre_map.rc; P.cc_mul = BC;
+  }
+  // threads per staged row (2^shift): the split of the 256 threads over (rows, granules) that costs a thread the fewest
+  // instructions: passes * (row set-up + trips * copy). Per-sample rows pay ~8 instructions of set-up (table load and
+  // row address), rectangle rows ~6; a copy ~4.
+  auto shift_for = [](int granules, int rows, int setup) {
+    int best = 0, best_cost = 1 << 30;
+    for (int sh = 0; sh <= 5; ++sh) {
+      const int lpr = 1 << sh, rows_per_pass = 256 >> sh;
+      const int cost = ((rows + rows_per_pass - 1) / rows_per_pass) * (setup + ((granules + lpr - 1) / lpr) * 4);
+      if (cost <= best_cost) { best_cost = cost; best = sh; }  // ties: more threads per row (longer contiguous runs)
+    }
+    return best;
+  };
+  P.l_lpr_shift = shift_for(g.l_pitch / G, g.l_rows, skip ? 8 : 6);
+  P.c_lpr_shift = shift_for(g.c_pitch / G, g.c_rows, skip_c ? 8 : 6);
+  P.off_u = g.l_rows * g.l_pitch;
+  P.off_v = P.off_u + (P.interleaved ? 0 : g.c_rows * g.c_pitch);
+  P.off_out = (int)g.stage_bytes;
+}
+
+template <typename T>
+static cudaError_t upload(T** dev, const std::vector<T>& host) {
+  *dev = nullptr;
+  if (host.empty()) return cudaSuccess;
+  cudaError_t e = cudaMalloc((void**)dev, host.size() * sizeof(T));
+  if (e == cudaSuccess) e = cudaMemcpy(*dev, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice);
+  return e;
+}
+
+static void free_tables(TileTables& t) {
+  if (t.geom_dev) (void)cudaFree(t.geom_dev);
+  if (t.rt_dev) (void)cudaFree(t.rt_dev);
+  if (t.ct_dev) (void)cudaFree(t.ct_dev);
+  if (t.lrow_dev) (void)cudaFree(t.lrow_dev);
+  if (t.crow_dev) (void)cudaFree(t.crow_dev);
+  t = TileTables();
+}
+
+template <int G>
+static cudaError_t build_tables(const BandCuPlanDesc& d, bool skip, bool skip_c, TileTables* out) {
   const bool inter = d.pixel_stride_uv == 2;
-  const int TR = 32, TC = 32;  // lanes run along one tile edge: both stay 32
+  out->g = tile_geometry<G>(d, 32, 32, inter, skip, skip_c);
+  TileParams P;
+  memset(&P, 0, sizeof(P));
+  fill_geometry_params(P, d, out->g, G, skip, skip_c);
+  const bool swap = d.luma_map.rr == 0;
+  const int ps = d.pixel_stride_uv;
+  // per-tile source rectangles and the tile constants of the two affine address forms
+  std::vector<TileEntry> geom((size_t)P.tiles_x * P.tiles_y);
+  for (int ty = 0; ty < P.tiles_y; ++ty) {
+    for (int tx = 0; tx < P.tiles_x; ++tx) {
+      const int oy0 = ty * 32, ox0 = tx * 32;
+      const int oy1 = (oy0 + 32 < d.dst_height ? oy0 + 32 : d.dst_height) - 1;
+      const int ox1 = (ox0 + 32 < d.dst_width ? ox0 + 32 : d.dst_width) - 1;
+      Rect L, C;
+      tile_rects(d, virtual_rect(d, oy0, oy1, ox0, ox1), &L, &C);
+      TileEntry& e = geom[(size_t)ty * P.tiles_x + tx];
+      memset(&e, 0, sizeof(e));
+      // granules per staged row: the launch-wide pitch, but never past the end of the plane row (the pitch is the
+      // worst case over all tiles and odd; a tile at the right edge must not read into memory behind the last row)
+      const int c_row_bytes = ((d.src_width + 1) >> 1) * ps;
+      const int l_first = L.c0, c_first = C.c0 * ps;
+      const int l_gpr = std::min(P.l_pitch / G, (d.src_width - (l_first / G) * G + G - 1) / G);
+      const int c_gpr = std::min(P.c_pitch / G, (c_row_bytes - (c_first / G) * G + G - 1) / G);
+      e.l_r0 = L.r0; e.l_rows_gpr = (L.r1 - L.r0 + 1) | (l_gpr << 16); e.l_col0 = (l_first / G) * G;
+      e.c_r0 = C.r0; e.c_rows_gpr = (C.r1 - C.r0 + 1) | (c_gpr << 16); e.c_col0 = (c_first / G) * G;
+      e.AL = (skip ? 0 : (d.luma_map.r0 - e.l_r0) * P.l_pitch) + d.luma_map.c0 - e.l_col0;
+      e.AC = (skip_c ? 0 : (d.chroma_map.r0 - e.c_r0) * P.c_pitch) + d.chroma_map.c0 * ps - e.c_col0;
+    }
+  }
+  // row / column terms of every output row / column (tile position = index % 32)
+  std::vector<RowTerms> rt(d.dst_height);
+  std::vector<ColTerms> ct(d.dst_width);
+  for (int oy = 0; oy < d.dst_height; ++oy)
+    rt[oy] = row_terms(P, oy, oy & 31, (skip && !swap) ? P.l_pitch : 0, (skip_c && !swap) ? P.c_pitch : 0);
+  for (int ox = 0; ox < d.dst_width; ++ox)
+    ct[ox] = col_terms(P, ox, ox & 31, (skip && swap) ? P.l_pitch : 0, (skip_c && swap) ? P.c_pitch : 0);
+  // per-sample staging: the source row of every slot (two per position along the axis that maps to source rows)
+  std::vector<int> lrow, crow;
+  const int npos = swap ? d.dst_width : d.dst_height;
+  if (skip || skip_c) {
+    for (int p = 0; p < npos; ++p) {
+      int a, b;
+      if (swap) virt_cols(d, p, &a, &b);
+      else virt_rows(d, p, &a, &b);
+      if (skip) {
+        lrow.push_back(P.l_row_0 + P.l_row_mul * a);
+        lrow.push_back(P.l_row_0 + P.l_row_mul * b);
+      }
+      if (skip_c) {
+        const int q0 = swap ? P.cc_0 : P.cr_0, qs = swap ? P.cc_s : P.cr_s;
+        crow.push_back(P.c_row_0 + P.c_row_mul * ((q0 + qs * a) >> 1));
+        crow.push_back(P.c_row_0 + P.c_row_mul * ((q0 + qs * b) >> 1));
+      }
+    }
+  }
+  cudaError_t e = upload(&out->geom_dev, geom);
+  if (e == cudaSuccess) e = upload(&out->rt_dev, rt);
+  if (e == cudaSuccess) e = upload(&out->ct_dev, ct);
+  if (e == cudaSuccess) e = upload(&out->lrow_dev, lrow);
+  if (e == cudaSuccess) e = upload(&out->crow_dev, crow);
+  return e;
+}
+
+static size_t tile_smem_bytes(const TileGeom& g) { return g.stage_bytes + 3200 + 2048; }  // + the [32][25]-word output tile + row / column terms
+
+int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   // per-sample luma staging pays once the down-scale along the axis that maps to source rows reaches 2
   const char* ns = getenv("BANDCU_TILE_NO_SKIP");
   const bool skip = !(ns && ns[0] == '1') && (d.luma_map.rr != 0 ? d.dy : d.dx) >= 0x20000;
@@ -512,44 +663,27 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
   const bool luma_rows_from_vrows = d.luma_map.rr != 0;
   const bool chroma_rows_from_vrows = d.pre_map.rr != 0 ? d.chroma_map.rr != 0 : d.chroma_map.rc != 0;
   const bool skip_c = skip && luma_rows_from_vrows == chroma_rows_from_vrows && (luma_rows_from_vrows ? d.dy : d.dx) >= 0x60000;
-  const TileGeom g16 = tile_geometry<16>(d, TR, TC, inter, skip, skip_c), g4 = tile_geometry<4>(d, TR, TC, inter, skip, skip_c);
-  if (g16.stage_bytes + 2048 + 3200 > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
+  {
+    const TileGeom probe = tile_geometry<16>(d, 32, 32, d.pixel_stride_uv == 2, skip, skip_c);
+    if (tile_smem_bytes(probe) > 100 * 1024) return BANDCU_E_UNSUPPORTED;  // very large ratios: keep >= 2 CTAs per SM
+  }
   TilePlan* p = new TilePlan();
   p->lut_dev = nullptr;
-  p->geom_dev = nullptr;
-  {
-    const int tiles_x = (d.dst_width + TC - 1) / TC, tiles_y = (d.dst_height + TR - 1) / TR;
-    std::vector<TileEntry> geom((size_t)tiles_x * tiles_y);
-    for (int ty = 0; ty < tiles_y; ++ty) {
-      for (int tx = 0; tx < tiles_x; ++tx) {
-        const int oy0 = ty * TR, ox0 = tx * TC;
-        const int oy1 = (oy0 + TR < d.dst_height ? oy0 + TR : d.dst_height) - 1;
-        const int ox1 = (ox0 + TC < d.dst_width ? ox0 + TC : d.dst_width) - 1;
-        Rect L, C;
-        tile_rects(d, virtual_rect(d, oy0, oy1, ox0, ox1), &L, &C);
-        TileEntry& e = geom[(size_t)ty * tiles_x + tx];
-        memset(&e, 0, sizeof(e));
-        e.l_r0 = L.r0; e.l_rows = L.r1 - L.r0 + 1; e.l_first = L.c0;
-        e.c_r0 = C.r0; e.c_rows = C.r1 - C.r0 + 1; e.c_first = C.c0 * d.pixel_stride_uv;
-      }
-    }
-    cudaError_t e = cudaMalloc((void**)&p->geom_dev, geom.size() * sizeof(TileEntry));
-    if (e == cudaSuccess) e = cudaMemcpy(p->geom_dev, geom.data(), geom.size() * sizeof(TileEntry), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) { if (p->geom_dev) cudaFree(p->geom_dev); delete p; return (int)e; }
-  }
-  p->TR = TR; p->TC = TC;
-  p->g16 = g16; p->g4 = g4;
+  p->TR = 32; p->TC = 32;
   p->skip = skip;
   p->skip_c = skip_c;
+  cudaError_t e = build_tables<16>(d, skip, skip_c, &p->t16);
+  if (e == cudaSuccess) e = build_tables<4>(d, skip, skip_c, &p->t4);
+  if (e != cudaSuccess) { free_tables(p->t16); free_tables(p->t4); delete p; return (int)e; }
   if (d.normalize) {
-    cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
-    if (e != cudaSuccess) { cudaFree(p->geom_dev); delete p; return (int)e; }
+    e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
+    if (e != cudaSuccess) { free_tables(p->t16); free_tables(p->t4); delete p; return (int)e; }
     if (d.out_dtype == BANDCU_DT_I8) tile_build_byte_lut_kernel<int8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
     else if (d.out_dtype == BANDCU_DT_U8) tile_build_byte_lut_kernel<uint8_t><<<1, 256>>>((uint32_t*)p->lut_dev, d.mean, d.std_);
     else tile_build_lut_kernel<<<1, 256>>>(p->lut_dev, d.mean, d.std_);
     count_launch();
     e = cudaDeviceSynchronize();
-    if (e != cudaSuccess) { cudaFree(p->lut_dev); cudaFree(p->geom_dev); delete p; return (int)e; }
+    if (e != cudaSuccess) { cudaFree(p->lut_dev); free_tables(p->t16); free_tables(p->t4); delete p; return (int)e; }
   }
   *out = p;
   return BANDCU_OK;
@@ -558,7 +692,8 @@ int tile_plan_create(const BandCuPlanDesc& d, TilePlan** out) {
 void tile_plan_destroy(TilePlan* p) {
   if (!p) return;
   if (p->lut_dev) (void)cudaFree(p->lut_dev);
-  if (p->geom_dev) (void)cudaFree(p->geom_dev);
+  free_tables(p->t16);
+  free_tables(p->t4);
   delete p;
 }
 
@@ -577,33 +712,26 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
                 cudaStream_t stream) {
   TileParams P;
   memset(&P, 0, sizeof(P));
-  P.d = d;
   const bool f32_out = d.normalize && d.out_dtype == BANDCU_DT_F32;
-  P.batch = batch;
-  P.TR = p->TR; P.TC = p->TC;
-  P.tiles_x = (d.dst_width + P.TC - 1) / P.TC;
-  P.tiles_y = (d.dst_height + P.TR - 1) / P.TR;
-  P.lut = p->lut_dev;
-  P.geom = p->geom_dev;
+  int v_first = 0;
   bool aligned4, aligned16 = (d.stride0 % 16 == 0) && (d.stride_uv % 16 == 0) && (d.src_width % 16 == 0) &&
                              ((((d.src_width + 1) / 2) * d.pixel_stride_uv) % 16 == 0);
   if (d.pixel_stride_uv == 2) {
     if (batch.table) {
       if (!hints.valid || !hints.semi_planar) return BANDCU_E_UNSUPPORTED;
-      P.v_first = hints.vu ? 1 : 0;
+      v_first = hints.vu ? 1 : 0;
       aligned4 = hints.aligned16;
       aligned16 = aligned16 && hints.aligned16;
     } else {
-      if (batch.first.pv == batch.first.pu + 1) P.v_first = 0;
-      else if (batch.first.pu == batch.first.pv + 1) P.v_first = 1;
+      if (batch.first.pv == batch.first.pu + 1) v_first = 0;
+      else if (batch.first.pu == batch.first.pv + 1) v_first = 1;
       else return BANDCU_E_UNSUPPORTED;
-      const uint8_t* uv0 = P.v_first ? batch.first.pv : batch.first.pu;
+      const uint8_t* uv0 = v_first ? batch.first.pv : batch.first.pu;
       const uintptr_t bits = reinterpret_cast<uintptr_t>(batch.first.p0) | reinterpret_cast<uintptr_t>(uv0) |
                              (n == 1 ? 0 : (uintptr_t)batch.in_stride);
       aligned4 = (bits & 3) == 0;
       aligned16 = aligned16 && (bits & 15) == 0;
     }
-    P.interleaved = 1;
   } else {
     if (batch.table) {
       if (!hints.valid || !hints.planes_aligned4) return BANDCU_E_UNSUPPORTED;
@@ -617,47 +745,18 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
     }
   }
   if (!aligned4) return BANDCU_E_UNSUPPORTED;
-  const TileGeom& g = aligned16 ? p->g16 : p->g4;
-  P.l_pitch = g.l_pitch; P.c_pitch = g.c_pitch;
-  P.l_rows_max = g.l_rows; P.c_rows_max = g.c_rows;
-  // separable address forms (signed permutations: each mapped coordinate depends on one virtual coordinate)
-  const int ps = d.pixel_stride_uv;
-  P.skip = p->skip ? 1 : 0;
-  P.skip_c = p->skip_c ? 1 : 0;
-  P.c_row_0 = d.chroma_map.r0;
-  P.c_row_mul = d.chroma_map.rr != 0 ? d.chroma_map.rr : d.chroma_map.rc;
-  P.l_row_0 = d.luma_map.r0;
-  P.l_row_mul = d.luma_map.rr != 0 ? d.luma_map.rr : d.luma_map.rc;
-  P.lr_mul = d.luma_map.rr * g.l_pitch + d.luma_map.cr;
-  P.lc_mul = d.luma_map.rc * g.l_pitch + d.luma_map.cc;
-  const int BC = d.chroma_map.rr * g.c_pitch + d.chroma_map.cr * ps;  // per chroma-index row
-  const int CC = d.chroma_map.rc * g.c_pitch + d.chroma_map.cc * ps;  // per chroma-index column
-  if (d.pre_map.rr != 0) {  // conversion-image row <- virtual row
-    P.cr_0 = d.pre_map.r0; P.cr_s = d.pre_map.rr; P.cr_mul = BC;
-    P.cc_0 = d.pre_map.c0; P.cc_s = d.pre_map.cc; P.cc_mul = CC;
-  } else {                  // conversion-image row <- virtual column
-    P.cr_0 = d.pre_map.c0; P.cr_s = d.pre_map.cr; P.cr_mul = CC;
-    P.cc_0 = d.pre_map.r0; P.cc_s = d.pre_map.rc; P.cc_mul = BC;
-  }
+  const TileTables& t = aligned16 ? p->t16 : p->t4;
+  fill_geometry_params(P, d, t.g, aligned16 ? 16 : 4, p->skip, p->skip_c);
+  P.batch = batch;
+  P.v_first = v_first;
+  P.lut = p->lut_dev;
+  P.geom = t.geom_dev;
+  P.rt = t.rt_dev;
+  P.ct = t.ct_dev;
+  P.lrow = t.lrow_dev;
+  P.crow = t.crow_dev;
   const bool swap = d.luma_map.rr == 0;
-  // threads per staged row (2^shift): the split of the 256 threads over (rows, granules) that costs a thread the fewest
-  // instructions: passes * (row set-up + trips * copy). Per-sample rows pay ~30 instructions of set-up (the row's
-  // source index), rectangle rows ~6; a copy ~4. C3: 64 sampled luma rows of 11 granules -> 4 threads per row, one pass,
-  // three copies each (was 16 threads per row, four passes).
-  auto shift_for = [](int granules, int rows, int setup) {
-    int best = 0, best_cost = 1 << 30;
-    for (int sh = 0; sh <= 5; ++sh) {
-      const int lpr = 1 << sh, rows_per_pass = 256 >> sh;
-      const int cost = ((rows + rows_per_pass - 1) / rows_per_pass) * (setup + ((granules + lpr - 1) / lpr) * 4);
-      if (cost <= best_cost) { best_cost = cost; best = sh; }  // ties: more threads per row (longer contiguous runs)
-    }
-    return best;
-  };
-  const int G = aligned16 ? 16 : 4;
-  P.l_lpr_shift = shift_for(g.l_pitch / G, g.l_rows, p->skip ? 30 : 6);
-  P.c_lpr_shift = shift_for(g.c_pitch / G, g.c_rows, p->skip_c ? 30 : 6);
-  P.off_terms = (int)g.stage_bytes;
-  const size_t smem = g.stage_bytes + 2048 + 3200;  // + row / column term tables + the [32][25]-word output tile
+  const size_t smem = tile_smem_bytes(t.g);
   {
     const int need = f32_out ? 15 : 3;
     bool ok;
