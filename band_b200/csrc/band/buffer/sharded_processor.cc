@@ -105,6 +105,24 @@ absl::Status ShardedBufferProcessor::ProcessBatchAsync(const Buffer* const* inpu
   for (size_t i = 0; i < n; ++i)
     if (inputs[i] == nullptr || outputs[i] == nullptr)
       return absl::InvalidArgumentError(absl::StrFormat("ProcessBatchSharded: entry %d is null", static_cast<int>(i)));
+  // Device-resident frames and outputs are used where they are: a slice that lives on another GPU than its shard
+  // would fault inside the kernel (and take the CUDA context with it). The ends of every slice are checked here -- two
+  // driver queries per shard, not per frame.
+  for (size_t k = 0; k < shards_.size(); ++k) {
+    size_t b, e;
+    SliceOf(n, shards_.size(), k, &b, &e);
+    if (b >= e) continue;
+    for (size_t i : {b, e - 1}) {
+      for (const Buffer* buf : {inputs[i], static_cast<const Buffer*>(outputs[i])}) {
+        if (buf->GetMemorySpace() != MemorySpace::kDevice || buf->GetNumPlanes() == 0) continue;
+        const int where = bandcu_pointer_device((*buf)[0].data);
+        if (where >= 0 && where != shards_[k]->device)
+          return absl::InvalidArgumentError(absl::StrFormat(
+              "ProcessBatchSharded: entry %d lives on device %d but belongs to shard %d on device %d (slices are "
+              "contiguous: see SliceOf / DeviceOf)", static_cast<int>(i), where, static_cast<int>(k), shards_[k]->device));
+      }
+    }
+  }
   for (size_t k = 0; k < shards_.size(); ++k) {
     size_t b, e;
     SliceOf(n, shards_.size(), k, &b, &e);

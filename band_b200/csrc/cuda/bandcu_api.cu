@@ -511,6 +511,15 @@ int bandcu_pointer_kind(const void* ptr) {
   if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return 2;
   return a.type == cudaMemoryTypeHost ? 1 : 0;
 }
+int bandcu_pointer_device(const void* ptr) {
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, ptr);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? a.device : -1;
+}
 const char* bandcu_last_error_string(void) { return g_err; }
 
 }  // extern "C"

@@ -245,6 +245,8 @@ BANDCU_API int bandcu_stream_wait_event(void* stream, void* ev);
 BANDCU_API int bandcu_pointer_is_device(const void* ptr);
 /* 0 pageable host memory, 1 pinned / registered host memory, 2 device or managed memory, <0 on error. */
 BANDCU_API int bandcu_pointer_kind(const void* ptr);
+/* ordinal of the device a device pointer was allocated on; -1 for host memory or on error. */
+BANDCU_API int bandcu_pointer_device(const void* ptr);
 BANDCU_API const char* bandcu_last_error_string(void);
 
 #ifdef __cplusplus
