@@ -356,19 +356,6 @@ template <int N>
 struct IntTag {
   static constexpr int value = N;
 };
-struct PlaneMap {
-  const uint8_t* src;
-  uint8_t* dst;
-  int src_stride, dst_stride;
-  int w, h;        // output elements
-  int esize;       // bytes per element: 1 .. 4
-  int vec;         // output rows are word aligned
-  BandCuAffine m;  // output element (r, c) -> source element (row, col)
-};
-struct PlaneMapParams {
-  PlaneMap pl[3];
-  long long src_step, dst_step;
-};
 // Tile: 32 output rows x kPlaneTew(E) output elements (64, 32, 32, 32 elements = 64, 64, 96, 128 bytes). Staged either
 // way round the map turns it: at most 64 rows of at most 128 bytes.
 __host__ __device__ constexpr int plane_tew(int E) { return E == 1 ? 64 : 32; }
@@ -691,6 +678,10 @@ static int run_plane_maps(PlaneMapParams& P, int n, cudaStream_t stream) {
       }
       return (int)cudaGetLastError();
     }
+  }
+  {  // quarter-turns of word-aligned planes: word-granular transposes (bandcu_turn.cu)
+    const int e = launch_plane_turns(P, n, stream);
+    if (e != BANDCU_E_UNSUPPORTED) return e;
   }
   bool turn = true;  // every present plane a quarter-turn of 1- / 2-byte elements: the large-tile kernel
   int tx = 1, ty = 1;

@@ -2,6 +2,7 @@
 // .cu translation units of libbandcu.so (not part of the C-ABI).
 #pragma once
 #include <cuda_runtime.h>
+#include <stdint.h>
 
 #include "bandcu.h"
 
@@ -55,4 +56,21 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
 // Same-size conversions (ColorSpaceConvert without a Resize, optionally behind a Crop): four pixels per thread, 32-bit
 // accesses (bandcu_copy.cu). BANDCU_E_UNSUPPORTED: another chain, or a batch that is not word aligned.
 int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream);
+// One plane of an index-mapped copy (Crop / Rotate / Flip of a 4:2:0 plane or of a packed image).
+struct PlaneMap {
+  const uint8_t* src;
+  uint8_t* dst;
+  int src_stride, dst_stride;
+  int w, h;        // output elements
+  int esize;       // bytes per element: 1 .. 4
+  int vec;         // output rows are word aligned
+  BandCuAffine m;  // output element (r, c) -> source element (row, col)
+};
+struct PlaneMapParams {
+  PlaneMap pl[3];
+  long long src_step, dst_step;
+};
+// Quarter-turns as word-granular register / shared-memory transposes (bandcu_turn.cu). BANDCU_E_UNSUPPORTED: some plane
+// is not a quarter-turn or misses the word alignment the kernel needs; the byte-staged kernels take it.
+int launch_plane_turns(const PlaneMapParams& P, int n, cudaStream_t stream);
 }  // namespace bandcu
