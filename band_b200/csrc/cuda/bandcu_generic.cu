@@ -10,6 +10,7 @@
 // (libyuv_image_operator.cc:1709-1727), ::Resize (:1627-1646), ::Crop
 // (:1609-1625), ::Rotate (:1648-1667), ::Flip* (:1669-1707) with a packed
 // output, and Normalize/DataTypeConvert (common_operator.cc:24-175).
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -737,10 +738,112 @@ static int launch_packed_map_tiles(const BandCuPlanDesc& d, const BatchArgs& bat
 }
 
 
+// Chroma REPACKS with untouched geometry (ColorSpaceConvert between 4:2:0 layouts: NV12ToI420, I420ToNV12 / NV21,
+// SwapUVPlane, libyuv_image_operator.cc:125-162,:213-250,:302-367): the luma plane is a straight copy and the chroma
+// samples only change their interleaving. The byte-per-thread kernel above moved one byte per load and store; here a
+// thread moves 16 luma bytes (blockIdx.z even) or EIGHT chroma samples of one row (odd): one 128-bit or two 64-bit loads,
+// four PRMTs to split or merge the U / V bytes, one 128-bit or two 64-bit stores.
+struct YuvRepackParams {
+  const uint8_t *sy, *su, *sv;  // su / sv: plane bases; interleaved sources are read from the lower of the two
+  uint8_t *dy, *du, *dv;
+  int src_stride_y, src_stride_uv, dst_stride_y, dst_stride_uv;
+  int width, height, cw, ch;
+  int src_il, dst_il;      // 0 planar, 1 interleaved U first, 2 interleaved V first
+  long long src_step, dst_step;
+};
+__global__ void __launch_bounds__(256) yuv_repack_rows_kernel(const __grid_constant__ YuvRepackParams P) {
+  const int f = blockIdx.z >> 1;
+  const long long so = (long long)f * P.src_step, dof = (long long)f * P.dst_step;
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y * blockDim.y + threadIdx.y;
+  if ((blockIdx.z & 1) == 0) {
+    if (!P.dy || x * 16 >= P.width || r >= P.height) return;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(P.sy + so + (long long)r * P.src_stride_y) + x);
+    reinterpret_cast<uint4*>(P.dy + dof + (long long)r * P.dst_stride_y)[x] = v;
+    return;
+  }
+  if (x * 8 >= P.cw || r >= P.ch) return;
+  uint2 u, v;  // eight U bytes, eight V bytes
+  if (P.src_il) {
+    const uint8_t* base = (P.src_il == 1 ? P.su : P.sv) + so + (long long)r * P.src_stride_uv;
+    const uint4 w = __ldg(reinterpret_cast<const uint4*>(base) + x);   // (first, second) x 8
+    const uint2 first = make_uint2(__byte_perm(w.x, w.y, 0x6420), __byte_perm(w.z, w.w, 0x6420));
+    const uint2 second = make_uint2(__byte_perm(w.x, w.y, 0x7531), __byte_perm(w.z, w.w, 0x7531));
+    u = P.src_il == 1 ? first : second;
+    v = P.src_il == 1 ? second : first;
+  } else {
+    u = __ldg(reinterpret_cast<const uint2*>(P.su + so + (long long)r * P.src_stride_uv) + x);
+    v = __ldg(reinterpret_cast<const uint2*>(P.sv + so + (long long)r * P.src_stride_uv) + x);
+  }
+  if (P.dst_il) {
+    const uint2 first = P.dst_il == 1 ? u : v, second = P.dst_il == 1 ? v : u;
+    uint8_t* base = (P.dst_il == 1 ? P.du : P.dv) + dof + (long long)r * P.dst_stride_uv;
+    reinterpret_cast<uint4*>(base)[x] = make_uint4(__byte_perm(first.x, second.x, 0x5140), __byte_perm(first.x, second.x, 0x7362),
+                                                   __byte_perm(first.y, second.y, 0x5140), __byte_perm(first.y, second.y, 0x7362));
+  } else {
+    reinterpret_cast<uint2*>(P.du + dof + (long long)r * P.dst_stride_uv)[x] = u;
+    reinterpret_cast<uint2*>(P.dv + dof + (long long)r * P.dst_stride_uv)[x] = v;
+  }
+}
+static bool yuv_map_is_identity(const BandCuAffine& m) {
+  return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
+}
+// BANDCU_E_UNSUPPORTED: index maps, widths that are not whole vectors, unaligned planes.
+static int launch_yuv_repack_rows(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, long long src_step, long long dst_step, int n,
+                                  cudaStream_t stream) {
+  static const bool off = getenv("BANDCU_DISABLE_COPY_ROWS") && getenv("BANDCU_DISABLE_COPY_ROWS")[0] == '1';
+  if (off || !yuv_map_is_identity(d.luma_map) || !yuv_map_is_identity(d.chroma_map) || d.chroma_width_override > 0)
+    return BANDCU_E_UNSUPPORTED;
+  YuvRepackParams P;
+  memset(&P, 0, sizeof(P));
+  auto layout = [](int ps, const void* u, const void* v) {
+    if (ps == 1) return 0;
+    const long long dd = (const uint8_t*)v - (const uint8_t*)u;
+    return ps == 2 && dd == 1 ? 1 : ps == 2 && dd == -1 ? 2 : -1;
+  };
+  P.src_il = layout(d.src_pixel_stride_uv, p.su, p.sv);
+  P.dst_il = layout(d.dst_pixel_stride_uv, p.du, p.dv);
+  if (P.src_il < 0 || P.dst_il < 0) return BANDCU_E_UNSUPPORTED;
+  P.width = d.dst_width; P.height = d.dst_height;
+  P.cw = (d.dst_width + 1) / 2; P.ch = (d.dst_height + 1) / 2;
+  if ((P.cw & 7) || (p.dy && (P.width & 15))) return BANDCU_E_UNSUPPORTED;
+  const uintptr_t steps = n == 1 ? 0 : ((uintptr_t)src_step | (uintptr_t)dst_step);
+  uintptr_t bits = steps | (uintptr_t)d.src_stride_uv | (uintptr_t)d.dst_stride_uv;
+  if (p.dy) bits |= reinterpret_cast<uintptr_t>(p.sy) | reinterpret_cast<uintptr_t>(p.dy) | (uintptr_t)d.src_stride_y | (uintptr_t)d.dst_stride_y;
+  // interleaved planes move as 16-byte vectors from the lower pointer, planar ones as 8-byte vectors
+  const uintptr_t sb = P.src_il ? reinterpret_cast<uintptr_t>(P.src_il == 1 ? p.su : p.sv)
+                                : ((reinterpret_cast<uintptr_t>(p.su) | reinterpret_cast<uintptr_t>(p.sv)) << 1);
+  const uintptr_t db = P.dst_il ? reinterpret_cast<uintptr_t>(P.dst_il == 1 ? p.du : p.dv)
+                                : ((reinterpret_cast<uintptr_t>(p.du) | reinterpret_cast<uintptr_t>(p.dv)) << 1);
+  if ((bits | sb | db) & 15) return BANDCU_E_UNSUPPORTED;
+  P.sy = (const uint8_t*)p.sy; P.su = (const uint8_t*)p.su; P.sv = (const uint8_t*)p.sv;
+  P.dy = (uint8_t*)p.dy; P.du = (uint8_t*)p.du; P.dv = (uint8_t*)p.dv;
+  P.src_stride_y = d.src_stride_y; P.src_stride_uv = d.src_stride_uv;
+  P.dst_stride_y = d.dst_stride_y; P.dst_stride_uv = d.dst_stride_uv;
+  P.src_step = src_step; P.dst_step = dst_step;
+  const dim3 block(32, 8, 1);
+  const int gx = std::max((P.width / 16 + 31) / 32, (P.cw / 8 + 31) / 32), gy = (P.height + 7) / 8;
+  for (int done = 0; done < n;) {
+    const int chunk = n - done > 32767 ? 32767 : n - done;
+    YuvRepackParams Q = P;
+    const long long so = (long long)done * src_step, dof = (long long)done * dst_step;
+    Q.sy += so; Q.su += so; Q.sv += so;
+    if (Q.dy) Q.dy += dof;
+    Q.du += dof; Q.dv += dof;
+    yuv_repack_rows_kernel<<<dim3(gx, gy, 2 * chunk), block, 0, stream>>>(Q);
+    count_launch();
+    done += chunk;
+  }
+  return (int)cudaGetLastError();
+}
+
 int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, long long src_step, long long dst_step, int n,
                    cudaStream_t stream) {
   {
     const int e = launch_plane_map_tiles(d, p, src_step, dst_step, n, stream);
+    if (e != BANDCU_E_UNSUPPORTED) return e;
+  }
+  {
+    const int e = launch_yuv_repack_rows(d, p, src_step, dst_step, n, stream);
     if (e != BANDCU_E_UNSUPPORTED) return e;
   }
   YuvMapParams P;
@@ -803,8 +906,130 @@ __global__ void __launch_bounds__(256) rgb_to_yuv420_kernel(const __grid_constan
   ((uint8_t*)P.p.du)[o] = (uint8_t)((56 * ab - 37 * ag - 19 * ar + 0x8080) >> 8);
   ((uint8_t*)P.p.dv)[o] = (uint8_t)((56 * ar - 47 * ag - 9 * ab + 0x8080) >> 8);
 }
+// Row form of the same conversion for untouched, word-aligned sources (the common case: a decoded RGBA / RGB frame
+// going to the encoder or to a 4:2:0 model input). The one-thread-per-chroma-sample kernel above issues twelve byte
+// loads and up to six byte stores per 2x2 block (0.50 of the measured HBM bandwidth on 1080p RGBA -> NV21). Here a
+// thread owns FOUR pixels of TWO rows: two 128-bit loads (RGBA) or six 32-bit loads (RGB, re-cut into pixel words by
+// funnel shifts), luma as one dot product per pixel (IDP4A: 66 R + 129 G + 25 B), the 2x2 channel sums in packed 16-bit
+// lanes, and word stores: four luma bytes per row, and both chroma samples of the thread (one word when the chroma is
+// interleaved, two half-words when it is planar). A warp reads 512 contiguous bytes per row and writes 128.
+// CH: 3 / 4 source bytes per pixel. UVMODE: 0 planar, 1 interleaved U first (NV12), 2 interleaved V first (NV21).
+template <int CH, int UVMODE>
+__global__ void __launch_bounds__(256) rgb_to_yuv420_rows_kernel(const __grid_constant__ RgbToYuvParams P) {
+  const BandCuRgbToYuvDesc& d = P.d;
+  const int x4 = blockIdx.x * blockDim.x + threadIdx.x;   // group of four pixels
+  const int cy = blockIdx.y * blockDim.y + threadIdx.y;   // chroma row = pair of luma rows
+  if (x4 * 4 >= d.width || cy * 2 >= d.height) return;
+  const long long do_f = (long long)blockIdx.z * P.dst_step;
+  const uint8_t* src = (const uint8_t*)P.p.src + (long long)blockIdx.z * P.src_step +
+                       (long long)(d.src_map.r0 + 2 * cy) * d.src_stride + (long long)(d.src_map.c0 + 4 * x4) * CH;
+  uint32_t px[2][4];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const uint8_t* q = src + (long long)r * d.src_stride;
+    if (CH == 4) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(q));
+      px[r][0] = v.x; px[r][1] = v.y; px[r][2] = v.z; px[r][3] = v.w;
+    } else {
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(q);
+      const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);  // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+      px[r][0] = w0;
+      px[r][1] = __funnelshift_r(w0, w1, 24);
+      px[r][2] = __funnelshift_r(w1, w2, 16);
+      px[r][3] = w2 >> 8;
+    }
+  }
+  // luma: (66 R + 129 G + 25 B + 0x1080) >> 8, byte 3 of a pixel word (alpha or the next pixel's red) weighs 0
+  uint8_t* dy = (uint8_t*)P.p.dy + do_f + (long long)(2 * cy) * d.dst_stride_y + 4 * x4;
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    uint32_t y[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) y[k] = __dp4a(px[r][k], 0x00198142u, 0x1080u) >> 8;
+    *reinterpret_cast<uint32_t*>(dy + (long long)r * d.dst_stride_y) = y[0] | (y[1] << 8) | (y[2] << 16) | (y[3] << 24);
+  }
+  // chroma: sums of R | B and of G over each 2x2 block in 16-bit lanes, "2x" average (sum + 1) >> 1
+  uint32_t uv[2][2];
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const uint32_t a = px[0][2 * c], b = px[0][2 * c + 1], e = px[1][2 * c], f = px[1][2 * c + 1];
+    const uint32_t rb = (a & 0x00FF00FFu) + (b & 0x00FF00FFu) + (e & 0x00FF00FFu) + (f & 0x00FF00FFu);
+    const uint32_t g = ((a >> 8) & 0xFFu) + ((b >> 8) & 0xFFu) + ((e >> 8) & 0xFFu) + ((f >> 8) & 0xFFu);
+    const int ar = (int)(((rb & 0xFFFFu) + 1u) >> 1), ab = (int)(((rb >> 16) + 1u) >> 1), ag = (int)((g + 1u) >> 1);
+    uv[c][0] = (uint32_t)((56 * ab - 37 * ag - 19 * ar + 0x8080) >> 8) & 0xFFu;
+    uv[c][1] = (uint32_t)((56 * ar - 47 * ag - 9 * ab + 0x8080) >> 8) & 0xFFu;
+  }
+  const long long co = do_f + (long long)cy * d.dst_stride_uv;
+  if (UVMODE == 0) {
+    *reinterpret_cast<uint16_t*>((uint8_t*)P.p.du + co + 2 * x4) = (uint16_t)(uv[0][0] | (uv[1][0] << 8));
+    *reinterpret_cast<uint16_t*>((uint8_t*)P.p.dv + co + 2 * x4) = (uint16_t)(uv[0][1] | (uv[1][1] << 8));
+  } else {
+    const int f = UVMODE == 1 ? 0 : 1, s2 = 1 - f;   // first / second byte of a pair
+    uint8_t* base = (uint8_t*)(UVMODE == 1 ? P.p.du : P.p.dv);
+    *reinterpret_cast<uint32_t*>(base + co + 4 * x4) = uv[0][f] | (uv[0][s2] << 8) | (uv[1][f] << 16) | (uv[1][s2] << 24);
+  }
+}
+
+// BANDCU_E_UNSUPPORTED: a source behind an index map other than a word-aligned crop, odd sizes, unaligned planes.
+static int launch_rgb_to_yuv_rows(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, long long src_step, long long dst_step,
+                                  int n, cudaStream_t stream) {
+  static const bool off = getenv("BANDCU_DISABLE_COPY_ROWS") && getenv("BANDCU_DISABLE_COPY_ROWS")[0] == '1';
+  if (off) return BANDCU_E_UNSUPPORTED;
+  const BandCuAffine& m = d.src_map;
+  if (!(m.rr == 1 && m.rc == 0 && m.cr == 0 && m.cc == 1 && m.r0 >= 0 && m.c0 >= 0)) return BANDCU_E_UNSUPPORTED;
+  if ((d.width & 3) || (d.height & 1)) return BANDCU_E_UNSUPPORTED;
+  const int CH = d.src_channels;
+  const uintptr_t steps = n == 1 ? 0 : ((uintptr_t)src_step | (uintptr_t)dst_step);
+  const uintptr_t sbits = reinterpret_cast<uintptr_t>(p.src) | (uintptr_t)d.src_stride | (uintptr_t)((long long)m.c0 * CH) | steps;
+  if (sbits & (CH == 4 ? 15 : 3)) return BANDCU_E_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(p.dy) | (uintptr_t)d.dst_stride_y | steps) & 3) return BANDCU_E_UNSUPPORTED;
+  int uvmode;
+  if (d.dst_pixel_stride_uv == 1) {
+    uvmode = 0;
+    if ((reinterpret_cast<uintptr_t>(p.du) | reinterpret_cast<uintptr_t>(p.dv) | (uintptr_t)d.dst_stride_uv | steps) & 1)
+      return BANDCU_E_UNSUPPORTED;
+  } else if (d.dst_pixel_stride_uv == 2) {
+    const long long dd = (const uint8_t*)p.dv - (const uint8_t*)p.du;
+    if (dd != 1 && dd != -1) return BANDCU_E_UNSUPPORTED;
+    uvmode = dd == 1 ? 1 : 2;
+    const void* first = dd == 1 ? p.du : p.dv;
+    if ((reinterpret_cast<uintptr_t>(first) | (uintptr_t)d.dst_stride_uv | steps) & 3) return BANDCU_E_UNSUPPORTED;
+  } else {
+    return BANDCU_E_UNSUPPORTED;
+  }
+  RgbToYuvParams P;
+  P.d = d;
+  P.src_step = src_step;
+  P.dst_step = dst_step;
+  const dim3 block(32, 8, 1);
+  const dim3 grid_xy((d.width / 4 + 31) / 32, (d.height / 2 + 7) / 8, 1);
+  for (int done = 0; done < n;) {
+    const int chunk = n - done > 65535 ? 65535 : n - done;
+    const long long so = (long long)done * src_step, dof = (long long)done * dst_step;
+    P.p.src = (const uint8_t*)p.src + so;
+    P.p.dy = (uint8_t*)p.dy + dof; P.p.du = (uint8_t*)p.du + dof; P.p.dv = (uint8_t*)p.dv + dof;
+    const dim3 grid(grid_xy.x, grid_xy.y, chunk);
+    if (CH == 4) {
+      if (uvmode == 0) rgb_to_yuv420_rows_kernel<4, 0><<<grid, block, 0, stream>>>(P);
+      else if (uvmode == 1) rgb_to_yuv420_rows_kernel<4, 1><<<grid, block, 0, stream>>>(P);
+      else rgb_to_yuv420_rows_kernel<4, 2><<<grid, block, 0, stream>>>(P);
+    } else {
+      if (uvmode == 0) rgb_to_yuv420_rows_kernel<3, 0><<<grid, block, 0, stream>>>(P);
+      else if (uvmode == 1) rgb_to_yuv420_rows_kernel<3, 1><<<grid, block, 0, stream>>>(P);
+      else rgb_to_yuv420_rows_kernel<3, 2><<<grid, block, 0, stream>>>(P);
+    }
+    count_launch();
+    done += chunk;
+  }
+  return (int)cudaGetLastError();
+}
+
 int launch_rgb_to_yuv(const BandCuRgbToYuvDesc& d, const BandCuRgbToYuvPtrs& p, long long src_step, long long dst_step,
                       int n, cudaStream_t stream) {
+  {
+    const int e = launch_rgb_to_yuv_rows(d, p, src_step, dst_step, n, stream);
+    if (e != BANDCU_E_UNSUPPORTED) return e;
+  }
   RgbToYuvParams P;
   P.d = d;
   P.src_step = src_step;

@@ -267,6 +267,12 @@ def g_cases(steps):
         image_case("g_1080p_nv21_to_gray", [(csc, B.kBandGrayScale)], W, H, B.kBandNV21, B.kBandGrayScale, W, H, n, steps),
         image_case("g_1080p_rgb_to_gray", [(csc, B.kBandGrayScale)], W, H, B.kBandRGB, B.kBandGrayScale, W, H, n, steps),
         image_case("g_1080p_rgba_to_nv21", [(csc, B.kBandNV21)], W, H, B.kBandRGBA, B.kBandNV21, W, H, n, steps),
+        image_case("g_1080p_rgb_to_yv12", [(csc, B.kBandYV12)], W, H, B.kBandRGB, B.kBandYV12, W, H, n, steps),
+        image_case("g_1080p_nv12_to_yv12_repack", [(csc, B.kBandYV12)], W, H, B.kBandNV12, B.kBandYV12, W, H, n, steps),
+        image_case("g_1080p_yv12_to_nv21_repack", [(csc, B.kBandNV21)], W, H, B.kBandYV12, B.kBandNV21, W, H, n, steps),
+        image_case("g_1080p_yv12_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandYV12, B.kBandYV12, H, W, n, steps),
+        image_case("g_1080p_rgba_rot270", [(B.BAND_ROTATE, 270)], W, H, B.kBandRGBA, B.kBandRGBA, H, W, n, steps),
+        image_case("g_1080p_gray_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandGrayScale, B.kBandGrayScale, H, W, n, steps),
         image_case("g_1080p_nv21_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandNV21, B.kBandNV21, H, W, n, steps),
         image_case("g_1080p_rgb_rot90", [(B.BAND_ROTATE, 90)], W, H, B.kBandRGB, B.kBandRGB, H, W, n, steps),
         image_case("g_1080p_nv21_flip_h", [(B.BAND_FLIP, 1, 0)], W, H, B.kBandNV21, B.kBandNV21, W, H, n, steps),
