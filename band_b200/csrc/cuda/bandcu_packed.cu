@@ -317,9 +317,132 @@ __global__ void __launch_bounds__(128) packed_up_rows_x16_kernel(const __grid_co
   }
 }
 
+typedef void (*PackedKernel)(PackedParams);
+// Small sources (the 64^2 end of BASELINE's RGBA sweep): Scale*BilinearUp as libyuv does it -- every source row filtered
+// horizontally ONCE, then output rows blended from pairs of filtered rows -- with the whole frame in shared memory.
+// The row-streaming kernels above filter a source row pair per thread strip straight from global memory: for a 64x64
+// source and a 2x - 4x up-scale that is a chain of dependent L2 round trips per thread and a handful of warps per frame
+// (ncu-free arithmetic: 7.9 M frames/s on RGBA 64^2 -> gray 128^2 = 0.04 of the HBM roofline). Here ONE CTA owns one
+// frame: (1) the source is staged with 128-bit loads, converted on the way (RGBA -> gray bytes / RGB words);
+// (2) pass 1 writes hf[r][ox] = column filter of source row r at output column ox for all sh rows (gray: four pixels
+// per thread packed into one word; RGB / RGBA: one pixel word each); (3) pass 2 blends hf[yi], hf[yi+1] per output row
+// with the packed InterpolateRow arithmetic and stores whole words, lanes along the output row.
+// Same clamps and blenders as packed_bilinear_kernel<.., kPackedUp, ..>; the parity tests compare with the oracle.
+template <int SRCCH, int CVT, int OUTCH>
+__global__ void __launch_bounds__(256) packed_small_up_kernel(const __grid_constant__ PackedParams P) {
+  constexpr bool PLANE = (OUTCH == 1);
+  constexpr int SB = PLANE ? 1 : 4;           // bytes per staged source element and per filtered element
+  extern __shared__ __align__(16) uint8_t sm[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // warps walk rows, lanes walk along a row: no divisions
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.x);
+  const int src_pitch = (P.sw * SB + 15) & ~15;        // staged source row pitch
+  const int hf_pitch = (P.dw * SB + 3) & ~3;           // filtered row pitch (bytes)
+  uint8_t* ssrc = sm;
+  uint8_t* hf = sm + P.sh * src_pitch;
+  // ---- stage + convert the source frame
+  if (SRCCH == 4) {
+    const int n4 = P.sw >> 2;  // groups of four pixels (sw % 4 == 0, 16-byte aligned rows: checked on the host)
+    for (int r = wid; r < P.sh; r += 8)
+    for (int g = lane; g < n4; g += 32) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(f.p0 + (size_t)r * P.stride0) + g);
+      if (PLANE) {
+        const uint32_t y0 = rgb_to_yj(v.x & 0xFF, (v.x >> 8) & 0xFF, (v.x >> 16) & 0xFF), y1 = rgb_to_yj(v.y & 0xFF, (v.y >> 8) & 0xFF, (v.y >> 16) & 0xFF);
+        const uint32_t y2 = rgb_to_yj(v.z & 0xFF, (v.z >> 8) & 0xFF, (v.z >> 16) & 0xFF), y3 = rgb_to_yj(v.w & 0xFF, (v.w >> 8) & 0xFF, (v.w >> 16) & 0xFF);
+        *reinterpret_cast<uint32_t*>(ssrc + r * src_pitch + 4 * g) = y0 | (y1 << 8) | (y2 << 16) | (y3 << 24);
+      } else {
+        const uint32_t m = CVT == BANDCU_CVT_RGBA2RGB ? 0x00FFFFFFu : 0xFFFFFFFFu;
+        *reinterpret_cast<uint4*>(ssrc + r * src_pitch + 16 * g) = make_uint4(v.x & m, v.y & m, v.z & m, v.w & m);
+      }
+    }
+  } else {  // gray or RGB sources: element-wise through the read-only path
+    for (int r = wid; r < P.sh; r += 8)
+    for (int c = lane; c < P.sw; c += 32) {
+      const uint32_t v = packed_fetch<SRCCH, CVT>(f.p0 + (size_t)r * P.stride0, c);
+      if (PLANE) ssrc[r * src_pitch + c] = (uint8_t)v;
+      else *reinterpret_cast<uint32_t*>(ssrc + r * src_pitch + 4 * c) = v;
+    }
+  }
+  __syncthreads();
+  // ---- pass 1: horizontal filter of every source row
+  auto hpixel = [&](const uint8_t* row, int ox) {
+    const int x = P.x0 + ox * P.dx;
+    const int xi = x >> 16;
+    const int c0 = min(max(xi, 0), P.sw - 1), c1 = min(max(xi + 1, 0), P.sw - 1);
+    if (PLANE) return packed_hblend<true>((uint32_t)row[c0], (uint32_t)row[c1], x);
+    return packed_hblend<false>(reinterpret_cast<const uint32_t*>(row)[c0], reinterpret_cast<const uint32_t*>(row)[c1], x);
+  };
+  if (PLANE) {
+    const int wpr = hf_pitch >> 2;  // words per filtered row
+    for (int r = wid; r < P.sh; r += 8)
+    for (int w = lane; w < wpr; w += 32) {
+      const uint8_t* row = ssrc + r * src_pitch;
+      const int ox = 4 * w;
+      uint32_t v = hpixel(row, min(ox, P.dw - 1)) & 0xFF;
+      v |= (hpixel(row, min(ox + 1, P.dw - 1)) & 0xFF) << 8;
+      v |= (hpixel(row, min(ox + 2, P.dw - 1)) & 0xFF) << 16;
+      v |= hpixel(row, min(ox + 3, P.dw - 1)) << 24;
+      *reinterpret_cast<uint32_t*>(hf + r * hf_pitch + 4 * w) = v;
+    }
+  } else {
+    for (int r = wid; r < P.sh; r += 8)
+      for (int ox = lane; ox < P.dw; ox += 32)
+        *reinterpret_cast<uint32_t*>(hf + r * hf_pitch + 4 * ox) = hpixel(ssrc + r * src_pitch, ox);
+  }
+  __syncthreads();
+  // ---- pass 2: vertical blend, whole output words, lanes along the row
+  const int row_bytes = P.dw * OUTCH;
+  const int row_words = (row_bytes + 3) >> 2, full_words = row_bytes >> 2;
+  // work item = (output row, group of NG words): gray / RGBA one word, RGB three words = four pixels
+  constexpr int NG = OUTCH == 3 ? 3 : 1;
+  const int gpr = (row_words + NG - 1) / NG;
+  for (int oy = wid; oy < P.dh; oy += 8) {
+    const int y = min(P.y0 + oy * P.dy, P.max_y);
+    const int yi = y >> 16;
+    const int yf = P.linear ? 0 : ((y >> 8) & 255);
+    const int r0 = min(max(yi, 0), P.sh - 1), r1 = min(max(yi + 1, 0), P.sh - 1);
+    const uint32_t* h0 = reinterpret_cast<const uint32_t*>(hf + r0 * hf_pitch);
+    const uint32_t* h1 = reinterpret_cast<const uint32_t*>(hf + r1 * hf_pitch);
+    uint8_t* orow = f.out + (long long)oy * P.dst_row_stride;
+   for (int g = lane; g < gpr; g += 32) {
+    uint32_t v[NG];
+    if (OUTCH == 3) {
+      uint32_t px[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int ox = min(4 * g + k, P.dw - 1);
+        px[k] = interp_rows4(h0[ox], h1[ox], yf);
+      }
+      v[0] = __byte_perm(px[0], px[1], 0x4210);
+      v[1] = __byte_perm(px[1], px[2], 0x5421);
+      v[2] = __byte_perm(px[2], px[3], 0x6542);
+    } else {
+      v[0] = interp_rows4(h0[g], h1[g], yf);
+    }
+#pragma unroll
+    for (int q = 0; q < NG; ++q) {
+      const int w = NG * g + q;
+      if (w < full_words && P.vec_ok) reinterpret_cast<uint32_t*>(orow)[w] = v[q];
+      else if (w < row_words) for (int k = 4 * w; k < row_bytes; ++k) orow[k] = (uint8_t)(v[q] >> (8 * (k - 4 * w)));
+    }
+   }
+  }
+}
+template <int SRCCH, int CVT, int OUTCH>
+static PackedKernel packed_small_up_of() { return packed_small_up_kernel<SRCCH, CVT, OUTCH>; }
+static PackedKernel packed_pick_small_up(const BandCuPlanDesc& d) {
+  if (d.src_kind == BANDCU_SRC_GRAY && d.cvt == BANDCU_CVT_NONE) return packed_small_up_of<1, BANDCU_CVT_NONE, 1>();
+  if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_NONE) return packed_small_up_of<3, BANDCU_CVT_NONE, 3>();
+  if (d.src_kind == BANDCU_SRC_RGB && d.cvt == BANDCU_CVT_RGB2GRAY) return packed_small_up_of<3, BANDCU_CVT_RGB2GRAY, 1>();
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_NONE) return packed_small_up_of<4, BANDCU_CVT_NONE, 4>();
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2GRAY) return packed_small_up_of<4, BANDCU_CVT_RGBA2GRAY, 1>();
+  if (d.src_kind == BANDCU_SRC_RGBA && d.cvt == BANDCU_CVT_RGBA2RGB) return packed_small_up_of<4, BANDCU_CVT_RGBA2RGB, 3>();
+  return nullptr;
+}
+
 struct PackedPlan {
   float* lut_dev;
   int up_rows_mode;  // BANDCU_PACKED_UP_ROWS when the plan was created: -1 default, 0 off, 2 word-interleaved form
+  int small_up;      // BANDCU_PACKED_SMALL_UP != 0 when the plan was created: shared-memory kernel for small sources
 };
 
 __global__ void packed_build_lut_kernel(float* lut, float mean, float sd) {
@@ -353,6 +476,8 @@ int packed_plan_create(const BandCuPlanDesc& d, PackedPlan** out) {
   p->lut_dev = nullptr;
   const char* ur = getenv("BANDCU_PACKED_UP_ROWS");  // read here, once per plan (never on the launch path)
   p->up_rows_mode = (ur && ur[0] >= '0' && ur[0] <= '9') ? ur[0] - '0' : -1;
+  const char* su = getenv("BANDCU_PACKED_SMALL_UP");
+  p->small_up = (su && su[0] == '0') ? 0 : 1;
   if (d.normalize) {
     cudaError_t e = cudaMalloc((void**)&p->lut_dev, 256 * sizeof(float));
     if (e != cudaSuccess) { delete p; return (int)e; }
@@ -371,7 +496,6 @@ void packed_plan_destroy(PackedPlan* p) {
   delete p;
 }
 
-typedef void (*PackedKernel)(PackedParams);
 template <int SRCCH, int CVT, int OUTCH>
 static PackedKernel packed_pick2(int mode, bool f32, int up_rows) {
   if (mode == kPackedUp) {
@@ -442,6 +566,41 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
       P.up_rows = rpt;
       block = dim3(32, 4, 1);  // each thread: its words of P.up_rows rows
       grid = dim3((row_words + per_warp - 1) / per_warp, (d.dst_height + 4 * rpt - 1) / (4 * rpt), 1);
+    }
+  }
+  // small sources: the whole frame and its column-filtered rows fit shared memory -> one CTA per frame
+  if (d.scale_mode == BANDCU_SCALE_BILINEAR_UP && !d.normalize && p->up_rows_mode != 0 && p->small_up != 0) {
+    const int sb = d.channels == 1 ? 1 : 4;
+    const size_t smem = (size_t)d.vh * ((d.vw * sb + 15) & ~15) + (size_t)d.vh * ((d.dst_width * sb + 3) & ~3);
+    const bool src_ok = d.src_kind != BANDCU_SRC_RGBA ||
+                        ((d.vw & 3) == 0 && d.stride0 % 16 == 0 &&
+                         (batch.table ? hints.aligned16
+                                      : ((reinterpret_cast<uintptr_t>(batch.first.p0) & 15) == 0 && (n == 1 || batch.in_stride % 16 == 0))));
+    bool out4;
+    if (batch.table) out4 = hints.out_aligned16;
+    else out4 = (reinterpret_cast<uintptr_t>(batch.first.out) & 3) == 0 && (n == 1 || batch.out_stride % 4 == 0);
+    PackedKernel small = packed_pick_small_up(d);
+    // one CTA per frame only pays while a frame is a few tens of KB: measured +5 % on RGBA 64^2 -> RGB 128^2 and +2 % on
+    // -> gray 256^2, but -27 % on -> RGB 256^2 (196 KB of output per CTA) and -38 % on -> gray 1024^2
+    const size_t out_bytes = (size_t)d.dst_width * d.dst_height * d.channels;
+    if (small && src_ok && smem <= 48 * 1024 && out_bytes <= 64 * 1024) {
+      P.vec_ok = (out4 && d.dst_row_stride % 4 == 0) ? 1 : 0;
+      cudaError_t e = cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+      for (int done = 0; done < n;) {
+        const int chunk = n - done > (1 << 30) ? (1 << 30) : n - done;
+        P.batch = batch;
+        if (P.batch.table) {
+          P.batch.table += done;
+        } else {
+          P.batch.first.p0 += (long long)done * batch.in_stride;
+          P.batch.first.out += (long long)done * batch.out_stride;
+        }
+        small<<<chunk, 256, smem, stream>>>(P);
+        count_launch();
+        done += chunk;
+      }
+      return (int)cudaGetLastError();
     }
   }
   PackedKernel kern = packed_pick(d, up_rows);
