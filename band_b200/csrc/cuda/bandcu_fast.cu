@@ -305,7 +305,7 @@ __device__ __forceinline__ uint32_t vblend2(uint32_t top, uint32_t bot, uint32_t
 }
 // ScaleARGBFilterCols_C on a packed pair: (L*(0x7f^xf) + R*xf) >> 7, truncating. wp = xf | (0x7f^xf) << 16, so
 // (L | R<<16) * wp = L*xf + (L*(0x7f^xf) + R*xf) << 16 (+ a term beyond bit 31); L*xf < 65536 never carries.
-// Returns the product: the 8-bit result sits in bits 23..30.
+// Returns the product: the 8-bit result sits in bits 23..30 (bits 24..31 with the weights shifted left once, as the kernel passes them).
 __device__ __forceinline__ uint32_t hblend_pair_raw(uint32_t v2, uint32_t wp) { return v2 * wp; }
 
 constexpr int kLutCopies = 8;  // the Normalize table is replicated so that lanes l and l' (l != l' mod 8) never collide
@@ -384,7 +384,9 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
         const int x = P.x0 + ox * P.dx;
         const uint32_t xi = (uint32_t)(x >> 16);
         const uint32_t xf = (uint32_t)((x >> 9) & 0x7f);
-        const uint32_t wp = xf | ((0x7fu ^ xf) << 16);
+        // column weights pre-shifted by one bit: the blended byte then lands in bits 24..31 of the product (a plain shift
+        // extracts it; no mask) -- 2 L xf < 65536 still cannot carry into the upper half
+        const uint32_t wp = (xf << 1) | ((0x7fu ^ xf) << 17);
         // byte offsets inside one staged row group: luma pair, left / right chroma pair (slot 2 = top chroma row)
         const uint32_t csh = CH == kChromaPlanar ? 0u : 1u;  // planar rows hold one byte per chroma sample
         const uint32_t cL = 2u * pitch + ((xi >> 1) << csh), cR = 2u * pitch + (((xi + 1u) >> 1) << csh);
@@ -406,18 +408,18 @@ __global__ void __launch_bounds__(1024) fast_nv_bilinear_down_kernel(const __gri
           const uint32_t b = hblend_pair_raw(vblend2(tb, bb, w0, w1), wp);
           if (sizeof(OT) == 1) {
             if (P.lut) {  // Normalize into a one-byte type (int8 / uint8 model inputs): the table holds the byte
-              o[0] = (uint8_t)lds_u32(lut_lane + ((r >> 18) & 0x1FE0u));
-              o[1] = (uint8_t)lds_u32(lut_lane + ((gq >> 18) & 0x1FE0u));
-              o[2] = (uint8_t)lds_u32(lut_lane + ((b >> 18) & 0x1FE0u));
+              o[0] = (uint8_t)lds_u32(lut_lane + (r >> 24) * (4u * kLutCopies));
+              o[1] = (uint8_t)lds_u32(lut_lane + (gq >> 24) * (4u * kLutCopies));
+              o[2] = (uint8_t)lds_u32(lut_lane + (b >> 24) * (4u * kLutCopies));
             } else {
-              o[0] = (uint8_t)(r >> 23); o[1] = (uint8_t)(gq >> 23); o[2] = (uint8_t)(b >> 23);
+              o[0] = (uint8_t)(r >> 24); o[1] = (uint8_t)(gq >> 24); o[2] = (uint8_t)(b >> 24);
             }
           } else {
-            // table index v = raw >> 23; byte offset v * 4 * kLutCopies = (raw >> 18) & 0x1FE0
+            // table index v = raw >> 24; byte offset v * 4 * kLutCopies + this lane's copy: one shift and one multiply-add
             float* of = reinterpret_cast<float*>(o);
-            of[0] = lds_f32(lut_lane + ((r >> 18) & 0x1FE0u));
-            of[1] = lds_f32(lut_lane + ((gq >> 18) & 0x1FE0u));
-            of[2] = lds_f32(lut_lane + ((b >> 18) & 0x1FE0u));
+            of[0] = lds_f32(lut_lane + (r >> 24) * (4u * kLutCopies));
+            of[1] = lds_f32(lut_lane + (gq >> 24) * (4u * kLutCopies));
+            of[2] = lds_f32(lut_lane + (b >> 24) * (4u * kLutCopies));
           }
         }
       }
