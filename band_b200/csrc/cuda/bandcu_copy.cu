@@ -23,6 +23,7 @@ struct CopyParams {
   long long luma_off, chroma_off;  // crop origin folded into the plane pointers
   long long dst_row_stride;
   int out16;                // output rows are 16-byte aligned (RGBA: one 128-bit store per thread and row)
+  float mean, std_;         // f32 variant: Normalize behind the conversion
 };
 
 // ---- packed LEFT|RIGHT pixel pairs: both lanes share one chroma sample ----
@@ -159,6 +160,47 @@ __global__ void __launch_bounds__(256) yuv_copy_rows_kernel(const __grid_constan
   }
 }
 
+// ColorSpaceConvert(RGB) -> Normalize into float32 with NO Resize in between (a model fed at camera resolution; the
+// reference runs NV12ToRAW and then NormalizeFromTo<uint8, float>, common_operator.cc:24-40). Same four-pixel, two-row
+// threads as above; the twelve bytes of a row group go through a 256-entry table built by the CTA with the element
+// arithmetic of the other kernels (IEEE subtract and divide) and leave as three 128-bit stores: a warp writes 1.5 KB
+// of contiguous floats per row. The pixel-per-thread kernel was the only path for this chain before.
+template <int CH>
+__global__ void __launch_bounds__(256) yuv_copy_rows_f32_kernel(const __grid_constant__ CopyParams P) {
+  __shared__ float lut[256];
+  lut[threadIdx.y * 32 + threadIdx.x] = normalize_elem<float>((float)(threadIdx.y * 32 + threadIdx.x), P.mean, P.std_);
+  __syncthreads();
+  const int x = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y = (blockIdx.y * 8 + threadIdx.y) * 2;
+  if (x >= P.W || y >= P.H) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  const uint8_t* yp = f.p0 + P.luma_off + (long long)y * P.stride0 + x;
+  const bool two = y + 1 < P.H;
+  const long long coff = P.chroma_off + (long long)(y >> 1) * P.stride_uv;
+  const uint32_t y0 = __ldg(reinterpret_cast<const uint32_t*>(yp));
+  const uint32_t y1 = two ? __ldg(reinterpret_cast<const uint32_t*>(yp + P.stride0)) : y0;
+  uint32_t w = 0, uu = 0, vv = 0;
+  if (CH == kCopyPlanar) {
+    uu = __ldg(reinterpret_cast<const uint16_t*>(f.pu + coff + (x >> 1)));
+    vv = __ldg(reinterpret_cast<const uint16_t*>(f.pv + coff + (x >> 1)));
+  } else {
+    w = __ldg(reinterpret_cast<const uint32_t*>((CH == kCopyVU ? f.pv : f.pu) + coff + x));
+  }
+  CChroma ca, cb;
+  c_group_chroma<CH>(w, uu, vv, ca, cb);
+  float4* op = reinterpret_cast<float4*>(f.out + (long long)y * P.dst_row_stride) + 3 * (x >> 2);
+#pragma unroll
+  for (int row = 0; row < 2; ++row) {
+    if (row == 1 && !two) break;
+    uint32_t o[4];
+    c_row4<3>(row == 0 ? y0 : y1, ca, cb, o);
+    float4* q = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(op) + (long long)row * P.dst_row_stride);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      q[k] = make_float4(lut[o[k] & 0xFF], lut[(o[k] >> 8) & 0xFF], lut[(o[k] >> 16) & 0xFF], lut[o[k] >> 24]);
+  }
+}
+
 // Packed sources, four pixels per thread: RGBA -> RGB (drop alpha), RGBA -> gray, RGB -> gray (RGBToYJ), and the
 // luma plane of a 4:2:0 frame -> gray (a strided copy). SRCB / DSTB = bytes per pixel.
 enum { kPkRgbaToRgb = 0, kPkRgbaToGray = 1, kPkRgbToGray = 2, kPkLumaCopy = 3 };
@@ -230,7 +272,11 @@ typedef void (*CopyKernel)(const CopyParams);
 int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream) {
   static const bool off = getenv("BANDCU_DISABLE_COPY_ROWS") && getenv("BANDCU_DISABLE_COPY_ROWS")[0] == '1';
   if (off) return BANDCU_E_UNSUPPORTED;
-  if (d.scale_mode != BANDCU_SCALE_COPY || d.normalize) return BANDCU_E_UNSUPPORTED;
+  if (d.scale_mode != BANDCU_SCALE_COPY) return BANDCU_E_UNSUPPORTED;
+  // Normalize behind the conversion: only 4:2:0 -> RGB -> float32 has a row kernel
+  const bool f32 = d.normalize != 0;
+  if (f32 && !(d.out_dtype == BANDCU_DT_F32 && d.src_kind == BANDCU_SRC_YUV420 && d.cvt == BANDCU_CVT_YUV2RGB))
+    return BANDCU_E_UNSUPPORTED;
   if (d.dst_width != d.vw || d.dst_height != d.vh || (d.vw & 3)) return BANDCU_E_UNSUPPORTED;
   if (!copy_is_translation(d.luma_map) || !copy_is_translation(d.pre_map) || !copy_is_translation(d.chroma_map))
     return BANDCU_E_UNSUPPORTED;
@@ -240,6 +286,8 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
   P.W = d.vw; P.H = d.vh;
   P.stride0 = d.stride0; P.stride_uv = d.stride_uv;
   P.dst_row_stride = d.dst_row_stride;
+  P.mean = d.mean;
+  P.std_ = d.std_;
   CopyKernel kern = nullptr;
   int src_bpp = 1, rows_per_thread = 1, px_per_thread = 4, pk_mode = -1;
   bool need_chroma = false;
@@ -306,7 +354,9 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
     }
     const bool rgba = d.cvt == BANDCU_CVT_YUV2RGBA;
     // eight pixels per thread when everything is 8-byte granular (planar chroma: 4-byte loads at x/2; RGBA: 16-byte stores)
-    if ((d.vw & 7) == 0 && !batch.table && in4 && out4) {
+    if (f32) {
+      if (!out16 || (d.dst_row_stride & 15)) return BANDCU_E_UNSUPPORTED;  // 128-bit stores
+    } else if ((d.vw & 7) == 0 && !batch.table && in4 && out4) {
       uintptr_t ib = reinterpret_cast<uintptr_t>(batch.first.p0) | (uintptr_t)d.stride0 | (uintptr_t)P.luma_off |
                      (n == 1 ? 0 : (uintptr_t)batch.in_stride);
       if (planar) {
@@ -325,7 +375,9 @@ int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const Tabl
 #define BANDCU_COPY_PICK(C) \
     (rgba ? (p8 ? yuv_copy_rows_kernel<C, 4, 8> : yuv_copy_rows_kernel<C, 4, 4>) \
           : (p8 ? yuv_copy_rows_kernel<C, 3, 8> : yuv_copy_rows_kernel<C, 3, 4>))
-    if (ch == kCopyUV) kern = BANDCU_COPY_PICK(kCopyUV);
+    if (f32) kern = ch == kCopyUV ? yuv_copy_rows_f32_kernel<kCopyUV> : ch == kCopyVU ? yuv_copy_rows_f32_kernel<kCopyVU>
+                                                                                      : yuv_copy_rows_f32_kernel<kCopyPlanar>;
+    else if (ch == kCopyUV) kern = BANDCU_COPY_PICK(kCopyUV);
     else if (ch == kCopyVU) kern = BANDCU_COPY_PICK(kCopyVU);
     else kern = BANDCU_COPY_PICK(kCopyPlanar);
 #undef BANDCU_COPY_PICK

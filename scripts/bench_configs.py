@@ -120,11 +120,11 @@ def cpu_fps(ops_oracle, W, H, fmt_o, out_dt, out_dims, seconds=2.0):
 NORM_O = (5, 0, 0, 0, 0, 127.5, 127.5)
 
 
-def tensor_case(name, W, H, fmt, dw, dh, f32, n, steps, cpu, pre_ops=(), pre_ops_o=(), i8=False):
+def tensor_case(name, W, H, fmt, dw, dh, f32, n, steps, cpu, pre_ops=(), pre_ops_o=(), i8=False, out_dims=None):
     """chain [pre_ops] -> CSC(RGB) -> Resize -> [Normalize] into device tensors."""
     ops = list(pre_ops) + (hotpath.chain_ops(dw, dh, True, mean=128.0, std=1.0) if i8 else hotpath.chain_ops(dw, dh, f32))
     dt = np.int8 if i8 else (np.float32 if f32 else np.uint8)  # i8: Normalize(128, 1) into an int8 tensor (quantized models)
-    rb = hotpath.ResidentBatch(ops, n, W, H, fmt, dt, (1, dh, dw, 3))
+    rb = hotpath.ResidentBatch(ops, n, W, H, fmt, dt, out_dims or (1, dh, dw, 3))
     rng = np.random.default_rng(3)
     uniq = rng.integers(0, 256, size=(4, rb.frame_bytes), dtype=np.uint8)
     L = B.lib()
@@ -328,6 +328,7 @@ def main():
                                pre_ops=[(B.BAND_ROTATE, 270)], pre_ops_o=[(O.OP_ROTATE, 270)]))
         out.append(tensor_case("x_1080p_nv21_to_224_i8_normalized", 1920, 1080, "NV21", 224, 224, False, 1024, a.steps, False,
                                i8=True))
+        out.append(tensor_case("x_1080p_nv12_to_rgb_f32_no_resize", 1920, 1080, "NV12", 0, 0, True, 64, a.steps, False, out_dims=(1, 1080, 1920, 3)))
         out.append(tensor_case("x_1080p_nv21_rot180_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
                                pre_ops=[(B.BAND_ROTATE, 180)], pre_ops_o=[(O.OP_ROTATE, 180)]))
     if "g" in want:  # single-operator image -> image chains

@@ -7,7 +7,7 @@ aligned planes), sizes that fall back to the element-wise kernels, and sizes who
 """
 import pytest
 
-from gpu_util import assert_same_bits, gpu_op, rand_frames
+from gpu_util import assert_same_bits, gpu_chain, gpu_op, oracle_chain, rand_frames
 
 pytestmark = pytest.mark.gpu
 
@@ -57,3 +57,18 @@ def test_quarter_turn_word_path_and_partial_tiles(O, angle, fmt_name, W, H):
     assert st == 0 and st2 == 0
     assert info[:3] == tuple(winfo)
     assert_same_bits(got, want, "rotate %d %s %dx%d" % (angle, fmt_name, W, H))
+
+
+@pytest.mark.parametrize("W,H", [(640, 480), (644, 482), (1284, 724), (322, 242), (8, 2)])
+@pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21"])
+@pytest.mark.parametrize("resident", [False, True])
+def test_convert_then_normalize_without_resize(O, W, H, fmt_name, resident):
+    """ColorSpaceConvert(RGB) -> Normalize(127.5, 127.5) into a float32 tensor at frame size (yuv_copy_rows_f32_kernel when
+    the width is a multiple of four and the tensor is 16-byte aligned; the pixel-per-thread kernel otherwise)."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 2, W, H, fmt, 2400 + W)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_NORMALIZE, 0, 0, 0, 0, 127.5, 127.5)]
+    st, want = oracle_chain(O, ops, fr, W, H, fmt, O.DT_F32, (1, H, W, 3))
+    st2, got = gpu_chain(ops, fr, W, H, fmt, O.DT_F32, (1, H, W, 3), device_resident=resident)
+    assert st == 0 and st2 == 0
+    assert_same_bits(got, want, "%s %dx%d -> RGB f32 (no resize)" % (fmt_name, W, H))
