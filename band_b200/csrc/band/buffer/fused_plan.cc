@@ -475,6 +475,18 @@ absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
     return absl::OkStatus();
   }
   if (view_->scaled || view_->normalized) RETURN_IF_ERROR(Flush());
+  {
+    // An UP-scale of a 4:2:0 source into RGB / RGBA (ConvertFromNv* then ResizeRgb's ARGBScale up path,
+    // libyuv_image_operator.cc:92-300,1146-1187): fused, every output pixel would convert its four source pixels again --
+    // (scale factor)^2 conversions per source pixel on the pixel-per-thread kernel. Materialising the converted image
+    // once (the same-size conversion kernel) and up-scaling it with the row-streaming packed kernels is what the
+    // reference does stage by stage, moves W*H*3 extra bytes against an output (factor)^2 times that size, and keeps
+    // both launches on vectorised kernels. Values are identical either way.
+    const View& cur = *view_;
+    const bool yuv_to_packed = Buffer::IsYUV(cur.src.format) && (cur.cvt == BANDCU_CVT_YUV2RGB || cur.cvt == BANDCU_CVT_YUV2RGBA);
+    if (yuv_to_packed && DispatchArgbScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP)
+      RETURN_IF_ERROR(Flush());
+  }
   View& v = *view_;
   terminal_noop_ = false;
   v.scale = v.format == BufferFormat::kGrayScale ? DispatchPlaneScale(v.w, v.h, dst_width, dst_height)

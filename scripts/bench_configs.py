@@ -329,6 +329,8 @@ def main():
         out.append(tensor_case("x_1080p_nv21_to_224_i8_normalized", 1920, 1080, "NV21", 224, 224, False, 1024, a.steps, False,
                                i8=True))
         out.append(tensor_case("x_1080p_nv12_to_rgb_f32_no_resize", 1920, 1080, "NV12", 0, 0, True, 64, a.steps, False, out_dims=(1, 1080, 1920, 3)))
+        out.append(tensor_case("x_640x480_nv21_up_to_1280x960_u8", 640, 480, "NV21", 1280, 960, False, 256, a.steps, False))
+        out.append(tensor_case("x_320x240_yv12_up_to_1024x768_f32", 320, 240, "YV12", 1024, 768, True, 128, a.steps, False))
         out.append(tensor_case("x_1080p_nv21_rot180_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
                                pre_ops=[(B.BAND_ROTATE, 180)], pre_ops_o=[(O.OP_ROTATE, 180)]))
     if "g" in want:  # single-operator image -> image chains
