@@ -143,3 +143,31 @@ def test_frozen_digests(O):
     for case in cases:
         out = mg.run_case(case)
         assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == frozen[case[0]], case[0]
+
+
+def test_yuv_to_rgb_agrees_with_opencv_as_an_independent_witness(O):
+    """K1 (YUV -> RGB values) is pinned by no vector the reference holds: the restated libyuv arithmetic IS
+    the spec. As a second, independent witness OpenCV's BT.601 limited-range conversion (its own 20-bit fixed point, not
+    libyuv's 6-bit one) must agree with the oracle within a few counts on random frames -- enough to catch a U/V swap, a
+    channel-order mistake, a range (full vs limited) mistake or a wrong plane order in any of the four 4:2:0 layouts."""
+    cv2 = pytest.importorskip("cv2")
+    W, H = 64, 48
+    rng = np.random.default_rng(99)
+    cases = [(O.FMT_NV12, cv2.COLOR_YUV2RGB_NV12), (O.FMT_NV21, cv2.COLOR_YUV2RGB_NV21),
+             (O.FMT_YV12, cv2.COLOR_YUV2RGB_YV12), (O.FMT_YV21, cv2.COLOR_YUV2RGB_I420)]
+    for fmt, code in cases:
+        # mid-range chroma keeps both converters away from their clamps, where rounding differences would be amplified
+        n = O.frame_bytes(W, H, fmt)
+        frame = rng.integers(16, 236, size=n, dtype=np.uint8)
+        frame[W * H:] = rng.integers(64, 192, size=n - W * H, dtype=np.uint8)
+        st, ours, (w, h, f) = O.run_op((O.OP_CSC, O.FMT_RGB), frame, W, H, fmt)
+        assert st == 0 and (w, h, f) == (W, H, O.FMT_RGB)
+        theirs = cv2.cvtColor(frame.reshape(H * 3 // 2, W), code)
+        diff = np.abs(ours.reshape(H, W, 3).astype(np.int32) - theirs.astype(np.int32))
+        assert diff.max() <= 3, (fmt, int(diff.max()))
+        assert diff.mean() < 1.0, (fmt, float(diff.mean()))
+        # the witness is sensitive: swapping the chroma planes moves the result far outside the tolerance
+        swapped_code = {cv2.COLOR_YUV2RGB_NV12: cv2.COLOR_YUV2RGB_NV21, cv2.COLOR_YUV2RGB_NV21: cv2.COLOR_YUV2RGB_NV12,
+                        cv2.COLOR_YUV2RGB_YV12: cv2.COLOR_YUV2RGB_I420, cv2.COLOR_YUV2RGB_I420: cv2.COLOR_YUV2RGB_YV12}[code]
+        wrong = cv2.cvtColor(frame.reshape(H * 3 // 2, W), swapped_code)
+        assert np.abs(ours.reshape(H, W, 3).astype(np.int32) - wrong.astype(np.int32)).max() > 20
