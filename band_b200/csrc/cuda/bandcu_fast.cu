@@ -84,16 +84,20 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// try_wait parks the warp in hardware until the phase completes or the time limit passes; with the default limit a
+// DRAM-bound launch still executed more wait-loop instructions than arithmetic (ncu: 214 K warp-instructions per frame on the
+// north star against 93 K of real work), which costs issue slots and -- under the 1000 W cap of a sustained run -- clock.
+// A 20 us suspend hint keeps the wake-up on completion and removes most of the polling.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
       "@p bra WAIT_DONE;\n"
       "bra WAIT_LOOP;\n"
       "WAIT_DONE:\n"
-      "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity), "r"(20000u)
       : "memory");
 }
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
