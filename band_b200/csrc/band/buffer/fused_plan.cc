@@ -484,8 +484,21 @@ absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
     // both launches on vectorised kernels. Values are identical either way.
     const View& cur = *view_;
     const bool yuv_to_packed = Buffer::IsYUV(cur.src.format) && (cur.cvt == BANDCU_CVT_YUV2RGB || cur.cvt == BANDCU_CVT_YUV2RGBA);
-    if (yuv_to_packed && DispatchArgbScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP)
+    if (yuv_to_packed && DispatchArgbScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP) {
+      // The scratch image is RGBA even when the chain asked for RGB: the up-scaler then fetches a source pixel with one
+      // 32-bit load instead of three byte loads and drops the alpha byte per fetch (ARGBToRGB24 semantics) -- the column
+      // filter of a small-ratio up-scale is bound by exactly those fetches. Same R, G, B values either way.
+      const bool widen = cur.cvt == BANDCU_CVT_YUV2RGB;
+      if (widen) {
+        view_->cvt = BANDCU_CVT_YUV2RGBA;
+        view_->format = BufferFormat::kRGBA;
+      }
       RETURN_IF_ERROR(Flush());
+      if (widen) {
+        view_->cvt = BANDCU_CVT_RGBA2RGB;
+        view_->format = BufferFormat::kRGB;
+      }
+    }
   }
   View& v = *view_;
   terminal_noop_ = false;
