@@ -483,6 +483,17 @@ absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
     // reference does stage by stage, moves W*H*3 extra bytes against an output (factor)^2 times that size, and keeps
     // both launches on vectorised kernels. Values are identical either way.
     const View& cur = *view_;
+    // RGB / RGBA -> gray in front of an up-scale (RAWToJ400 / ARGBToJ400 then ScalePlane): fused, every source pixel would be
+    // converted once per fetch, (factor)^2 times over; the gray image is a quarter of the source and is materialised first.
+    // (Outputs below 256 KB stay fused: there the second launch costs more than the conversions it saves -- measured on
+    // RGBA 64^2 -> gray 256^2.)
+    if ((cur.cvt == BANDCU_CVT_RGB2GRAY || cur.cvt == BANDCU_CVT_RGBA2GRAY) &&
+        static_cast<long long>(dst_width) * dst_height >= 256 * 1024 &&
+        DispatchPlaneScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP)
+      RETURN_IF_ERROR(Flush());
+  }
+  {
+    const View& cur = *view_;
     const bool yuv_to_packed = Buffer::IsYUV(cur.src.format) && (cur.cvt == BANDCU_CVT_YUV2RGB || cur.cvt == BANDCU_CVT_YUV2RGBA);
     if (yuv_to_packed && DispatchArgbScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP) {
       // The scratch image is RGBA even when the chain asked for RGB: the up-scaler then fetches a source pixel with one

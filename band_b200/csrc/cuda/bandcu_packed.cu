@@ -317,6 +317,96 @@ __global__ void __launch_bounds__(128) packed_up_rows_x16_kernel(const __grid_co
   }
 }
 
+// RGB outputs of SMALL-ratio up-scales (factor < 8): the row-streaming kernels above re-derive the column terms of a pixel (16.16
+// position, two clamped columns, 7-bit weight) every time a source row is filtered, and an RGB output WORD needs two pixels, so the
+// column filter -- run once per factor output rows -- dominates (640x480 -> 1280x960: 0.20 of the HBM roofline). Here a thread owns
+// FOUR PIXELS (twelve output bytes) and keeps their column terms in registers for all its rows: filtering a source row costs
+// two fetches and one packed blend per pixel. Rows are walked exactly as above (terms rebuilt when yi advances, the old bottom
+// row becomes the new top row); the four blended pixel words are packed into three output words with PRMT.
+template <int SRCCH, int CVT, int OUTCH>
+__global__ void __launch_bounds__(128) packed_up_rows_px4_kernel(const __grid_constant__ PackedParams P) {
+  constexpr bool PLANE = OUTCH == 1;
+  constexpr int NT = PLANE ? 1 : 4;  // blended units per thread: gray packs its four pixels into ONE word
+  const int ox0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int oy_begin = (blockIdx.y * blockDim.y + threadIdx.y) * P.up_rows;
+  if (ox0 >= P.dw || oy_begin >= P.dh) return;
+  const int oy_end = min(P.dh, oy_begin + P.up_rows);
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  int c0[4], c1[4], xw[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int ox = min(ox0 + k, P.dw - 1);  // pixels past the end of the row are never stored
+    const int x = P.x0 + ox * P.dx;
+    const int xi = x >> 16;
+    c0[k] = min(max(xi, 0), P.sw - 1);
+    c1[k] = min(max(xi + 1, 0), P.sw - 1);
+    xw[k] = x;  // packed_hblend takes the 16.16 position (7-bit truncating ARGB filter / rounding plane filter)
+  }
+  // column filter of one source row for this thread's four pixels
+  auto filter = [&](const uint8_t* __restrict__ row, uint32_t (&out)[NT]) {
+    uint32_t px[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      px[k] = packed_hblend<PLANE>(packed_fetch<SRCCH, CVT>(row, c0[k]), packed_fetch<SRCCH, CVT>(row, c1[k]), xw[k]);
+    if (PLANE) {
+      out[0] = (px[0] & 0xFF) | ((px[1] & 0xFF) << 8) | ((px[2] & 0xFF) << 16) | (px[3] << 24);
+    } else {
+#pragma unroll
+      for (int k = 0; k < NT; ++k) out[k] = px[k];
+    }
+  };
+  uint32_t h1[NT];
+  UpTerms t[NT];
+  int cur_yi = INT_MIN, have1 = -1;
+  int y_raw = P.y0 + oy_begin * P.dy;
+  uint8_t* o = f.out + (long long)oy_begin * P.dst_row_stride + OUTCH * (size_t)ox0;
+  const bool whole = ox0 + 4 <= P.dw && P.vec_ok;
+  for (int oy = oy_begin; oy < oy_end; ++oy, o += P.dst_row_stride, y_raw += P.dy) {
+    const int y = min(y_raw, P.max_y);
+    const int yi = y >> 16;
+    const uint32_t yf = P.linear ? 0u : (uint32_t)((y >> 8) & 255);
+    if (yi != cur_yi) {
+      const int r0 = min(max(yi, 0), P.sh - 1), r1 = min(max(yi + 1, 0), P.sh - 1);
+      uint32_t a[NT], b[NT];
+      if (r0 == have1) {
+#pragma unroll
+        for (int k = 0; k < NT; ++k) a[k] = h1[k];
+      } else {
+        filter(f.p0 + (size_t)r0 * P.stride0, a);
+      }
+      if (r1 == r0) {
+#pragma unroll
+        for (int k = 0; k < NT; ++k) b[k] = a[k];
+      } else {
+        filter(f.p0 + (size_t)r1 * P.stride0, b);
+      }
+#pragma unroll
+      for (int k = 0; k < NT; ++k) {
+        h1[k] = b[k];
+        t[k] = up_terms(a[k], b[k]);
+      }
+      cur_yi = yi;
+      have1 = r1;
+    }
+    uint32_t v[NT];
+#pragma unroll
+    for (int k = 0; k < NT; ++k) v[k] = __byte_perm(t[k].d_lo * yf + t[k].base_lo, t[k].d_hi * yf + t[k].base_hi, 0x7351);
+    if (PLANE) {
+      if (whole) *reinterpret_cast<uint32_t*>(o) = v[0];
+      else for (int k = 0; k < 4 && ox0 + k < P.dw; ++k) o[k] = (uint8_t)(v[0] >> (8 * k));
+    } else if (whole) {
+      uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+      ow[0] = __byte_perm(v[0], v[NT > 1 ? 1 : 0], 0x4210);
+      ow[1] = __byte_perm(v[NT > 1 ? 1 : 0], v[NT > 2 ? 2 : 0], 0x5421);
+      ow[2] = __byte_perm(v[NT > 2 ? 2 : 0], v[NT > 3 ? 3 : 0], 0x6542);
+    } else {
+      for (int k = 0; k < NT && ox0 + k < P.dw; ++k) {
+        o[3 * k] = (uint8_t)v[k]; o[3 * k + 1] = (uint8_t)(v[k] >> 8); o[3 * k + 2] = (uint8_t)(v[k] >> 16);
+      }
+    }
+  }
+}
+
 typedef void (*PackedKernel)(PackedParams);
 // Small sources (the 64^2 end of BASELINE's RGBA sweep): Scale*BilinearUp as libyuv does it -- every source row filtered
 // horizontally ONCE, then output rows blended from pairs of filtered rows -- with the whole frame in shared memory.
@@ -502,6 +592,10 @@ static PackedKernel packed_pick2(int mode, bool f32, int up_rows) {
     const bool rows = up_rows != 0, narrow = up_rows == 1;
     constexpr int NW = OUTCH == 3 ? 3 : 4;
     if (up_rows == 3) return packed_up_rows_x16_kernel<SRCCH, CVT, OUTCH>;  // u8, 16-byte aligned rows
+    if (up_rows == 4) {  // RGB outputs, factor < 8: four pixels per thread, column terms in registers
+      if (OUTCH == 3 || OUTCH == 1) return packed_up_rows_px4_kernel<SRCCH, CVT, (OUTCH == 4 ? 3 : OUTCH)>;
+      return nullptr;
+    }
     if (rows && narrow) return f32 ? packed_up_rows_kernel<SRCCH, CVT, OUTCH, float, 1> : packed_up_rows_kernel<SRCCH, CVT, OUTCH, uint8_t, 1>;
     if (rows) return f32 ? packed_up_rows_kernel<SRCCH, CVT, OUTCH, float, NW> : packed_up_rows_kernel<SRCCH, CVT, OUTCH, uint8_t, NW>;
     return f32 ? packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedUp, float> : packed_bilinear_kernel<SRCCH, CVT, OUTCH, kPackedUp, uint8_t>;
@@ -556,7 +650,13 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
       up_rows = row_words <= 64 ? 1 : 2;
       // u8 rows of at least 1 KB that start 16-byte aligned: four consecutive words per lane, 128-bit stores
       if (!d.normalize && P.vec_ok && row_words >= 256 && p->up_rows_mode != 2) up_rows = 3;
-      const int per_warp = up_rows == 3 ? 128 : 32 * (up_rows == 1 ? 1 : nwt);
+      // RGB outputs of small-ratio up-scales: the column filter dominates, keep its terms in registers (four pixels per thread)
+      // (measured: at factors >= 8 the 128-bit-store form wins for RGB and gray alike)
+      if (!d.normalize && p->up_rows_mode < 0 && (d.channels == 3 || d.channels == 1) && d.dst_height < 8 * d.vh) {
+        up_rows = 4;
+        P.vec_ok = 1;  // word stores: `ok` above established 4-byte aligned rows
+      }
+      const int per_warp = up_rows == 3 ? 128 : up_rows == 4 ? 32 * d.channels : 32 * (up_rows == 1 ? 1 : nwt);
       // rows per thread: long enough to amortise the column filter of a source row pair (~4 source rows), short
       // enough to leave >= ~8 threads per lane of the machine
       const long long col_threads = (long long)n * ((row_words + per_warp - 1) / per_warp) * 32;
