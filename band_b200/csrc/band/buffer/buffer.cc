@@ -27,7 +27,16 @@ std::shared_ptr<unsigned char> Allocate(size_t bytes, MemorySpace* space) {
 }
 }  // namespace
 
-Buffer::~Buffer() = default;
+namespace {
+std::atomic<uint64_t> g_buffer_epoch{1};
+}
+uint64_t Buffer::Epoch() { return g_buffer_epoch.load(std::memory_order_relaxed); }
+void Buffer::SetOrientation(BufferOrientation orientation) {
+  orientation_ = orientation;
+  g_buffer_epoch.fetch_add(1, std::memory_order_relaxed);
+}
+
+Buffer::~Buffer() { g_buffer_epoch.fetch_add(1, std::memory_order_relaxed); }
 
 Buffer::Buffer(std::vector<size_t> dimension, std::vector<DataPlane> data_planes, BufferFormat buffer_format,
                DataType data_type, BufferOrientation orientation, MemorySpace space)
@@ -36,7 +45,9 @@ Buffer::Buffer(std::vector<size_t> dimension, std::vector<DataPlane> data_planes
       buffer_format_(buffer_format),
       data_type_(data_type),
       orientation_(orientation),
-      space_(space) {}
+      space_(space) {
+  g_buffer_epoch.fetch_add(1, std::memory_order_relaxed);
+}
 
 // buffer.cc:16-22
 Buffer* Buffer::CreateFromPlanes(const std::vector<DataPlane>& data_planes, const std::vector<size_t>& dims,
@@ -236,7 +247,10 @@ size_t Buffer::GetSize(const std::vector<size_t>& dims) {
 
 const std::vector<size_t>& Buffer::GetDimension() const { return dimension_; }
 const Buffer::DataPlane& Buffer::operator[](size_t index) const { return data_planes_[index]; }
-Buffer::DataPlane& Buffer::operator[](size_t index) { return data_planes_[index]; }
+Buffer::DataPlane& Buffer::operator[](size_t index) {
+  g_buffer_epoch.fetch_add(1, std::memory_order_relaxed);  // the caller may re-point the plane
+  return data_planes_[index];
+}
 size_t Buffer::GetNumPlanes() const { return data_planes_.size(); }
 size_t Buffer::GetNumElements() const { return GetSize(dimension_); }
 size_t Buffer::GetPixelBytes() const {

@@ -9,6 +9,8 @@
 #ifndef BAND_BUFFER_BUFFER_H_
 #define BAND_BUFFER_BUFFER_H_
 
+#include <atomic>
+#include <cstdint>
 #include <memory>
 #include <ostream>
 #include <vector>
@@ -67,11 +69,15 @@ class Buffer {
   BufferFormat GetBufferFormat() const;
   BufferOrientation GetOrientation() const;
   // additive: the camera layer knows the sensor orientation only after the view exists (BandBufferSetOrientation)
-  void SetOrientation(BufferOrientation orientation) { orientation_ = orientation; }
+  void SetOrientation(BufferOrientation orientation);
   // additive: every plane of this HOST buffer lies in pinned (page-locked, device-mapped) memory. Asked of the CUDA
   // runtime once per buffer and remembered: batch calls hand the same views over and over.
   bool IsPinnedHost() const;
   MemorySpace GetMemorySpace() const { return space_; }  // additive
+  // additive: a process-wide counter that moves whenever ANY Buffer is created, destroyed or may have been changed in
+  // place (non-const plane access, SetOrientation). While it stands still, a list of Buffer pointers names the same
+  // views over the same memory as before, so a processor may replay its last batch without re-validating it.
+  static uint64_t Epoch();
 
   absl::Status CopyFrom(const Buffer& rhs);
 

@@ -878,11 +878,15 @@ SlotPointers FusedPlan::Resolve(int slot, int frame) const {
 }
 
 // Launches every segment for frames [first, last) on the compute stream.
-absl::Status FusedPlan::RunSegments(int first, int last) {
+absl::Status FusedPlan::RunSegments(int first, int last, bool rerun) {
   const int m = last - first;
   for (Segment& seg : segments_) {
     switch (seg.kind) {
       case Segment::Kind::kPixel: {
+        if (rerun) {  // the shim still holds this segment's previous batch (pointers, strides or table, alignment hints)
+          if (bandcu_plan_rerun(seg.plan, stream_) != BANDCU_OK) return CudaError("bandcu_plan_rerun");
+          break;
+        }
         frames_.resize(m);
         for (int f = 0; f < m; ++f) {
           const SlotPointers s = Resolve(seg.src_slot, first + f), d = Resolve(seg.dst_slot, first + f);
@@ -934,6 +938,10 @@ absl::Status FusedPlan::RunSegments(int first, int last) {
         frames_.resize(m);
         for (int k = 0; k < 3; ++k) {
           if (!seg.plane_plan[k]) continue;
+          if (rerun) {
+            if (bandcu_plan_rerun(seg.plane_plan[k], stream_) != BANDCU_OK) return CudaError("bandcu_plan_rerun");
+            continue;
+          }
           for (int f = 0; f < m; ++f) {
             const SlotPointers s = Resolve(seg.src_slot, first + f), d = Resolve(seg.dst_slot, first + f);
             const unsigned char* sp = k == 0 ? s.y : (seg.interleaved_uv ? std::min(s.u, s.v) : (k == 1 ? s.u : s.v));
@@ -1011,7 +1019,7 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
                 (static_cast<size_t>(segments_[0].pixel.dst_width) * segments_[0].pixel.channels *
                  GetDataTypeBytes(output_.dtype)) % 16 == 0;
   for (int f = 0; zc_out && f < m; ++f) {
-    const unsigned char* p = (*outputs[f])[0].data;
+    const unsigned char* p = static_cast<const Buffer&>(*outputs[f])[0].data;
     if ((reinterpret_cast<uintptr_t>(p) & 15) != 0 || !outputs[f]->IsPinnedHost()) zc_out = false;
   }
   if (IsSingleFastLaunch() && bandcu_plan_set_host_output(segments_[0].plan, zc_out ? 1 : 0) != BANDCU_OK)
@@ -1172,7 +1180,18 @@ absl::Status FusedPlan::RunPass(const Buffer* const* inputs, Buffer* const* outp
   return absl::OkStatus();
 }
 
+absl::Status FusedPlan::Rerun(bool synchronize) {
+  if (!rerunnable_ || last_frames_ <= 0) return absl::FailedPreconditionError("Rerun: no replayable batch");
+  RETURN_IF_ERROR(RunSegments(0, last_frames_, /*rerun=*/true));
+  in_flight_ = true;
+  if (!synchronize) return absl::OkStatus();
+  if (bandcu_stream_sync(stream_) != BANDCU_OK) return CudaError("stream sync");
+  in_flight_ = false;
+  return absl::OkStatus();
+}
+
 absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs, int n, bool synchronize) {
+  rerunnable_ = false;
   if (n <= 0) return absl::OkStatus();
   if (inputs == nullptr || (writes_output_ && outputs == nullptr)) return absl::InvalidArgumentError("null frame list");
   const MemorySpace in_space = inputs[0] ? inputs[0]->GetMemorySpace() : MemorySpace::kHost;
@@ -1194,6 +1213,9 @@ absl::Status FusedPlan::Run(const Buffer* const* inputs, Buffer* const* outputs,
     RETURN_IF_ERROR(RunPass(inputs + base, writes_output_ ? outputs + base : nullptr, m,
                             in_space == MemorySpace::kHost, out_space == MemorySpace::kHost, synchronize));
   }
+  // one pass that moved nothing through staging and holds no registered host range: the same launches may be replayed
+  rerunnable_ = n <= kMaxPassFrames && !last_pass_staged_ && !register_host_;
+  last_frames_ = n;
   return absl::OkStatus();
 }
 

@@ -81,6 +81,11 @@ class FusedPlan {
   // of a call in the same space); host frames are staged through plan-owned
   // device memory. Synchronous: returns after the stream has drained.
   absl::Status Run(const Buffer* const* inputs, Buffer* const* outputs, int n, bool synchronize = true);
+  // Launches the previous Run() again -- same frames, same outputs, no validation, no pointer resolution. Only legal when
+  // CanRerun(): the previous Run was one pass over device-resident or in-place (pinned) memory. The caller
+  // (BufferProcessor) establishes that the frame lists name the same views as before (Buffer::Epoch()).
+  bool CanRerun() const { return rerunnable_; }
+  absl::Status Rerun(bool synchronize);
   // Waits for everything a Run(..., false) enqueued (compute and copy-out streams).
   absl::Status Synchronize();
   // Records one Run() over DEVICE-resident (or pinned, zero-copy) frames into a CUDA graph and returns the executable
@@ -105,7 +110,7 @@ class FusedPlan {
   absl::Status EnsureCapacity(int frames, size_t in_bytes, size_t out_bytes);
   absl::Status RunPass(const Buffer* const* inputs, Buffer* const* outputs, int m, bool in_host, bool out_host,
                        bool synchronize);
-  absl::Status RunSegments(int first, int last);
+  absl::Status RunSegments(int first, int last, bool rerun = false);
   // the frame's planes are device-readable in place: pinned memory, or registered through the HostRegistry now
   bool HostFrameIsMapped(const Buffer& frame);
   void ReleaseHeldHost();
@@ -138,6 +143,8 @@ class FusedPlan {
   void* fence_b_ = nullptr;  // orders a new pass's kernels after the previous pass's downloads
   bool in_flight_ = false;   // an unsynchronised pass may still be running
   bool last_pass_staged_ = false;  // the last RunPass moved frames or results through staging copies
+  bool rerunnable_ = false;        // the last Run() was a single pointer-only pass: Rerun() may replay it
+  int last_frames_ = 0;
   // environment switches, read ONCE when the plan is created (never on the launch path)
   bool zero_copy_allowed_ = true;  // BAND_NO_ZERO_COPY
   int chunk_frames_ = 32;          // BAND_CHUNK_FRAMES: frames per upload/compute/download pipeline stage

@@ -181,7 +181,9 @@ BandStatus BandImageProcessorProcess(BandImageProcessor* image_processor, BandBu
     BAND_LOG(LogSeverity::kError, "BandBuffer has no data");
     return kBandErr;
   }
-  std::unique_ptr<Buffer> tensor_buffer(Buffer::CreateFromTensor(target_tensor->impl.get()));
+  // the cached view of the tensor (its type and dims never change): the reference builds a temporary Buffer per call
+  // (c_api_buffer.cc:209-212); reusing one keeps the processor's repeat fast path alive
+  Buffer* tensor_buffer = target_tensor->View();
   if (!tensor_buffer) return kBandErr;
   absl::Status status = image_processor->impl->Process(*buffer->impl, *tensor_buffer);
   if (!status.ok()) g_last_error = status.ToString();

@@ -49,6 +49,10 @@ struct BandCuPlan {
   bool table_pending;
   cudaStream_t table_stream;  // stream the upload was ordered on
   int table_valid_n;        // >0: table_dev holds exactly table_host[0..n) (reused when the next call repeats it)
+  // the previous successful batch, for bandcu_plan_rerun
+  BatchArgs last_b;
+  TableHints last_hints;
+  int last_n;
 };
 
 static int validate_desc(const BandCuPlanDesc* d) {
@@ -198,7 +202,10 @@ int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* first, long lon
   b.in_stride = in_stride;
   b.out_stride = out_stride;
   b.table = nullptr;
-  return run_batch(plan, b, TableHints(), n, (cudaStream_t)stream);
+  const int e = run_batch(plan, b, TableHints(), n, (cudaStream_t)stream);
+  if (e == BANDCU_OK) { plan->last_b = b; plan->last_hints = TableHints(); plan->last_n = n; }
+  else plan->last_n = 0;
+  return e;
 }
 
 int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* stream) {
@@ -263,6 +270,7 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
     // this launch reads the table too: a later rewrite must wait for it, not only for the launch that uploaded it
     CU_TRY(cudaEventRecord(plan->table_free, s), "plan_run: event record");
     plan->table_pending = true;
+    plan->last_b = b; plan->last_hints = hints; plan->last_n = n;
     return BANDCU_OK;
   }
   if (plan->table_pending) {  // previous launch may still read the table
@@ -289,11 +297,31 @@ int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* st
   memset(&b, 0, sizeof(b));
   b.table = plan->table_dev;
   int e = run_batch(plan, b, hints, n, s);
-  if (e != BANDCU_OK) return e;
+  if (e != BANDCU_OK) { plan->last_n = 0; return e; }
   CU_TRY(cudaEventRecord(plan->table_free, s), "plan_run: event record");
   plan->table_pending = true;
   plan->table_valid_n = n;
   plan->table_stream = s;
+  plan->last_b = b; plan->last_hints = hints; plan->last_n = n;
+  return BANDCU_OK;
+}
+
+int bandcu_plan_rerun(BandCuPlan* plan, void* stream) {
+  if (!plan || plan->last_n <= 0) return fail(BANDCU_E_INVALID, "plan_rerun: no previous batch");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (plan->last_b.table) {
+    // the device table still holds the previous batch only if nothing rewrote it and the stream is the one it was ordered on
+    if (plan->table_valid_n != plan->last_n || plan->table_stream != s) return fail(BANDCU_E_INVALID, "plan_rerun: pointer table changed");
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone)
+      return fail(BANDCU_E_UNSUPPORTED, "plan_rerun: a pointer-table batch cannot be recorded into a CUDA graph");
+  }
+  const int e = run_batch(plan, plan->last_b, plan->last_hints, plan->last_n, s);
+  if (e != BANDCU_OK) return e;
+  if (plan->last_b.table) {
+    CU_TRY(cudaEventRecord(plan->table_free, s), "plan_rerun: event record");
+    plan->table_pending = true;
+  }
   return BANDCU_OK;
 }
 

@@ -71,6 +71,11 @@ struct FastPlan {
   int R, S;
   int bulk_store;  // results leave through shared memory + cp.async.bulk stores (outputs in pinned host memory)
   int no_bulk;     // BANDCU_FAST_NO_BULK=1 when the plan was created: stage with producer-warp byte copies
+  // occupancy of the last launch configuration (kernel, block, shared memory): asked of the runtime once, not per launch
+  // (cudaFuncSetAttribute + cudaOccupancyMaxActiveBlocksPerMultiprocessor cost ~2 us, a fifth of a single-frame call)
+  const void* occ_kern;
+  int occ_block, occ_per_sm;
+  size_t occ_smem;
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -627,9 +632,14 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   // persistent grid: every SM holds as many CTAs as shared memory, threads and registers allow
   FastKernel kern = f32_out ? pick_kernel<float>(ch, bulk_out) : pick_kernel<uint8_t>(ch, bulk_out);
   int per_sm = 1;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
-  if (e != cudaSuccess) return (int)e;
+  if (p->occ_kern == (const void*)kern && p->occ_block == block && p->occ_smem == smem) {
+    per_sm = p->occ_per_sm;
+  } else {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
+    if (e != cudaSuccess) return (int)e;
+    p->occ_kern = (const void*)kern; p->occ_block = block; p->occ_smem = smem; p->occ_per_sm = per_sm;
+  }
   if (per_sm < 1) return BANDCU_E_UNSUPPORTED;
   long long want = (long long)p->num_sms * per_sm;
   int grid = (int)(P.n_items < want ? P.n_items : want);

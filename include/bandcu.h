@@ -156,6 +156,10 @@ BANDCU_API int bandcu_plan_run_strided(BandCuPlan* plan, const BandCuFrame* firs
                                        long long out_stride, int n, void* stream);
 /* Run n frames with arbitrary device pointers (host array; uploaded internally). */
 BANDCU_API int bandcu_plan_run(BandCuPlan* plan, const BandCuFrame* frames, int n, void* stream);
+/* Launch the plan's previous batch again: same frame pointers, same count (bandcu_plan_run / _run_strided must have
+ * succeeded on this plan before). Skips the per-frame host work -- stride detection, alignment hints, pointer-table
+ * comparison -- which bounds the rate of batches of very small frames. */
+BANDCU_API int bandcu_plan_rerun(BandCuPlan* plan, void* stream);
 /* number of kernel launches issued by this library on the calling process so far */
 BANDCU_API long long bandcu_launch_count(void);
 

@@ -369,3 +369,66 @@ def test_registration_cache_brings_pageable_frames_to_the_in_place_path(O):
         assert s3["entries"] == 0 and s3["registered_bytes"] == 0, s3
     finally:
         B.host_registration_cache(False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mem", ["device", "pinned"])
+def test_repeat_calls_replay_the_launch_and_follow_memory_and_handles(O, mem):
+    """A camera loop hands the processor the SAME BandBuffer / BandTensor objects call after call: from the second call on
+    the processor replays its launch without re-validating (Buffer::Epoch). The replay must read what the frame memory holds
+    NOW, must notice a handle that was re-pointed (BandBufferSetFromRawData creates a new view), and a bad call in between
+    must still fail."""
+    from band_b200 import band_c as B
+    from band_b200 import hotpath
+    L = B.lib()
+    n, W, H, dw, dh = 6, 640, 480, 224, 224
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh), NORM]
+    fa = rand_frames(O, n, W, H, O.FMT_NV12, seed=301)
+    fb = rand_frames(O, n, W, H, O.FMT_NV12, seed=302)
+    _, want_a = oracle_chain(O, ops, fa, W, H, O.FMT_NV12, O.DT_F32, (1, dh, dw, 3))
+    _, want_b = oracle_chain(O, ops, fb, W, H, O.FMT_NV12, O.DT_F32, (1, dh, dw, 3))
+    fbytes = fa.shape[1]
+    pitch = (fbytes + 255) // 256 * 256
+    dev = mem == "device"
+    alloc, free = (L.BandDeviceAlloc, L.BandDeviceFree) if dev else (L.BandHostAlloc, L.BandHostFree)
+    base, other = alloc(pitch * n), alloc(pitch * n)
+
+    def fill(dst, frames):
+        for i in range(n):
+            if dev:
+                assert L.BandCopyToDevice(dst + i * pitch, frames[i].ctypes.data, fbytes) == B.kBandOk
+            else:
+                C.memmove(dst + i * pitch, frames[i].ctypes.data, fbytes)
+
+    fill(base, fa)
+    fill(other, fb)
+    bufs = [B.Buffer().set_raw(base + i * pitch, W, H, B.kBandNV12, device=dev) for i in range(n)]
+    tens = [B.Tensor(np.float32, (1, dh, dw, 3), device=dev) for _ in range(n)]
+    proc = B.ImageProcessor(to_capi_ops(ops))
+    got = lambda: np.stack([t.numpy() for t in tens])
+    assert proc.process_batch(bufs, tens) == B.kBandOk, B.last_error()
+    assert_same_bits(got(), want_a, "first call")
+    for _ in range(3):   # replays
+        n0 = hotpath.launch_count()
+        assert proc.process_batch(bufs, tens) == B.kBandOk, B.last_error()
+        assert hotpath.launch_count() - n0 == 1
+    assert_same_bits(got(), want_a, "replayed call")
+    fill(base, fb)       # the camera refills the same memory
+    assert proc.process_batch(bufs, tens) == B.kBandOk
+    assert_same_bits(got(), want_b, "replay reads the refilled frames")
+    fill(base, fa)
+    bufs[2].set_raw(other + 2 * pitch, W, H, B.kBandNV12, device=dev)   # handle 2 now views another frame (holds fb[2])
+    assert proc.process_batch(bufs, tens) == B.kBandOk
+    want_mix = want_a.copy(); want_mix[2] = want_b[2]
+    assert_same_bits(got(), want_mix, "a re-pointed handle is noticed")
+    bad = B.Tensor(np.float32, (1, dh + 1, dw, 3), device=dev)
+    assert proc.process_batch(bufs[:1], [bad]) == B.kBandErr
+    assert proc.process_batch(bufs, tens) == B.kBandOk
+    assert_same_bits(got(), want_mix, "after a failed call")
+    # single-frame entry point, repeated
+    for _ in range(3):
+        assert proc.process(bufs[0], tens[0]) == B.kBandOk
+    assert_same_bits(tens[0].numpy(), want_a[0], "BandImageProcessorProcess repeated")
+    for x in bufs + tens + [bad, proc]:
+        x.close()
+    free(base); free(other)
