@@ -635,7 +635,9 @@ int launch_fast(FastPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
   if (p->occ_kern == (const void*)kern && p->occ_block == block && p->occ_smem == smem) {
     per_sm = p->occ_per_sm;
   } else {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the attribute belongs to the kernel, not to this plan: every plan raises it to the same cap, so that a plan with a
+    // smaller ring never lowers it under another plan's cached geometry
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_cap);
     if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem);
     if (e != cudaSuccess) return (int)e;
     p->occ_kern = (const void*)kern; p->occ_block = block; p->occ_smem = smem; p->occ_per_sm = per_sm;

@@ -685,7 +685,7 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
     const size_t out_bytes = (size_t)d.dst_width * d.dst_height * d.channels;
     if (small && src_ok && smem <= 48 * 1024 && out_bytes <= 64 * 1024) {
       P.vec_ok = (out4 && d.dst_row_stride % 4 == 0) ? 1 : 0;
-      cudaError_t e = cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaError_t e = cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024);  // one value for every plan
       if (e != cudaSuccess) return (int)e;
       for (int done = 0; done < n;) {
         const int chunk = n - done > (1 << 30) ? (1 << 30) : n - done;

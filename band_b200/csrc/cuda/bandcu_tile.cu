@@ -765,7 +765,7 @@ int launch_tile(TilePlan* p, const BandCuPlanDesc& d, const BatchArgs& batch, co
     P.out_vec = (ok && (d.dst_row_stride & need) == 0) ? 1 : 0;
   }
   TileKernel kern = f32_out ? pick_tile_kernel<float>(aligned16, swap, P.interleaved != 0) : pick_tile_kernel<uint8_t>(aligned16, swap, P.interleaved != 0);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);  // one value for every plan (G = 16 and G = 4 tiles share kernels)
   if (e != cudaSuccess) return (int)e;
   for (int done = 0; done < n;) {
     const int chunk = n - done > 65535 ? 65535 : n - done;

@@ -236,6 +236,42 @@ def test_alternating_layouts_reuse_their_plans(O):
 
 
 @pytest.mark.gpu
+def test_processors_with_different_rings_share_a_kernel(O):
+    """Two processors whose chains pick the SAME row-staged kernel with DIFFERENT shared-memory rings (1920- and
+    640-wide NV12 sources), called in turn. The dynamic shared-memory limit is an attribute of the kernel, not of a plan:
+    the wide plan's cached launch geometry must survive the narrow plan's set-up (the round-2 final bench crashed on
+    exactly this with cudaErrorLaunchOutOfResources)."""
+    from band_b200 import band_c as B
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 224, 224), NORM]
+    made = []
+    for k, (w, h) in enumerate([(1920, 1080), (640, 480)]):
+        f = rand_frames(O, 1, w, h, O.FMT_NV12, seed=70 + k)
+        st, want = oracle_chain(O, ops, f, w, h, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+        assert st == 0
+        made.append((B.ImageProcessor(to_capi_ops(ops)), B.Buffer.from_numpy(f[0], w, h, B.FORMATS["NV12"]), want[0]))
+    t = B.Tensor(np.float32, (1, 224, 224, 3), device=False)
+    for rnd in range(3):
+        for proc, buf, want in made:
+            assert proc.process(buf, t) == B.kBandOk, B.last_error()
+            assert_same_bits(t.numpy(), want, "round %d" % rnd)
+    # and the other order of first use
+    for proc, buf, _ in made:
+        buf.close(); proc.close()
+    made2 = []
+    for k, (w, h) in enumerate([(640, 480), (1920, 1080)]):
+        f = rand_frames(O, 1, w, h, O.FMT_NV12, seed=80 + k)
+        st, want = oracle_chain(O, ops, f, w, h, O.FMT_NV12, O.DT_F32, (1, 224, 224, 3))
+        made2.append((B.ImageProcessor(to_capi_ops(ops)), B.Buffer.from_numpy(f[0], w, h, B.FORMATS["NV12"]), want[0]))
+    for rnd in range(2):
+        for proc, buf, want in made2:
+            assert proc.process(buf, t) == B.kBandOk, B.last_error()
+            assert_same_bits(t.numpy(), want, "second order, round %d" % rnd)
+    for proc, buf, _ in made2:
+        buf.close(); proc.close()
+    t.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mem", ["host", "pinned", "device"])
 def test_sharded_batch_equals_single_processor_and_oracle(O, mem):
     """24 frames through BandImageProcessorProcessBatchSharded == the same frames through one processor == the oracle.
