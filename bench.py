@@ -209,31 +209,20 @@ def simd_proxy_frames_per_s(threads, seconds=3.0):
     """What an optimised SIMD CPU library does with the same chain on this host: OpenCV's cvtColor(NV12 -> RGB) + bilinear
     resize + float normalise (AVX2 rows, one OpenCV thread per Python thread, the GIL released inside the calls). NOT the
     reference's arithmetic (OpenCV's fixed point differs in the last bits), so it is no parity arm -- it is the stand-in for the
-    AVX2 rows of the real libyuv, which the scalar oracle port lacks. Returns (frames/s, what) or (None, why)."""
+    AVX2 rows of the real libyuv, which the scalar oracle port lacks. Runs in a child interpreter (scripts/simd_proxy.py):
+    importing cv2 into a process that already holds torch + a CUDA context crashed on the GPU box. Returns (frames/s, what)
+    or (None, why)."""
+    import subprocess
+    script = os.path.join(os.path.dirname(os.path.abspath(__file__)), "scripts", "simd_proxy.py")
     try:
-        import cv2
+        r = subprocess.run([sys.executable, script, str(W), str(H), str(DW), str(DH), str(threads), str(seconds)],
+                           capture_output=True, text=True, timeout=seconds * 4 + 120)
+        if r.returncode != 0:
+            return None, "scripts/simd_proxy.py exited %d (%s)" % (r.returncode, (r.stderr or "").strip().splitlines()[-1:] or "")
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        return d["frames_per_s"], d["what"]
     except Exception as e:  # noqa: BLE001
-        return None, "OpenCV not importable (%s)" % type(e).__name__
-    cv2.setNumThreads(1)
-    frame = synth_frames(1)[0].reshape(H * 3 // 2, W)
-    counts = [0] * threads
-
-    def work(i):
-        t_end = time.perf_counter() + seconds
-        while time.perf_counter() < t_end:
-            rgb = cv2.cvtColor(frame, cv2.COLOR_YUV2RGB_NV12)
-            small = cv2.resize(rgb, (DW, DH), interpolation=cv2.INTER_LINEAR)
-            _ = (small.astype(np.float32) - MEAN) / STD
-            counts[i] += 1
-
-    ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
-    t0 = time.perf_counter()
-    for t in ths:
-        t.start()
-    for t in ths:
-        t.join()
-    return sum(counts) / (time.perf_counter() - t0), "OpenCV %s cvtColor(YUV2RGB_NV12) + resize(INTER_LINEAR) + float normalise, %d threads, %.0f s" % (
-        cv2.__version__, threads, seconds)
+        return None, "simd proxy unavailable (%s)" % type(e).__name__
 
 
 def host_threads():
