@@ -5,7 +5,7 @@ N=${1:-2}
 O=gpurun_out
 mkdir -p $O
 nvidia-smi topo -m > $O/r02_topo_${N}gpu.txt 2>&1; lscpu | grep -i -E "numa|model name|^CPU\(s\)|socket" >> $O/r02_topo_${N}gpu.txt
-nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o /tmp/pcie_multi_probe scripts/pcie_multi_probe.cu -lpthread && \
+[ -z "$SKIP_PROBE" ] && nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o /tmp/pcie_multi_probe scripts/pcie_multi_probe.cu -lpthread && \
   timeout 600 /tmp/pcie_multi_probe > $O/r02_pcie_multi_probe_${N}gpu.txt 2>&1; echo "probe rc=$?"; cat $O/r02_pcie_multi_probe_${N}gpu.txt
 python -m pytest tests/test_gpu_host_layer.py -m gpu -x -q > $O/r02_multi_pytest_${N}gpu.log 2>&1; echo "pytest rc=$?"; tail -3 $O/r02_multi_pytest_${N}gpu.log
 for n in 1 2 4 8; do
