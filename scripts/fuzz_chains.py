@@ -1,0 +1,214 @@
+#!/usr/bin/env python
+"""Differential fuzzer: random operator chains on random frames through the product's C API (CUDA) and through the CPU
+oracle; every byte of every output (or the ok / not-ok verdict when the reference rejects the chain) must agree.
+
+The hand-written parity tests pin the cases somebody thought of; this walks the rest of the space: every source format,
+odd and tiny dimensions, every order of Crop / Rotate / Flip / ColorSpaceConvert / Resize the builder accepts, exact-ratio
+and free resizes in both directions, Normalize / DataTypeConvert into every tensor type, single frames and batches,
+host and HBM-resident buffers. A failing case prints the one-line recipe that replays it (--only SEED).
+
+  python scripts/fuzz_chains.py --cases 3000 --seed 1        # on a B200
+  python scripts/fuzz_chains.py --only 1234                  # replay one case verbosely
+"""
+import argparse
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from oracle import oracle as O         # noqa: E402  (test infrastructure: the checker)
+
+FMT_NAMES = {O.FMT_GRAY: "GRAY", O.FMT_RGB: "RGB", O.FMT_RGBA: "RGBA", O.FMT_YV12: "YV12", O.FMT_YV21: "YV21",
+             O.FMT_NV21: "NV21", O.FMT_NV12: "NV12"}
+YUV = (O.FMT_YV12, O.FMT_YV21, O.FMT_NV21, O.FMT_NV12)
+CHANNELS = {O.FMT_GRAY: 1, O.FMT_RGB: 3, O.FMT_RGBA: 4}
+OP_NAMES = {O.OP_CROP: "Crop", O.OP_RESIZE: "Resize", O.OP_ROTATE: "Rotate", O.OP_FLIP: "Flip", O.OP_CSC: "CSC",
+            O.OP_NORMALIZE: "Normalize", O.OP_DTC: "DTC", O.OP_AUTO: "Auto"}
+
+
+def pick_dims(rng):
+    r = rng.random()
+    if r < 0.25:
+        return int(rng.integers(1, 24)), int(rng.integers(1, 24))
+    if r < 0.75:
+        return int(rng.integers(8, 200)), int(rng.integers(8, 160))
+    if r < 0.93:
+        w, h = int(rng.integers(100, 700)), int(rng.integers(60, 500))
+        if rng.random() < 0.5:
+            w, h = w // 16 * 16 + 16, h // 2 * 2 + 2   # the aligned shapes the staged kernels take
+        return w, h
+    return int(rng.choice([640, 1280, 1920])), int(rng.choice([360, 480, 720]))
+
+
+def pick_resize(rng, w, h):
+    r = rng.random()
+    if r < 0.30:   # exact ratios: libyuv's special cases (Down2, Down4, 3/4, 3/8, Up2, same size)
+        num, den = [(1, 2), (1, 4), (3, 4), (3, 8), (2, 1), (1, 1), (1, 3), (4, 1)][int(rng.integers(0, 8))]
+        return max(1, w * num // den), max(1, h * num // den)
+    if r < 0.60:   # free down-scale
+        return max(1, int(w * rng.uniform(0.05, 1.0))), max(1, int(h * rng.uniform(0.05, 1.0)))
+    if r < 0.80:   # free up-scale (bounded output)
+        f = rng.uniform(1.0, 4.0)
+        return min(1024, max(1, int(w * f))), min(1024, max(1, int(h * rng.uniform(1.0, 4.0))))
+    if r < 0.9:    # mixed
+        return min(1024, max(1, int(w * rng.uniform(0.3, 2.0)))), min(1024, max(1, int(h * rng.uniform(0.3, 2.0))))
+    return int(rng.choice([224, 300, 64, 128, 96])), int(rng.choice([224, 300, 64, 128, 96]))
+
+
+def make_case(seed):
+    rng = np.random.default_rng(seed)
+    fmt = int(rng.choice(list(FMT_NAMES)))
+    W, H = pick_dims(rng)
+    if fmt in YUV and rng.random() < 0.7:
+        W, H = max(2, W // 2 * 2), max(2, H // 2 * 2)
+    kinds = [O.OP_CROP, O.OP_ROTATE, O.OP_FLIP, O.OP_CSC, O.OP_RESIZE]
+    rng.shuffle(kinds)
+    kinds = kinds[:int(rng.integers(0, 6))]
+    mode = "tensor" if rng.random() < 0.7 else "image"
+    ops = []
+    w, h, f = W, H, fmt
+    ok = True
+    for k in kinds:
+        if k == O.OP_CROP:
+            if rng.random() < 0.04:
+                op = (k, int(rng.integers(0, w + 3)), int(rng.integers(0, h + 3)), int(rng.integers(0, w + 3)), int(rng.integers(0, h + 3)))
+            else:
+                x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
+                x1, y1 = int(rng.integers(x0, w)), int(rng.integers(y0, h))
+                if rng.random() < 0.5:  # even origin and extent: what a YUV crop wants
+                    x0, y0 = x0 // 2 * 2, y0 // 2 * 2
+                    x1, y1 = min(w - 1, x0 + ((x1 - x0 + 1) // 2 * 2 or 2) - 1), min(h - 1, y0 + ((y1 - y0 + 1) // 2 * 2 or 2) - 1)
+                op = (k, x0, y0, x1, y1)
+        elif k == O.OP_ROTATE:
+            op = (k, int(rng.choice([90, 180, 270, 90, 270, 0, 45])))
+        elif k == O.OP_FLIP:
+            hv = int(rng.integers(1, 4))
+            op = (k, hv & 1, hv >> 1)
+        elif k == O.OP_CSC:
+            op = (k, int(rng.choice([O.FMT_RGB, O.FMT_RGB, O.FMT_RGBA, O.FMT_GRAY, O.FMT_NV21, O.FMT_NV12, O.FMT_YV12, O.FMT_YV21])))
+        else:
+            op = (k,) + pick_resize(rng, w, h)
+        ops.append(op)
+        if ok:  # follow the shape down the chain with the oracle's own operators (tiny frames would do, the real one is used)
+            pass
+    tail = None
+    out_dt = O.DT_U8
+    if mode == "tensor":
+        r = rng.random()
+        if r < 0.45:
+            mean, std = [(127.5, 127.5), (0.0, 255.0), (128.0, 1.0), (103.5, 57.375), (0.0, 1.0)][int(rng.integers(0, 5))]
+            tail = (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)
+            out_dt = int(rng.choice([O.DT_F32, O.DT_F32, O.DT_F32, O.DT_I8, O.DT_U8, O.DT_I16, O.DT_I32]))
+        elif r < 0.6:
+            tail = (O.OP_DTC,)
+            out_dt = int(rng.choice([O.DT_F32, O.DT_I8, O.DT_U8, O.DT_I16, O.DT_I32]))
+        elif r < 0.7 and not ops:
+            out_dt = O.DT_U8  # empty builder: AutoConvert
+    if tail:
+        ops.append(tail)
+    n = int(rng.choice([1, 1, 1, 2, 3, 5]))
+    resident = bool(rng.random() < 0.5)
+    return dict(seed=seed, fmt=fmt, W=W, H=H, ops=ops, mode=mode, out_dt=out_dt, n=n, resident=resident, tail=tail)
+
+
+def describe(c):
+    ops = " -> ".join("%s%s" % (OP_NAMES[o[0]], tuple(o[1:]) if len(o) > 1 else "") for o in c["ops"]) or "(AutoConvert)"
+    return "seed %d: %s %dx%d x%d %s %s | %s | out dt %d" % (c["seed"], FMT_NAMES[c["fmt"]], c["W"], c["H"], c["n"],
+                                                             "resident" if c["resident"] else "host", c["mode"], ops, c["out_dt"])
+
+
+def walk_shape(c, frame):
+    """Final (w, h, format) of the image operators, by the oracle's stand-alone operators; None if one rejects."""
+    cur, w, h, f = frame, c["W"], c["H"], c["fmt"]
+    for op in c["ops"]:
+        if op[0] in (O.OP_NORMALIZE, O.OP_DTC):
+            break
+        st, cur, info = O.run_op(op, cur, w, h, f)
+        if st != 0:
+            return None, None
+        w, h, f = info
+    return (w, h, f), cur
+
+
+def run_case(c, verbose=False):
+    """-> (verdict, detail): 'same', 'both_reject', or a failure string."""
+    import gpu_util as G
+    from band_b200 import band_c as B
+    frames = G.rand_frames(O, c["n"], c["W"], c["H"], c["fmt"], seed=c["seed"] * 7 + 1)
+    shape, final = walk_shape(c, frames[0])
+    if c["mode"] == "image":
+        if shape is None or c["tail"]:
+            return "skipped", "image mode needs a chain the oracle walks"
+        if not c["ops"]:
+            return "skipped", "empty image chain"
+        w, h, f = shape
+        st, got, info = G.gpu_image_chain(c["ops"], frames[0], c["W"], c["H"], c["fmt"], f, O.DT_U8, w, h)
+        if st != 0:
+            return "FAIL", "oracle ok (%dx%d %s), product status %d: %s" % (w, h, FMT_NAMES[f], st, B.last_error())
+        if info[:3] != (w, h, f):
+            return "FAIL", "output info %s, oracle %s" % (info[:3], (w, h, f))
+        bad = int((np.asarray(got) != np.asarray(final)).sum()) if got.shape == final.shape else -1
+        return ("same", "") if bad == 0 else ("FAIL", "%d of %d bytes differ (image %dx%d %s)" % (bad, final.size, w, h, FMT_NAMES[f]))
+    # tensor mode: the whole chain on both sides, the oracle's verdict is the reference's
+    if shape is not None:
+        w, h, f = shape
+        ch = CHANNELS.get(f, 3)
+    else:
+        w, h, ch = 8, 8, 3
+    if not c["ops"]:
+        ch = 3 if c["fmt"] != O.FMT_GRAY else 1
+    dims = (1, h, w, ch)
+    st_o, want = G.oracle_chain(O, c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims)
+    st_g, got = G.gpu_chain(c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims, device_resident=c["resident"])
+    if verbose:
+        print("  oracle status", st_o, "product status", st_g, B.last_error() if st_g else "")
+    if (st_o == 0) != (st_g == 0):
+        return "FAIL", "oracle status %d, product status %d (%s), tensor dims %s" % (st_o, st_g, B.last_error(), dims)
+    if st_o != 0:
+        return "both_reject", ""
+    g = np.ascontiguousarray(got).view(np.uint8)
+    wv = np.ascontiguousarray(want).view(np.uint8)
+    if g.shape != wv.shape:
+        return "FAIL", "shape %s vs %s" % (got.shape, want.shape)
+    bad = int((g != wv).sum())
+    return ("same", "") if bad == 0 else ("FAIL", "%d of %d bytes differ (tensor %s)" % (bad, g.size, dims))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", type=int, default=500)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--only", type=int, default=None)
+    ap.add_argument("--max-fail", type=int, default=40)
+    a = ap.parse_args()
+    if a.only is not None:
+        c = make_case(a.only)
+        print(describe(c))
+        print(run_case(c, verbose=True))
+        return 0
+    counts = {}
+    fails = []
+    t0 = time.time()
+    for s in range(a.seed, a.seed + a.cases):
+        c = make_case(s)
+        try:
+            v, detail = run_case(c)
+        except Exception as e:  # noqa: BLE001
+            v, detail = "FAIL", "exception %s: %s" % (type(e).__name__, e)
+        counts[v] = counts.get(v, 0) + 1
+        if v == "FAIL":
+            fails.append(s)
+            print("FAIL", describe(c), "::", detail, flush=True)
+            if len(fails) >= a.max_fail:
+                break
+    print("fuzz_chains: seeds %d..%d in %.0f s: %s; failing seeds: %s" % (a.seed, a.seed + a.cases - 1, time.time() - t0, counts, fails))
+    return 1 if fails else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
