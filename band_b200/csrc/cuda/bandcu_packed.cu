@@ -512,7 +512,10 @@ __global__ void __launch_bounds__(256) packed_small_up_kernel(const __grid_const
     for (int q = 0; q < NG; ++q) {
       const int w = NG * g + q;
       if (w < full_words && P.vec_ok) reinterpret_cast<uint32_t*>(orow)[w] = v[q];
-      else if (w < row_words) for (int k = 4 * w; k < row_bytes; ++k) orow[k] = (uint8_t)(v[q] >> (8 * (k - 4 * w)));
+      else if (w < row_words) {  // rows that are not word-aligned, and the partial last word of a row: this word's bytes only
+        const int kend = min(row_bytes, 4 * w + 4);
+        for (int k = 4 * w; k < kend; ++k) orow[k] = (uint8_t)(v[q] >> (8 * (k - 4 * w)));
+      }
     }
    }
   }

@@ -60,55 +60,92 @@ def pick_resize(rng, w, h):
     return int(rng.choice([224, 300, 64, 128, 96])), int(rng.choice([224, 300, 64, 128, 96]))
 
 
+VALID_TARGETS = {  # ColorSpaceConvert::ValidateOutput, image_operator.cc:367-399
+    O.FMT_GRAY: [],
+    O.FMT_RGB: [O.FMT_GRAY, O.FMT_NV21, O.FMT_NV12, O.FMT_YV12, O.FMT_YV21],
+    O.FMT_RGBA: [O.FMT_RGB, O.FMT_RGB, O.FMT_GRAY, O.FMT_NV21, O.FMT_NV12, O.FMT_YV12, O.FMT_YV21],
+}
+for _f in YUV:
+    VALID_TARGETS[_f] = [O.FMT_RGB, O.FMT_RGB, O.FMT_RGB, O.FMT_RGBA, O.FMT_GRAY] + [g for g in YUV if g != _f]
+
+
 def make_case(seed):
+    """A chain that is USUALLY valid (the shape and format are followed down the chain), with a few per cent of each kind of
+    mistake the reference rejects: bad angles, crop boxes outside the image, conversions it does not have, a tensor of the
+    wrong type."""
     rng = np.random.default_rng(seed)
     fmt = int(rng.choice(list(FMT_NAMES)))
     W, H = pick_dims(rng)
-    if fmt in YUV and rng.random() < 0.7:
+    if fmt in YUV and rng.random() < 0.8:
         W, H = max(2, W // 2 * 2), max(2, H // 2 * 2)
+    mode = "tensor" if rng.random() < 0.7 else "image"
     kinds = [O.OP_CROP, O.OP_ROTATE, O.OP_FLIP, O.OP_CSC, O.OP_RESIZE]
     rng.shuffle(kinds)
     kinds = kinds[:int(rng.integers(0, 6))]
-    mode = "tensor" if rng.random() < 0.7 else "image"
+    if mode == "tensor" and fmt != O.FMT_RGB and O.OP_CSC not in kinds and fmt != O.FMT_GRAY and rng.random() < 0.92:
+        kinds.insert(int(rng.integers(0, len(kinds) + 1)), O.OP_CSC)   # a tensor is an RGB image (buffer.cc:106-152)
     ops = []
     w, h, f = W, H, fmt
-    ok = True
     for k in kinds:
         if k == O.OP_CROP:
-            if rng.random() < 0.04:
-                op = (k, int(rng.integers(0, w + 3)), int(rng.integers(0, h + 3)), int(rng.integers(0, w + 3)), int(rng.integers(0, h + 3)))
+            if rng.random() < 0.04 or w < 1 or h < 1:
+                op = (k, int(rng.integers(0, max(1, w) + 3)), int(rng.integers(0, max(1, h) + 3)),
+                      int(rng.integers(0, max(1, w) + 3)), int(rng.integers(0, max(1, h) + 3)))
             else:
                 x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
                 x1, y1 = int(rng.integers(x0, w)), int(rng.integers(y0, h))
-                if rng.random() < 0.5:  # even origin and extent: what a YUV crop wants
+                if rng.random() < 0.6:  # even origin and extent: what a YUV crop wants
                     x0, y0 = x0 // 2 * 2, y0 // 2 * 2
-                    x1, y1 = min(w - 1, x0 + ((x1 - x0 + 1) // 2 * 2 or 2) - 1), min(h - 1, y0 + ((y1 - y0 + 1) // 2 * 2 or 2) - 1)
+                    x1 = min(w - 1, x0 + max(2, (x1 - x0 + 1) // 2 * 2) - 1)
+                    y1 = min(h - 1, y0 + max(2, (y1 - y0 + 1) // 2 * 2) - 1)
                 op = (k, x0, y0, x1, y1)
+            w, h = op[3] - op[1] + 1, op[4] - op[2] + 1
         elif k == O.OP_ROTATE:
-            op = (k, int(rng.choice([90, 180, 270, 90, 270, 0, 45])))
+            op = (k, int(rng.choice([90, 180, 270])) if rng.random() < 0.96 else int(rng.choice([0, 45, 360])))
+            if op[1] in (90, 270):
+                w, h = h, w
         elif k == O.OP_FLIP:
             hv = int(rng.integers(1, 4))
             op = (k, hv & 1, hv >> 1)
         elif k == O.OP_CSC:
-            op = (k, int(rng.choice([O.FMT_RGB, O.FMT_RGB, O.FMT_RGBA, O.FMT_GRAY, O.FMT_NV21, O.FMT_NV12, O.FMT_YV12, O.FMT_YV21])))
+            targets = VALID_TARGETS[f]
+            if mode == "tensor" and O.FMT_RGB in targets and rng.random() < 0.85:
+                t = O.FMT_RGB
+            elif targets and rng.random() < 0.95:
+                t = int(rng.choice(targets))
+            else:
+                t = int(rng.choice(list(FMT_NAMES)))
+            op = (k, t)
+            f = t
         else:
-            op = (k,) + pick_resize(rng, w, h)
+            op = (k,) + pick_resize(rng, max(1, w), max(1, h))
+            w, h = op[1], op[2]
         ops.append(op)
-        if ok:  # follow the shape down the chain with the oracle's own operators (tiny frames would do, the real one is used)
-            pass
+    if mode == "tensor" and ops and ops[-1][0] == O.OP_FLIP and ops[-1][1] and ops[-1][2]:
+        # a two-axis Flip writing the caller's buffer dereferences an intermediate that only CreateOutput makes
+        # (image_operator.cc:299-309): the reference crashes, nothing to compare with
+        ops[-1] = (O.OP_FLIP, 1, 0)
     tail = None
     out_dt = O.DT_U8
     if mode == "tensor":
         r = rng.random()
-        if r < 0.45:
-            mean, std = [(127.5, 127.5), (0.0, 255.0), (128.0, 1.0), (103.5, 57.375), (0.0, 1.0)][int(rng.integers(0, 5))]
-            tail = (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)
+        if r < 0.5:
+            # the reference casts (x - mean) to the output type BEFORE dividing (common_operator.cc:24-40): a difference the
+            # type cannot hold is undefined behaviour in C++, so each type only gets means that keep it in range
             out_dt = int(rng.choice([O.DT_F32, O.DT_F32, O.DT_F32, O.DT_I8, O.DT_U8, O.DT_I16, O.DT_I32]))
-        elif r < 0.6:
+            if out_dt == O.DT_U8:
+                choices = [(0.0, 255.0), (0.0, 1.0), (0.0, 2.0)]
+            elif out_dt == O.DT_I8:
+                choices = [(128.0, 1.0), (127.5, 127.5), (127.5, 1.0), (128.0, 2.0)]
+            else:
+                choices = [(127.5, 127.5), (0.0, 255.0), (128.0, 1.0), (103.5, 57.375), (0.0, 1.0)]
+            mean, std = choices[int(rng.integers(0, len(choices)))]
+            tail = (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)
+        elif r < 0.65:
             tail = (O.OP_DTC,)
-            out_dt = int(rng.choice([O.DT_F32, O.DT_I8, O.DT_U8, O.DT_I16, O.DT_I32]))
-        elif r < 0.7 and not ops:
-            out_dt = O.DT_U8  # empty builder: AutoConvert
+            out_dt = int(rng.choice([O.DT_F32, O.DT_U8, O.DT_I16, O.DT_I32]))   # u8 -> i8 overflows above 127: undefined
+        elif r < 0.68:
+            out_dt = int(rng.choice([O.DT_F32, O.DT_I8]))   # no converting operator: the reference rejects the type
     if tail:
         ops.append(tail)
     n = int(rng.choice([1, 1, 1, 2, 3, 5]))
@@ -135,12 +172,107 @@ def walk_shape(c, frame):
     return (w, h, f), cur
 
 
-def run_case(c, verbose=False):
-    """-> (verdict, detail): 'same', 'both_reject', or a failure string."""
+def arith_shape(c):
+    """The output shape the chain's arguments ask for, whether or not an operator will reject them: the tensor handed to
+    the processor has THIS shape (a mismatching one is undefined behaviour in the reference: ColorSpaceConvert validates
+    formats only, image_operator.cc:367-399, and libyuv then writes input-sized rows into it)."""
+    w, h, f = c["W"], c["H"], c["fmt"]
+    for op in c["ops"]:
+        if op[0] == O.OP_CROP:
+            w, h = op[3] - op[1] + 1, op[4] - op[2] + 1
+        elif op[0] == O.OP_ROTATE and op[1] in (90, 270):
+            w, h = h, w
+        elif op[0] == O.OP_RESIZE:
+            w, h = op[1], op[2]
+        elif op[0] == O.OP_CSC:
+            f = op[1]
+    if w <= 0 or h <= 0:
+        return None
+    return w, h, f
+
+
+def oracle_side(seed):
+    """Everything the checker computes for one case (runs in the worker process: a chain the reference would crash on
+    takes the worker down, not the run)."""
+    import gpu_util as G
+    c = make_case(seed)
+    frames = G.rand_frames(O, c["n"], c["W"], c["H"], c["fmt"], seed=seed * 7 + 1)
+    shape, final = walk_shape(c, frames[0])
+    r = dict(shape=shape, final=final)
+    if c["mode"] == "tensor":
+        a = arith_shape(c)
+        if a is None:
+            r["skip"] = "degenerate shape"
+            return r
+        w, h, f = a
+        if w < 2 or h < 2:
+            r["skip"] = "a tensor dimension of 1 is squeezed away (buffer.cc:106-152): raw output, undefined in the reference"
+            return r
+        r["dims"] = (1, h, w, 3)
+        r["st"], r["want"] = G.oracle_chain(O, c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], r["dims"])
+    return r
+
+
+class OracleWorker:
+    """A child interpreter answering oracle_side(seed) over pipes; restarted when it dies."""
+
+    def __init__(self):
+        self.p = None
+
+    def start(self):
+        import subprocess
+        self.p = subprocess.Popen([sys.executable, os.path.abspath(__file__), "--oracle-worker"], stdin=subprocess.PIPE,
+                                  stdout=subprocess.PIPE)
+
+    def ask(self, seed):
+        import pickle
+        import struct
+        if self.p is None or self.p.poll() is not None:
+            self.start()
+        try:
+            self.p.stdin.write(struct.pack("<q", seed))
+            self.p.stdin.flush()
+            head = self.p.stdout.read(8)
+            if len(head) < 8:
+                raise EOFError
+            n = struct.unpack("<q", head)[0]
+            return pickle.loads(self.p.stdout.read(n))
+        except (EOFError, BrokenPipeError, OSError):
+            self.p.wait()
+            rc = self.p.returncode
+            self.p = None
+            return dict(crashed=rc)
+
+    def close(self):
+        if self.p is not None and self.p.poll() is None:
+            self.p.stdin.close()
+            self.p.wait()
+
+
+def oracle_worker_loop():
+    import pickle
+    import struct
+    inp, out = sys.stdin.buffer, sys.stdout.buffer
+    while True:
+        head = inp.read(8)
+        if len(head) < 8:
+            return
+        r = oracle_side(struct.unpack("<q", head)[0])
+        blob = pickle.dumps(r, protocol=4)
+        out.write(struct.pack("<q", len(blob)))
+        out.write(blob)
+        out.flush()
+
+
+def run_case(c, worker, verbose=False):
+    """-> (verdict, detail): 'same', 'both_reject', 'skipped', 'reference_crashes', or 'FAIL' with the difference."""
     import gpu_util as G
     from band_b200 import band_c as B
     frames = G.rand_frames(O, c["n"], c["W"], c["H"], c["fmt"], seed=c["seed"] * 7 + 1)
-    shape, final = walk_shape(c, frames[0])
+    r = worker.ask(c["seed"])
+    if "crashed" in r:
+        return "reference_crashes", "oracle worker died with %s" % r["crashed"]
+    shape, final = r["shape"], r["final"]
     if c["mode"] == "image":
         if shape is None or c["tail"]:
             return "skipped", "image mode needs a chain the oracle walks"
@@ -155,18 +287,17 @@ def run_case(c, verbose=False):
         bad = int((np.asarray(got) != np.asarray(final)).sum()) if got.shape == final.shape else -1
         return ("same", "") if bad == 0 else ("FAIL", "%d of %d bytes differ (image %dx%d %s)" % (bad, final.size, w, h, FMT_NAMES[f]))
     # tensor mode: the whole chain on both sides, the oracle's verdict is the reference's
-    if shape is not None:
-        w, h, f = shape
-        ch = CHANNELS.get(f, 3)
-    else:
-        w, h, ch = 8, 8, 3
-    if not c["ops"]:
-        ch = 3 if c["fmt"] != O.FMT_GRAY else 1
-    dims = (1, h, w, ch)
-    st_o, want = G.oracle_chain(O, c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims)
+    if "skip" in r:
+        return "skipped", r["skip"]
+    dims, st_o, want = r["dims"], r["st"], r["want"]
     st_g, got = G.gpu_chain(c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims, device_resident=c["resident"])
     if verbose:
-        print("  oracle status", st_o, "product status", st_g, B.last_error() if st_g else "")
+        print("  dims", dims, "oracle status", st_o, "product status", st_g, B.last_error() if st_g else "")
+    if st_o == 0 and st_g != 0 and "Crop: input and output buffer formats must match" in B.last_error():
+        # deliberate deviation: Crop of an RGBA image into an RGB buffer passes the reference's compatibility test
+        # (buffer.cc IsBufferFormatCompatible) and then copies 4-byte pixels into 3-byte rows -- past the end of the
+        # output on the last row. The product refuses instead of overrunning.
+        return "reference_overruns", ""
     if (st_o == 0) != (st_g == 0):
         return "FAIL", "oracle status %d, product status %d (%s), tensor dims %s" % (st_o, st_g, B.last_error(), dims)
     if st_o != 0:
@@ -185,27 +316,40 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--only", type=int, default=None)
     ap.add_argument("--max-fail", type=int, default=40)
+    ap.add_argument("--seeds", type=str, default=None, help="comma-separated seeds instead of a range")
+    ap.add_argument("--quiet", action="store_true")
+    ap.add_argument("--oracle-worker", action="store_true", help=argparse.SUPPRESS)
     a = ap.parse_args()
+    if a.oracle_worker:
+        oracle_worker_loop()
+        return 0
+    worker = OracleWorker()
     if a.only is not None:
         c = make_case(a.only)
         print(describe(c))
-        print(run_case(c, verbose=True))
+        print(run_case(c, worker, verbose=True))
+        worker.close()
         return 0
     counts = {}
     fails = []
     t0 = time.time()
-    for s in range(a.seed, a.seed + a.cases):
+    seeds = [int(x) for x in a.seeds.split(",")] if a.seeds else range(a.seed, a.seed + a.cases)
+    for s in seeds:
         c = make_case(s)
         try:
-            v, detail = run_case(c)
+            v, detail = run_case(c, worker)
         except Exception as e:  # noqa: BLE001
             v, detail = "FAIL", "exception %s: %s" % (type(e).__name__, e)
         counts[v] = counts.get(v, 0) + 1
+        if v == "reference_crashes":
+            print("note", describe(c), "::", detail, flush=True)
         if v == "FAIL":
             fails.append(s)
-            print("FAIL", describe(c), "::", detail, flush=True)
+            if not a.quiet:
+                print("FAIL", describe(c), "::", detail, flush=True)
             if len(fails) >= a.max_fail:
                 break
+    worker.close()
     print("fuzz_chains: seeds %d..%d in %.0f s: %s; failing seeds: %s" % (a.seed, a.seed + a.cases - 1, time.time() - t0, counts, fails))
     return 1 if fails else 0
 
