@@ -69,7 +69,88 @@ for _f in YUV:
     VALID_TARGETS[_f] = [O.FMT_RGB, O.FMT_RGB, O.FMT_RGB, O.FMT_RGBA, O.FMT_GRAY] + [g for g in YUV if g != _f]
 
 
+def make_staged_case(seed):
+    """The shapes the staged kernels are built for -- 4:2:0 source, (Crop / Rotate / Flip) -> ColorSpaceConvert(RGB) ->
+    Resize down -> (Normalize) in the orders that fold into one launch -- with the geometry left free: source sizes around the
+    16- and 32-byte granules, even and odd crop boxes, output sizes from 8 to 640 (two passes above 512 columns), every
+    layout, batches, pageable / pinned / HBM-resident / padded-stride frames."""
+    rng = np.random.default_rng(seed)
+    fmt = int(rng.choice(YUV))
+    r = rng.random()
+    if r < 0.45:
+        W, H = int(rng.integers(4, 60)) * 16, int(rng.integers(20, 300)) * 2
+    elif r < 0.75:
+        W, H = int(rng.integers(20, 500)) * 2, int(rng.integers(20, 300)) * 2
+    elif r < 0.85:
+        W, H = int(rng.integers(33, 700)), int(rng.integers(33, 500))
+    else:
+        W, H = [(640, 480), (1280, 720), (1920, 1080), (1920, 1088), (3840, 2160)][int(rng.integers(0, 5))]
+    pre = []
+    w, h = W, H
+    kinds = [O.OP_CROP, O.OP_ROTATE, O.OP_FLIP]
+    rng.shuffle(kinds)
+    for k in kinds[:int(rng.choice([0, 0, 1, 1, 2, 3]))]:
+        if k == O.OP_CROP:
+            x0, y0 = int(rng.integers(0, w // 2)), int(rng.integers(0, h // 2))
+            x1, y1 = int(rng.integers(x0 + w // 4, w)), int(rng.integers(y0 + h // 4, h))
+            if rng.random() < 0.8:
+                x0, y0 = x0 // 2 * 2, y0 // 2 * 2
+                x1, y1 = min(w - 1, x0 + max(2, (x1 - x0 + 1) // 2 * 2) - 1), min(h - 1, y0 + max(2, (y1 - y0 + 1) // 2 * 2) - 1)
+            pre.append((k, x0, y0, x1, y1))
+            w, h = x1 - x0 + 1, y1 - y0 + 1
+        elif k == O.OP_ROTATE:
+            a = int(rng.choice([90, 180, 270]))
+            pre.append((k, a))
+            if a != 180:
+                w, h = h, w
+        else:
+            hv = int(rng.integers(1, 4))
+            pre.append((k, hv & 1, hv >> 1))
+    r = rng.random()
+    if r < 0.7:
+        dw, dh = max(2, int(w * rng.uniform(0.08, 1.0))), max(2, int(h * rng.uniform(0.08, 1.0)))
+    elif r < 0.9:
+        dw = dh = int(rng.choice([64, 96, 128, 224, 256, 299, 300, 320, 384, 512, 513, 640]))
+    else:
+        dw, dh = max(2, w // int(rng.choice([1, 2, 3, 4]))), max(2, h // int(rng.choice([1, 2, 3, 4])))
+    dw, dh = min(dw, 1024), min(dh, 1024)
+    post = []
+    if rng.random() < 0.15:  # an index operator AFTER the conversion (does not fold into the row-staged kernel)
+        post = [(O.OP_FLIP, 1, 0)] if not any(o[0] == O.OP_FLIP for o in pre) else []
+    order = rng.random()
+    if order < 0.8:
+        ops = pre + [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh)] + post
+    else:  # conversion first: the index operators act on the RGB image
+        ops = [(O.OP_CSC, O.FMT_RGB)] + pre + [(O.OP_RESIZE, dw, dh)] + post
+    out_dt, tail = O.DT_U8, None
+    r = rng.random()
+    if r < 0.6:
+        out_dt = O.DT_F32
+        mean, std = [(127.5, 127.5), (0.0, 255.0), (128.0, 1.0), (103.5, 57.375)][int(rng.integers(0, 4))]
+        tail = (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)
+    elif r < 0.7:
+        out_dt = O.DT_I8
+        tail = (O.OP_NORMALIZE, 0, 0, 0, 0, 128.0, 1.0)
+    elif r < 0.75:
+        out_dt = O.DT_F32
+        tail = (O.OP_DTC,)
+    if tail:
+        ops.append(tail)
+    big = W * H > 1000 * 1000
+    n = int(rng.choice([1, 2, 3, 7, 16])) if not big else int(rng.choice([1, 2, 3]))
+    mem = str(rng.choice(["host", "resident", "pinned", "padded_host", "padded_resident", "resident", "pinned"]))
+    return dict(seed=seed, fmt=fmt, W=W, H=H, ops=ops, mode="tensor", out_dt=out_dt, n=n, resident=(mem == "resident"),
+                tail=tail, mem=mem, pads=(int(rng.choice([0, 16, 64, 8, 3])), int(rng.choice([0, 16, 32, 6, 1]))),
+                misalign=int(rng.choice([0, 0, 0, 4, 1])))
+
+
 def make_case(seed):
+    if seed % 3 == 0:
+        return make_staged_case(seed)
+    return make_free_case(seed)
+
+
+def make_free_case(seed):
     """A chain that is USUALLY valid (the shape and format are followed down the chain), with a few per cent of each kind of
     mistake the reference rejects: bad angles, crop boxes outside the image, conversions it does not have, a tensor of the
     wrong type."""
@@ -155,8 +236,13 @@ def make_case(seed):
 
 def describe(c):
     ops = " -> ".join("%s%s" % (OP_NAMES[o[0]], tuple(o[1:]) if len(o) > 1 else "") for o in c["ops"]) or "(AutoConvert)"
-    return "seed %d: %s %dx%d x%d %s %s | %s | out dt %d" % (c["seed"], FMT_NAMES[c["fmt"]], c["W"], c["H"], c["n"],
-                                                             "resident" if c["resident"] else "host", c["mode"], ops, c["out_dt"])
+    mem = c.get("mem") or ("resident" if c["resident"] else "host")
+    if mem.startswith("padded"):
+        mem += "%s" % (c["pads"],)
+    if mem == "pinned" and c.get("misalign"):
+        mem += "+%d" % c["misalign"]
+    return "seed %d: %s %dx%d x%d %s %s | %s | out dt %d" % (c["seed"], FMT_NAMES[c["fmt"]], c["W"], c["H"], c["n"], mem,
+                                                             c["mode"], ops, c["out_dt"])
 
 
 def walk_shape(c, frame):
@@ -264,6 +350,81 @@ def oracle_worker_loop():
         out.flush()
 
 
+def _padded_layout(frame, W, H, fmt, y_pad, c_pad):
+    """The same pixels with padded rows: -> (backing array, y_off, u_off, v_off, y_stride, c_stride, pixel_stride)."""
+    cw, ch = (W + 1) // 2, (H + 1) // 2
+    ys = W + y_pad
+    y = frame[:W * H].reshape(H, W)
+    if fmt in (O.FMT_NV12, O.FMT_NV21):
+        cs = 2 * cw + c_pad
+        back = np.full(H * ys + ch * cs + 64, 0xEE, dtype=np.uint8)
+        back[:H * ys].reshape(H, ys)[:, :W] = y
+        back[H * ys:H * ys + ch * cs].reshape(ch, cs)[:, :2 * cw] = frame[W * H:].reshape(ch, 2 * cw)
+        first, second = H * ys, H * ys + 1
+        u_off, v_off = (first, second) if fmt == O.FMT_NV12 else (second, first)
+        return back, 0, u_off, v_off, ys, cs, 2
+    cs = cw + c_pad
+    back = np.full(H * ys + 2 * ch * cs + 64, 0xEE, dtype=np.uint8)
+    back[:H * ys].reshape(H, ys)[:, :W] = y
+    p1 = frame[W * H:W * H + cw * ch].reshape(ch, cw)
+    p2 = frame[W * H + cw * ch:].reshape(ch, cw)
+    back[H * ys:H * ys + ch * cs].reshape(ch, cs)[:, :cw] = p1
+    back[H * ys + ch * cs:H * ys + 2 * ch * cs].reshape(ch, cs)[:, :cw] = p2
+    o1, o2 = H * ys, H * ys + ch * cs
+    u_off, v_off = (o2, o1) if fmt == O.FMT_YV12 else (o1, o2)   # YV12: Y, V, U; YV21: Y, U, V (buffer.cc:48-78)
+    return back, 0, u_off, v_off, ys, cs, 1
+
+
+def gpu_tensor_chain(c, frames, dims):
+    """The product side of a tensor-mode case for every memory kind -> (status, ndarray or None)."""
+    import ctypes as C
+    import gpu_util as G
+    from band_b200 import band_c as B
+    mem = c.get("mem") or ("resident" if c["resident"] else "host")
+    ops = c["ops"] or [(O.OP_AUTO,)]
+    if mem in ("host", "resident"):
+        return G.gpu_chain(ops, frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims, device_resident=(mem == "resident"))
+    L = B.lib()
+    n, fb = frames.shape
+    W, H, fmt = c["W"], c["H"], c["fmt"]
+    device = mem.endswith("resident")
+    proc = B.ImageProcessor(G.to_capi_ops(ops))
+    tens = [B.Tensor(G.NP_OF_ORC[c["out_dt"]], dims, device=device) for _ in range(n)]
+    bufs, host, dev, keep = [], None, None, []
+    try:
+        if mem == "pinned":
+            pitch = (fb + 255) // 256 * 256
+            host = L.BandHostAlloc(pitch * n + 64)
+            for i in range(n):
+                ptr = host + c.get("misalign", 0) + i * pitch
+                C.memmove(ptr, frames[i].ctypes.data, fb)
+                bufs.append(B.Buffer().set_raw(ptr, W, H, fmt))
+        else:
+            y_pad, c_pad = c["pads"]
+            lays = [_padded_layout(frames[i], W, H, fmt, y_pad, c_pad) for i in range(n)]
+            size = lays[0][0].size
+            pitch = (size + 255) // 256 * 256
+            if device:
+                dev = L.BandDeviceAlloc(pitch * n)
+                for i, lay in enumerate(lays):
+                    if L.BandCopyToDevice(dev + i * pitch, lay[0].ctypes.data, size) != B.kBandOk:
+                        raise B.BandError("device upload failed")
+            for i, (back, yo, uo, vo, ys, cs, ps) in enumerate(lays):
+                base = dev + i * pitch if device else back.ctypes.data
+                keep.append(back)
+                bufs.append(B.Buffer().set_yuv(base + yo, base + uo, base + vo, W, H, ys, cs, ps, fmt, device=device))
+        st = proc.process_batch(bufs, tens) if n != 1 else proc.process(bufs[0], tens[0])
+        out = np.stack([t.numpy() for t in tens]) if st == B.kBandOk else None
+        return st, out
+    finally:
+        for x in bufs + tens + [proc]:
+            x.close()
+        if host:
+            L.BandHostFree(host)
+        if dev:
+            L.BandDeviceFree(dev)
+
+
 def run_case(c, worker, verbose=False):
     """-> (verdict, detail): 'same', 'both_reject', 'skipped', 'reference_crashes', or 'FAIL' with the difference."""
     import gpu_util as G
@@ -290,13 +451,13 @@ def run_case(c, worker, verbose=False):
     if "skip" in r:
         return "skipped", r["skip"]
     dims, st_o, want = r["dims"], r["st"], r["want"]
-    st_g, got = G.gpu_chain(c["ops"] or [(O.OP_AUTO,)], frames, c["W"], c["H"], c["fmt"], c["out_dt"], dims, device_resident=c["resident"])
+    st_g, got = gpu_tensor_chain(c, frames, dims)
     if verbose:
         print("  dims", dims, "oracle status", st_o, "product status", st_g, B.last_error() if st_g else "")
-    if st_o == 0 and st_g != 0 and "Crop: input and output buffer formats must match" in B.last_error():
-        # deliberate deviation: Crop of an RGBA image into an RGB buffer passes the reference's compatibility test
-        # (buffer.cc IsBufferFormatCompatible) and then copies 4-byte pixels into 3-byte rows -- past the end of the
-        # output on the last row. The product refuses instead of overrunning.
+    if st_o == 0 and st_g != 0 and "input and output buffer formats must match" in B.last_error():
+        # deliberate deviation: Crop / Flip / Rotate of an RGBA image into an RGB buffer passes the reference's
+        # compatibility test (buffer.cc IsBufferFormatCompatible) and then moves 4-byte pixels into 3-byte rows -- past
+        # the end of the output (larger frames abort the oracle worker with a corrupted heap). The product refuses.
         return "reference_overruns", ""
     if (st_o == 0) != (st_g == 0):
         return "FAIL", "oracle status %d, product status %d (%s), tensor dims %s" % (st_o, st_g, B.last_error(), dims)
