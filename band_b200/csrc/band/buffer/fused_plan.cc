@@ -200,7 +200,10 @@ absl::Status ChainLowering::Flush() {
 
 absl::Status ChainLowering::EmitInto(int dst_slot, const ImageLayout& dst) {
   View& v = *view_;
-  if (dst.format != v.format || dst.width != v.w || dst.height != v.h)
+  // YV12 <-> YV21: both sides' U and V planes are resolved by name (BufferPointers), like the reference's *Yv routines
+  auto planar = [](BufferFormat f) { return f == BufferFormat::kYV12 || f == BufferFormat::kYV21; };
+  const bool same_layout = dst.format == v.format || (planar(dst.format) && planar(v.format));
+  if (!same_layout || dst.width != v.w || dst.height != v.h)
     return absl::InvalidArgumentError(absl::StrFormat(
         "output buffer is %s %dx%d but the chain produces %s %dx%d", ToString(dst.format), dst.width, dst.height,
         ToString(v.format), v.w, v.h));

@@ -24,6 +24,23 @@ Buffer* EmptyLike(const Buffer& input, size_t w, size_t h, BufferFormat format, 
 
 bool QuarterTurn(int angle_deg) { return (angle_deg / 90) % 2 == 1; }
 
+// An index operator (or a YUV-domain Resize) whose cached output carries another layout than this call's input. The
+// reference accepts every pair inside {RGB, RGBA} and inside the four 4:2:0 layouts (Buffer::IsBufferFormatCompatible,
+// buffer.cc:367-388). What it then does is only well defined for the two PLANAR layouts: CropYv / RotateYv / FlipYv /
+// ResizeYv resolve the U and V planes of both buffers by name (libyuv_image_operator.cc GetYuvDataFromBuffer), so a
+// processor that first saw YV21 and now sees YV12 produces the same pixels as a fresh one -- a camera that swaps its
+// planar layout mid-stream keeps working. The other pairs are refused here: semi-planar pairs copy the interleaved
+// plane raw and relabel it (U and V change places) or, for Rotate, write it one byte off (:816-887); planar <->
+// semi-planar and RGBA -> RGB move rows of one geometry into buffers of another, past their end.
+bool PlanarPair(BufferFormat a, BufferFormat b) {
+  const bool pa = a == BufferFormat::kYV12 || a == BufferFormat::kYV21;
+  const bool pb = b == BufferFormat::kYV12 || b == BufferFormat::kYV21;
+  return pa && pb;
+}
+bool LayoutsAgree(const Buffer& input, const Buffer& output) {
+  return input.GetBufferFormat() == output.GetBufferFormat() || PlanarPair(input.GetBufferFormat(), output.GetBufferFormat());
+}
+
 }  // namespace
 
 IBufferOperator::Type Crop::GetOpType() const { return Type::kImage; }
@@ -94,7 +111,7 @@ absl::Status Crop::CreateOutput(const Buffer& input) {
 }
 
 absl::Status Crop::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
-  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+  if (!LayoutsAgree(input, *GetOutput()))
     return absl::InvalidArgumentError("Crop: input and output buffer formats must match");
   return lowering.Crop(x0_, y0_, x1_, y1_);
 }
@@ -145,7 +162,7 @@ absl::Status Resize::CreateOutput(const Buffer& input) {
 absl::Status Resize::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
   // Deliberate deviation (memory safety): the reference lets RGBA resize into an
   // RGB buffer and writes 4 bytes per pixel into it (libyuv_image_operator.cc:1213-1229).
-  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+  if (!LayoutsAgree(input, *GetOutput()))
     return absl::InvalidArgumentError("Resize: input and output buffer formats must match");
   return lowering.Scale(static_cast<int>(GetOutput()->GetDimension()[0]),
                         static_cast<int>(GetOutput()->GetDimension()[1]));
@@ -182,7 +199,7 @@ absl::Status Rotate::CreateOutput(const Buffer& input) {
 }
 
 absl::Status Rotate::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
-  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+  if (!LayoutsAgree(input, *GetOutput()))
     return absl::InvalidArgumentError("Rotate: input and output buffer formats must match");
   return lowering.Rotate(angle_deg_);
 }
@@ -216,7 +233,7 @@ absl::Status Flip::CreateOutput(const Buffer& input) {
 }
 
 absl::Status Flip::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
-  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+  if (!LayoutsAgree(input, *GetOutput()))
     return absl::InvalidArgumentError("Flip: input and output buffer formats must match");
   return lowering.Flip(horizontal_, vertical_);
 }
@@ -271,7 +288,7 @@ absl::Status AutoOrient::CreateOutput(const Buffer& input) {
 }
 
 absl::Status AutoOrient::Lower(cuda::ChainLowering& lowering, const Buffer& input) const {
-  if (input.GetBufferFormat() != GetOutput()->GetBufferFormat())
+  if (!LayoutsAgree(input, *GetOutput()))
     return absl::InvalidArgumentError("AutoOrient: input and output buffer formats must match");
   bool mirror;
   int angle;

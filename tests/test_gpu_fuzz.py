@@ -48,3 +48,54 @@ def test_fuzz_generator_is_deterministic_and_mostly_valid(O):
         else:
             rej += 1
     assert ok >= 25, (ok, rej)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("first", [1, 61])
+def test_random_sessions_match_a_persistent_oracle_processor(O, first):
+    """scripts/fuzz_sessions.py: one processor, many calls -- refilled buffers, new handles, other layouts, other memory
+    kinds, other batch sizes, host and HBM tensors -- against an oracle processor that lives as long."""
+    import fuzz_sessions as S
+    bad = []
+    for s in range(first, first + 60):
+        bad += S.run_session(s)
+    assert not bad, "\n".join(bad[:10])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("first_op", ["flip", "rotate", "crop"])
+def test_planar_layout_may_change_under_an_index_first_processor(O, first_op):
+    """A processor whose first operator is Crop / Rotate / Flip caches an intermediate in the first frame's layout. The
+    reference accepts the other planar layout on later calls and resolves U and V by name on both sides
+    (buffer.cc:367-388, libyuv_image_operator.cc *Yv routines): same pixels as a fresh processor. Semi-planar pairs are
+    refused (the reference exchanges U and V there, or writes the plane one byte off)."""
+    import numpy as np
+    from band_b200 import band_c as B
+    from gpu_util import assert_same_bits, oracle_chain, rand_frames, to_capi_ops
+    W, H = 96, 64
+    pre = {"flip": (O.OP_FLIP, 1, 0), "rotate": (O.OP_ROTATE, 90), "crop": (O.OP_CROP, 8, 4, 71, 51)}[first_op]
+    ow, oh = {"flip": (48, 32), "rotate": (32, 48), "crop": (32, 24)}[first_op]
+    ops = [pre, (O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, ow, oh)]
+    proc = B.ImageProcessor(to_capi_ops(ops))
+    t = B.Tensor(np.uint8, (1, oh, ow, 3), device=False)
+    for k, name in enumerate(["YV21", "YV12", "YV21", "YV12"]):
+        fmt = getattr(O, "FMT_" + name)
+        f = rand_frames(O, 1, W, H, fmt, seed=300 + k)
+        st, want = oracle_chain(O, ops, f, W, H, fmt, O.DT_U8, (1, oh, ow, 3))
+        assert st == 0
+        buf = B.Buffer.from_numpy(f[0], W, H, B.FORMATS[name])
+        assert proc.process(buf, t) == B.kBandOk, B.last_error()
+        assert_same_bits(t.numpy(), want[0], "call %d (%s)" % (k, name))
+        buf.close()
+    # semi-planar after planar: refused, and the processor keeps working afterwards
+    f = rand_frames(O, 1, W, H, O.FMT_NV12, seed=310)
+    buf = B.Buffer.from_numpy(f[0], W, H, B.FORMATS["NV12"])
+    assert proc.process(buf, t) != B.kBandOk
+    assert "formats must match" in B.last_error()
+    buf.close()
+    f = rand_frames(O, 1, W, H, O.FMT_YV12, seed=311)
+    st, want = oracle_chain(O, ops, f, W, H, O.FMT_YV12, O.DT_U8, (1, oh, ow, 3))
+    buf = B.Buffer.from_numpy(f[0], W, H, B.FORMATS["YV12"])
+    assert proc.process(buf, t) == B.kBandOk, B.last_error()
+    assert_same_bits(t.numpy(), want[0], "after the refused call")
+    buf.close(); t.close(); proc.close()
