@@ -154,9 +154,12 @@ struct ChainLowering::View {
   // common_operator.cc:24-40) instead of the fused u8 store stage
   bool elementwise = false;
   DataType ew_in_dtype = DataType::kUInt8;
+  // the view IS the image in memory. A Crop whose box starts at (0, 0) leaves identity maps but a smaller image: its rows
+  // are not contiguous in the source, so linear-memory stages (element-wise Normalize, plane scalers) must not take it
+  // for materialised memory (found by scripts/fuzz_chains.py, seed 19022).
   bool Untouched() const {
     return IsIdentity(luma) && IsIdentity(pre) && IsIdentity(chroma) && cvt == BANDCU_CVT_NONE && !scaled &&
-           !normalized;
+           !normalized && w == src.width && h == src.height;
   }
   bool IsYuv() const { return Buffer::IsYUV(format); }
 };

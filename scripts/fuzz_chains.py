@@ -311,6 +311,14 @@ class OracleWorker:
                                   stdout=subprocess.PIPE)
 
     def ask(self, seed):
+        """One retry in a fresh worker: an earlier undefined-behaviour chain may have damaged the old worker's heap, and
+        the crash then lands on an innocent seed."""
+        r = self._ask_once(seed)
+        if "crashed" in r:
+            r = self._ask_once(seed)
+        return r
+
+    def _ask_once(self, seed):
         import pickle
         import struct
         if self.p is None or self.p.poll() is not None:

@@ -99,3 +99,30 @@ def test_planar_layout_may_change_under_an_index_first_processor(O, first_op):
     assert proc.process(buf, t) == B.kBandOk, B.last_error()
     assert_same_bits(t.numpy(), want[0], "after the refused call")
     buf.close(); t.close(); proc.close()
+
+
+@pytest.mark.gpu
+def test_seeds_that_found_bugs_stay_fixed(O):
+    """16 / 46 / 284 / 482: packed_small_up_kernel byte stores on rows that are not word-aligned.
+    19022: a Crop whose box starts at (0, 0) left identity index maps, and the Normalize behind it took the smaller view
+    for materialised memory (linear index over the UNcropped rows)."""
+    counts, fails = _run([16, 46, 284, 482, 19022])
+    assert not fails, "\n".join(fails)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("box", [(0, 0, 1, 1), (0, 0, 4, 2), (0, 0, 7, 1), (0, 0, 2, 3)])
+@pytest.mark.parametrize("out_dt_name,mean,std", [("DT_U8", 0.0, 1.0), ("DT_F32", 127.5, 127.5), ("DT_I8", 128.0, 1.0)])
+def test_crop_at_the_origin_behind_a_resize_then_normalize(O, box, out_dt_name, mean, std):
+    from gpu_util import assert_same_bits, gpu_chain, oracle_chain, rand_frames
+    W, H = 20, 6
+    out_dt = getattr(O, out_dt_name)
+    ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, 8, 4), (O.OP_CROP,) + box, (O.OP_NORMALIZE, 0, 0, 0, 0, mean, std)]
+    dims = (1, box[3] - box[1] + 1, box[2] - box[0] + 1, 3)
+    fr = rand_frames(O, 2, W, H, O.FMT_NV21, seed=77)
+    st, want = oracle_chain(O, ops, fr, W, H, O.FMT_NV21, out_dt, dims)
+    assert st == 0
+    for resident in (False, True):
+        st, got = gpu_chain(ops, fr, W, H, O.FMT_NV21, out_dt, dims, device_resident=resident)
+        assert st == 0
+        assert_same_bits(got, want, "crop %s -> %s" % (box, out_dt_name))
