@@ -26,6 +26,8 @@ static int fail(int code, const char* what) {
   }
   return code;
 }
+// the same thread-local message for the entry points that live in other files (bandcu_noalloc.cu)
+int report_error(int code, const char* what) { return fail(code, what); }
 #define CU_TRY(expr, what)                      \
   do {                                          \
     cudaError_t _e = (expr);                    \

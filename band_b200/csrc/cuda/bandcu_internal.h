@@ -10,6 +10,8 @@ namespace bandcu {
 struct BatchArgs;
 
 void count_launch();
+// records the calling thread's bandcu_last_error_string() and returns `code` (cudaError_t or BANDCU_E_*)
+int report_error(int code, const char* what);
 int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaStream_t stream);
 int launch_yuv_map(const BandCuYuvMapDesc& d, const BandCuYuvPtrs& p, long long src_step, long long dst_step, int n,
                    cudaStream_t stream);

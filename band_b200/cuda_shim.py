@@ -123,9 +123,13 @@ def lib():
     L.bandcu_pointer_kind.argtypes = [vp]
     L.bandcu_pointer_device.argtypes = [vp]
     L.bandcu_plan_rerun.argtypes = [vp, vp]
+    L.bandcu_two_stage_run_noalloc.argtypes = [C.POINTER(PlanDesc), C.POINTER(PlanDesc), C.POINTER(Frame), vp]
     L.bandcu_last_error_string.restype = C.c_char_p
     _lib = L
     return L
+
+
+NOALLOC_SCRATCH_BYTES = 8 << 20   # BANDCU_NOALLOC_SCRATCH_BYTES (include/bandcu.h)
 
 
 def check(code, what=""):
@@ -142,4 +146,5 @@ EXPORTED = [
     "bandcu_event_create", "bandcu_event_create_sync", "bandcu_stream_wait_event", "bandcu_event_destroy", "bandcu_event_record", "bandcu_event_elapsed_ms",
     "bandcu_pointer_is_device", "bandcu_pointer_kind", "bandcu_last_error_string",
     "bandcu_pointer_device", "bandcu_plan_rerun", "bandcu_memcpy2d_d2h", "bandcu_host_register", "bandcu_host_unregister", "bandcu_registered_host_pointers_usable",
+    "bandcu_two_stage_run_noalloc",
 ]

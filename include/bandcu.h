@@ -163,6 +163,26 @@ BANDCU_API int bandcu_plan_rerun(BandCuPlan* plan, void* stream);
 /* number of kernel launches issued by this library on the calling process so far */
 BANDCU_API long long bandcu_launch_count(void);
 
+/* ---- a two-stage chain that allocates nothing -------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * Runs `first` on the frame's planes into an intermediate u8 image, then `second` (whose source is that image:
+ * src_kind GRAY / RGB / RGBA == first->channels, stride0 == first->dst_row_stride) into frame->out -- what the plan
+ * compiler does with plan-owned cudaMalloc'ed scratch for chains that cannot be one launch, e.g. 4:2:0 -> RGBA followed
+ * by the bilinear up-scale of that image. The intermediate image lives in a file-scope device array of
+ * BANDCU_NOALLOC_SCRATCH_BYTES (bandcu_noalloc.cu): every GPU that loads libbandcu.so holds those 8 MiB until exit.
+ * first->dst_row_stride * first->dst_height above that size is rejected with BANDCU_E_INVALID and a message; so is a
+ * second stage whose index map leaves the intermediate image. Both stages run on the pixel-per-thread kernel (values
+ * identical to bandcu_plan_run's). The call makes no cudaMalloc / cudaFree / cudaMallocHost and no allocating library
+ * call; the first call on a device resolves the array's address (cudaGetSymbolAddress) -- make that one outside stream
+ * capture. ALL calls share the array, which keeps the previous call's bytes (nothing needs to start at zero: stage 1
+ * writes every pixel stage 2 reads); calls that overlap on one GPU (two streams, two threads) RACE on it -- one call at
+ * a time per GPU. frame->p0/pu/pv/out are device pointers as for bandcu_plan_run. */
+#define BANDCU_NOALLOC_SCRATCH_BYTES (8u << 20)
+BANDCU_API int bandcu_two_stage_run_noalloc(const BandCuPlanDesc* first, const BandCuPlanDesc* second,
+                                            const BandCuFrame* frame, void* stream);
+
 /* ---- 4:2:0 -> 4:2:0 index-mapped copy (Crop/Rotate/Flip/ColorSpaceConvert with a
  * YUV output: CropNv/CropYv :950-1037, RotateYv/RotateNv :786-887, YUV<->YUV
  * repacks :125-162,:213-250,:302-367, Flip* :1232-1363) -------------------- */
