@@ -173,6 +173,11 @@ static int run_batch(BandCuPlan* plan, const BatchArgs& b, const TableHints& hin
     if (e == BANDCU_OK) { trace_path("tile-staged", plan, n); return BANDCU_OK; }
     if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: tile kernel launch");
   }
+  {  // u8 plane down-scales (Resize of a 4:2:0 buffer, of a gray image): ahead of the packed kernel, which covers gray only
+    int e = launch_plane_rows(plan->d, b, hints, n, s);
+    if (e == BANDCU_OK) { trace_path("plane-rows", plan, n); return BANDCU_OK; }
+    if (e != BANDCU_E_UNSUPPORTED) return fail(e, "plan_run: plane-rows kernel launch");
+  }
   if (plan->packed) {
     int e = launch_packed(plan->packed, plan->d, b, hints, n, s);
     if (e == BANDCU_OK) { trace_path("packed", plan, n); return BANDCU_OK; }

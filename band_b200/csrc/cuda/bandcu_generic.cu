@@ -253,6 +253,37 @@ __global__ void __launch_bounds__(256) fused_generic_kernel(const __grid_constan
   }
 }
 
+// Plane scalers (ScalePlane on gray / Y / planar U, V; UVScale on interleaved chroma: ResizeYv / ResizeNv,
+// libyuv_image_operator.cc:376-435) on the paths no staged kernel covers -- point sampling, ratios above 2, 3/4, 3/8, the 2x
+// up-samplers: FOUR adjacent output pixels per thread through the same scale_px(), stored as one word (gray) or two (UV).
+// One pixel per thread meant one byte store per thread (a warp wrote 32 bytes) and the row terms of the scaler -- y, its clamp,
+// the row pointers -- computed once per output BYTE; here they are shared by four pixels and a warp stores 128 / 256 bytes.
+template <int SRC>
+__global__ void __launch_bounds__(256) fused_plane_x4_kernel(const __grid_constant__ GenericParams P) {
+  const BandCuPlanDesc& d = P.d;
+  constexpr int CH = SRC == BANDCU_SRC_UV ? 2 : 1;
+  const int ox0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int oy = blockIdx.y * blockDim.y + threadIdx.y;
+  if (ox0 >= d.dst_width || oy >= d.dst_height) return;
+  const FramePtrs f = frame_ptrs(P.batch, blockIdx.z);
+  uint32_t px[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) px[k] = scale_px<SRC, BANDCU_CVT_NONE, 1>(d, f, oy, min(ox0 + k, d.dst_width - 1));
+  uint8_t* o = f.out + (long long)oy * d.dst_row_stride + (long long)ox0 * CH;
+  const int nvalid = min(4, d.dst_width - ox0);
+  if (nvalid == 4 && (reinterpret_cast<uintptr_t>(o) & 3) == 0) {
+    if (CH == 1) {
+      *reinterpret_cast<uint32_t*>(o) = (px[0] & 0xFF) | ((px[1] & 0xFF) << 8) | ((px[2] & 0xFF) << 16) | (px[3] << 24);
+    } else {
+      reinterpret_cast<uint32_t*>(o)[0] = (px[0] & 0xFFFF) | (px[1] << 16);
+      reinterpret_cast<uint32_t*>(o)[1] = (px[2] & 0xFFFF) | (px[3] << 16);
+    }
+    return;
+  }
+  for (int k = 0; k < nvalid; ++k)
+    for (int c = 0; c < CH; ++c) o[k * CH + c] = (uint8_t)(px[k] >> (8 * c));
+}
+
 static bool is_identity_map(const BandCuAffine& m) {
   return m.r0 == 0 && m.rr == 1 && m.rc == 0 && m.c0 == 0 && m.cr == 0 && m.cc == 1;
 }
@@ -292,6 +323,15 @@ int launch_generic(const BandCuPlanDesc& d, const BatchArgs& batch, int n, cudaS
   if (P.transposed) grid = dim3((d.dst_height + 31) / 32, (d.dst_width + 7) / 8, 1);
   const bool ident = is_identity_map(d.luma_map) && is_identity_map(d.pre_map) && is_identity_map(d.chroma_map);
   void (*kern)(GenericParams) = pick_generic(d.src_kind, d.cvt, ident);
+  {  // u8 planes without index maps: four pixels per thread
+    static const bool x4_off = getenv("BANDCU_DISABLE_PLANE_X4") && getenv("BANDCU_DISABLE_PLANE_X4")[0] == '1';
+    const bool gray = d.src_kind == BANDCU_SRC_GRAY && d.channels == 1, uv = d.src_kind == BANDCU_SRC_UV && d.channels == 2;
+    if (!x4_off && (gray || uv) && d.cvt == BANDCU_CVT_NONE && ident && !d.normalize && d.out_dtype == BANDCU_DT_U8 &&
+        d.scale_mode != BANDCU_SCALE_COPY) {
+      kern = gray ? fused_plane_x4_kernel<BANDCU_SRC_GRAY> : fused_plane_x4_kernel<BANDCU_SRC_UV>;
+      grid = dim3((d.dst_width + 127) / 128, (d.dst_height + 7) / 8, 1);
+    }
+  }
   // gridDim.z is limited to 65535: chunk very large batches
   for (int done = 0; done < n;) {
     int chunk = n - done > 65535 ? 65535 : n - done;

@@ -58,6 +58,9 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
 // Same-size conversions (ColorSpaceConvert without a Resize, optionally behind a Crop): four pixels per thread, 32-bit
 // accesses (bandcu_copy.cu). BANDCU_E_UNSUPPORTED: another chain, or a batch that is not word aligned.
 int launch_copy_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream);
+// Down-scaling one u8 plane (gray / Y / U / V, or interleaved chroma): blended row pair in shared memory, then the column
+// filter (bandcu_planes.cu). BANDCU_E_UNSUPPORTED for anything else.
+int launch_plane_rows(const BandCuPlanDesc& d, const BatchArgs& batch, const TableHints& hints, int n, cudaStream_t stream);
 // One plane of an index-mapped copy (Crop / Rotate / Flip of a 4:2:0 plane or of a packed image).
 struct PlaneMap {
   const uint8_t* src;

@@ -257,6 +257,21 @@ def image_case(name, ops, W, H, fmt, out_fmt, ow, oh, n, steps):
             "alg_bytes_per_frame": alg, "achieved_GBps": fps * alg / 1e9, "frac_of_measured_hbm": fps * alg / 1e9 / peak()}
 
 
+def r_cases(steps):
+    W, H, n = 1920, 1080, 256
+    return [
+        image_case("g_1080p_nv21_resize_640x360", [(B.BAND_RESIZE, 640, 360)], W, H, B.kBandNV21, B.kBandNV21, 640, 360, n, steps),
+        # YUV-domain Resize (ResizeNv / ResizeYv, libyuv_image_operator.cc:376-435) at ratios that take libyuv's other paths:
+        # 1/3 above is point-sampled; 2/3 bilinear down, 1/2 the 2x2 box, 0.55 a free bilinear ratio, 2x the up-samplers
+        image_case("g_1080p_nv21_resize_1280x720", [(B.BAND_RESIZE, 1280, 720)], W, H, B.kBandNV21, B.kBandNV21, 1280, 720, n, steps),
+        image_case("g_1080p_yv12_resize_1280x720", [(B.BAND_RESIZE, 1280, 720)], W, H, B.kBandYV12, B.kBandYV12, 1280, 720, n, steps),
+        image_case("g_1080p_nv21_resize_960x540", [(B.BAND_RESIZE, 960, 540)], W, H, B.kBandNV21, B.kBandNV21, 960, 540, n, steps),
+        image_case("g_1080p_nv21_resize_1056x594", [(B.BAND_RESIZE, 1056, 594)], W, H, B.kBandNV21, B.kBandNV21, 1056, 594, n, steps),
+        image_case("g_1080p_yv12_resize_416x234", [(B.BAND_RESIZE, 416, 234)], W, H, B.kBandYV12, B.kBandYV12, 416, 234, n, steps),
+        image_case("g_540p_nv21_resize_up_1920x1080", [(B.BAND_RESIZE, 1920, 1080)], 960, 540, B.kBandNV21, B.kBandNV21, 1920, 1080, n, steps),
+    ]
+
+
 def g_cases(steps):
     W, H, n = 1920, 1080, 256
     csc = B.BAND_COLOR_SPACE_CONVERT
@@ -285,7 +300,7 @@ def g_cases(steps):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x,g")
+    ap.add_argument("--configs", default="c1,c2,c3,c4,c5,x,g,r")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--cpu", action="store_true")
     ap.add_argument("--device", type=int, default=0)
@@ -333,6 +348,9 @@ def main():
         out.append(tensor_case("x_320x240_yv12_up_to_1024x768_f32", 320, 240, "YV12", 1024, 768, True, 128, a.steps, False))
         out.append(tensor_case("x_1080p_nv21_rot180_to_224_f32", 1920, 1080, "NV21", 224, 224, True, 1024, a.steps, a.cpu,
                                pre_ops=[(B.BAND_ROTATE, 180)], pre_ops_o=[(O.OP_ROTATE, 180)]))
+    if "r" in want:  # Resize in the YUV domain, every libyuv path
+        for r in r_cases(a.steps):
+            print(json.dumps(r), flush=True)
     if "g" in want:  # single-operator image -> image chains
         out += g_cases(a.steps)
     if "c5" in want:

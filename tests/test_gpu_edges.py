@@ -156,6 +156,26 @@ def test_resize_in_yuv_domain(O, fmt_name, W, H, dw, dh):
     assert_same_bits(got, want, "yuv resize %s %dx%d->%dx%d" % (fmt_name, W, H, dw, dh))
 
 
+@pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21", "GRAY"])
+@pytest.mark.parametrize("W,H,dw,dh", [
+    (1920, 1080, 1280, 720), (1920, 1080, 960, 540), (1920, 1080, 1056, 594), (1920, 1080, 416, 234), (1920, 1080, 480, 270),
+    (1282, 722, 801, 403),    # chroma rows of 641 bytes: partial last word, odd strides -> the fallback kernels
+    (1284, 724, 803, 405),    # word-aligned strides, odd output width: byte stores at the row ends
+    (648, 488, 640, 240),     # unit-ish horizontal step, 1/2 vertical
+    (640, 480, 700, 300),     # up horizontally, down vertically: still Scale*BilinearDown
+    (3840, 2160, 1280, 1080), (640, 480, 160, 120), (640, 480, 80, 120)])
+def test_plane_down_scales_row_staged(O, fmt_name, W, H, dw, dh):
+    """bandcu_planes.cu: one warp per output row, blended row pair in shared memory, then the column filter -- against the
+    oracle's ScalePlane / UVScale (and, through BANDCU_DISABLE_PLANE_ROWS in the variants run, the pixel-per-thread kernel)."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, W + 5 * dw)[0]
+    st, want, winfo = O.run_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt, cap=max(1 << 16, dw * dh * 4))
+    assert st == 0 and st2 == 0, (st, st2)
+    assert info[:3] == tuple(winfo)
+    assert_same_bits(got, want, "plane rows %s %dx%d->%dx%d" % (fmt_name, W, H, dw, dh))
+
+
 @pytest.mark.parametrize("fmt_name", ["NV21", "YV12"])
 def test_resize_yuv_then_convert_chain(O, fmt_name):
     """Chain order matters: Resize in the YUV domain THEN ColorSpaceConvert uses the plane blenders, not the ARGB one."""
