@@ -176,6 +176,43 @@ def test_plane_down_scales_row_staged(O, fmt_name, W, H, dw, dh):
     assert_same_bits(got, want, "plane rows %s %dx%d->%dx%d" % (fmt_name, W, H, dw, dh))
 
 
+@pytest.mark.parametrize("fmt_name", ["NV12", "NV21", "YV12", "YV21", "GRAY"])
+@pytest.mark.parametrize("W,H,dw,dh", [
+    (960, 540, 1920, 1080), (642, 362, 1284, 724), (641, 361, 1282, 722), (641, 361, 1281, 721), (642, 362, 1283, 723),
+    (100, 60, 200, 60), (100, 60, 199, 60), (102, 62, 204, 186),   # rows kept / tripled: the Linear form
+    (6, 4, 12, 8), (2, 2, 4, 4), (3, 3, 5, 5), (1920, 32, 3840, 64)])
+def test_plane_exact_2x_up_samplers(O, fmt_name, W, H, dw, dh):
+    """ScalePlaneUp2_{Linear,Bilinear} / ScaleUV{Linear,Bilinear}Up2 and their edge rules (bandcu_planes.cu plane_up2_kernel)."""
+    fmt = getattr(O, "FMT_" + fmt_name)
+    fr = rand_frames(O, 1, W, H, fmt, W + 7 * dw)[0]
+    st, want, winfo = O.run_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt)
+    st2, got, info = gpu_op((O.OP_RESIZE, dw, dh), fr, W, H, fmt, cap=max(1 << 16, dw * dh * 4))
+    assert st == 0 and st2 == 0, (st, st2)
+    assert info[:3] == tuple(winfo)
+    assert_same_bits(got, want, "up2 %s %dx%d->%dx%d" % (fmt_name, W, H, dw, dh))
+
+
+@pytest.mark.parametrize("src_name", ["RGBA", "RGB"])
+@pytest.mark.parametrize("W,H,dw,dh", [(64, 64, 128, 128), (100, 60, 200, 120), (33, 21, 65, 41), (33, 21, 66, 42), (50, 40, 100, 40)])
+def test_gray_conversion_then_exact_2x_up(O, src_name, W, H, dw, dh):
+    """CSC(Gray) -> Resize at exactly 2x: RAWToJ400 / ARGBToJ400 on the fetch, then ScalePlaneUp2 (BASELINE configs[4]'s
+    RGBA 64^2 -> gray 128^2 point)."""
+    fmt = getattr(O, "FMT_" + src_name)
+    ops = [(O.OP_CSC, O.FMT_GRAY), (O.OP_RESIZE, dw, dh)]
+    fr = rand_frames(O, 3, W, H, fmt, 17 + W)
+    cur_w = []
+    for f in fr:
+        cur, w, h, ff = f, W, H, fmt
+        for op in ops:
+            st, cur, (w, h, ff) = O.run_op(op, cur, w, h, ff)
+            assert st == 0
+        cur_w.append(cur)
+    for k, f in enumerate(fr):
+        st, got, info = gpu_image_chain(ops, f, W, H, fmt, O.FMT_GRAY, O.DT_U8, dw, dh)
+        assert st == 0 and info[:3] == (dw, dh, O.FMT_GRAY)
+        assert_same_bits(got, cur_w[k], "%s -> gray -> %dx%d" % (src_name, dw, dh))
+
+
 @pytest.mark.parametrize("fmt_name", ["NV21", "YV12"])
 def test_resize_yuv_then_convert_chain(O, fmt_name):
     """Chain order matters: Resize in the YUV domain THEN ColorSpaceConvert uses the plane blenders, not the ARGB one."""
