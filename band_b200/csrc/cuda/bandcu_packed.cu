@@ -665,7 +665,12 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
       const long long col_threads = (long long)n * ((row_words + per_warp - 1) / per_warp) * 32;
       int rpt = (int)((4LL * d.dst_height + d.vh - 1) / d.vh);
       rpt = rpt < 16 ? 16 : rpt > 256 ? 256 : rpt;
-      while (rpt > 16 && col_threads * ((d.dst_height + rpt - 1) / rpt) < 148LL * 2048 * 4) rpt >>= 1;
+      // ... and at least 2 (gray) / 3 (RGB, RGBA) waves of resident threads (64 registers: 1024 threads per SM). The target used to
+      // be 8 waves: on small batches of large outputs that cut a thread's strip to 16 rows, and the column filter of a source
+      // row pair -- rebuilt at the top of every strip -- was amortised over half a source row's worth of output
+      // (ncu: 8.9 instructions per output byte on RGBA 64^2 -> gray 2048^2; 0.52 -> 0.80 of the HBM roofline with 2 waves)
+      const long long want_threads = 148LL * 1024 * (d.channels == 1 ? 2 : 3);
+      while (rpt > 16 && col_threads * ((d.dst_height + rpt - 1) / rpt) < want_threads) rpt >>= 1;
       P.up_rows = rpt;
       block = dim3(32, 4, 1);  // each thread: its words of P.up_rows rows
       grid = dim3((row_words + per_warp - 1) / per_warp, (d.dst_height + 4 * rpt - 1) / (4 * rpt), 1);
