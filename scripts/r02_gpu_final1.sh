@@ -11,4 +11,4 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
   python bench.py --steps 20 --warmup 5 --no-cpu --no-secondary --no-pageable --sustain-seconds 0.02 --no-check > $O/r02_final_ncu_launches.log 2>&1; echo "ncu list rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:fast_nv_bilinear -s 4 -c 2 -f -o $O/r02_final_fast_F2048 \
   python bench.py --steps 3 --warmup 3 --no-cpu --no-secondary --no-pageable --sustain-seconds 0.001 --no-check > $O/r02_final_ncu_full.log 2>&1; echo "ncu full rc=$?"
-python scripts/bench_configs.py --configs c1,c2,c3,c4,c5,x,g > $O/r02_final_configs.jsonl 2> $O/r02_final_configs.err; echo "configs rc=$?"
+python scripts/bench_configs.py --configs c1,c2,c3,c4,c5,x,g,r > $O/r02_final_configs.jsonl 2> $O/r02_final_configs.err; echo "configs rc=$?"
