@@ -482,12 +482,6 @@ absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
   }
   if (view_->scaled || view_->normalized) RETURN_IF_ERROR(Flush());
   {
-    // An UP-scale of a 4:2:0 source into RGB / RGBA (ConvertFromNv* then ResizeRgb's ARGBScale up path,
-    // libyuv_image_operator.cc:92-300,1146-1187): fused, every output pixel would convert its four source pixels again --
-    // (scale factor)^2 conversions per source pixel on the pixel-per-thread kernel. Materialising the converted image
-    // once (the same-size conversion kernel) and up-scaling it with the row-streaming packed kernels is what the
-    // reference does stage by stage, moves W*H*3 extra bytes against an output (factor)^2 times that size, and keeps
-    // both launches on vectorised kernels. Values are identical either way.
     const View& cur = *view_;
     // RGB / RGBA -> gray in front of an up-scale (RAWToJ400 / ARGBToJ400 then ScalePlane): fused, every source pixel would be
     // converted once per fetch, (factor)^2 times over; the gray image is a quarter of the source and is materialised first.
@@ -499,6 +493,12 @@ absl::Status ChainLowering::Scale(int dst_width, int dst_height) {
       RETURN_IF_ERROR(Flush());
   }
   {
+    // An UP-scale of a 4:2:0 source into RGB / RGBA (ConvertFromNv* then ResizeRgb's ARGBScale up path,
+    // libyuv_image_operator.cc:92-300,1146-1187): fused, every output pixel would convert its four source pixels again --
+    // (scale factor)^2 conversions per source pixel on the pixel-per-thread kernel. Materialising the converted image
+    // once (the same-size conversion kernel) and up-scaling it with the row-streaming packed kernels is what the
+    // reference does stage by stage, moves W*H*3 extra bytes against an output (factor)^2 times that size, and keeps
+    // both launches on vectorised kernels. Values are identical either way.
     const View& cur = *view_;
     const bool yuv_to_packed = Buffer::IsYUV(cur.src.format) && (cur.cvt == BANDCU_CVT_YUV2RGB || cur.cvt == BANDCU_CVT_YUV2RGBA);
     if (yuv_to_packed && DispatchArgbScale(cur.w, cur.h, dst_width, dst_height).mode == BANDCU_SCALE_BILINEAR_UP) {
