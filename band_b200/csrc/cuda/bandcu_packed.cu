@@ -652,7 +652,7 @@ int launch_packed(PackedPlan* p, const BandCuPlanDesc& d, const BatchArgs& batch
       const int nwt = d.channels == 3 ? 3 : 4;
       up_rows = row_words <= 64 ? 1 : 2;
       // u8 rows of at least 1 KB that start 16-byte aligned: four consecutive words per lane, 128-bit stores
-      if (!d.normalize && P.vec_ok && row_words >= 256 && p->up_rows_mode != 2) up_rows = 3;
+      if (!d.normalize && P.vec_ok && row_words >= 128 && p->up_rows_mode != 2) up_rows = 3;
       // RGB outputs of small-ratio up-scales: the column filter dominates, keep its terms in registers (four pixels per thread)
       // (measured: at factors >= 8 the 128-bit-store form wins for RGB and gray alike)
       if (!d.normalize && p->up_rows_mode < 0 && (d.channels == 3 || d.channels == 1) && d.dst_height < 8 * d.vh) {
