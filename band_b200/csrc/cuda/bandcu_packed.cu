@@ -342,20 +342,37 @@ __global__ void __launch_bounds__(128) packed_up_rows_px4_kernel(const __grid_co
     c1[k] = min(max(xi + 1, 0), P.sw - 1);
     xw[k] = x;  // packed_hblend takes the 16.16 position (7-bit truncating ARGB filter / rounding plane filter)
   }
-  // column filter of one source row for this thread's four pixels
-  auto filter = [&](const uint8_t* __restrict__ row, uint32_t (&out)[NT]) {
-    uint32_t px[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      px[k] = packed_hblend<PLANE>(packed_fetch<SRCCH, CVT>(row, c0[k]), packed_fetch<SRCCH, CVT>(row, c1[k]), xw[k]);
+  // column filter of one source row for this thread's four pixels. Results stay in LANE form -- channels 0, 2 in the 16-bit
+  // lanes of .x, channels 1, 3 in those of .y -- which is what the truncating blend produces and what the row terms consume:
+  // packing them into bytes only for up_terms() to split them again cost ~8 of ~50 instructions per pixel and source row
+  // (ncu: the px4 kernel is ALU-bound at small factors, profiles/r02_ncu_px4_nv21_up2x.txt).
+  auto filter = [&](const uint8_t* __restrict__ row, uint2 (&out)[NT]) {
     if (PLANE) {
-      out[0] = (px[0] & 0xFF) | ((px[1] & 0xFF) << 8) | ((px[2] & 0xFF) << 16) | (px[3] << 24);
+      uint32_t px[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        px[k] = packed_hblend<true>(packed_fetch<SRCCH, CVT>(row, c0[k]), packed_fetch<SRCCH, CVT>(row, c1[k]), xw[k]);
+      out[0] = make_uint2((px[0] & 0xFF) | ((px[2] & 0xFF) << 16), (px[1] & 0xFF) | ((px[3] & 0xFF) << 16));
     } else {
 #pragma unroll
-      for (int k = 0; k < NT; ++k) out[k] = px[k];
+      for (int k = 0; k < NT; ++k) {
+        const uint32_t a = packed_fetch<SRCCH, CVT>(row, c0[k]), b = packed_fetch<SRCCH, CVT>(row, c1[k]);
+        const uint32_t f7 = (uint32_t)((xw[k] >> 9) & 0x7f), w0 = 0x7fu ^ f7;  // blend_cols4_trunc7 without its final pack
+        const uint32_t lo = (a & 0x00FF00FFu) * w0 + (b & 0x00FF00FFu) * f7;
+        const uint32_t hi = ((a >> 8) & 0x00FF00FFu) * w0 + ((b >> 8) & 0x00FF00FFu) * f7;
+        out[k] = make_uint2((lo >> 7) & 0x00FF00FFu, (hi >> 7) & 0x00FF00FFu);
+      }
     }
   };
-  uint32_t h1[NT];
+  auto lane_terms = [](const uint2 a, const uint2 b) {
+    UpTerms t;
+    t.d_lo = b.x - a.x;
+    t.d_hi = b.y - a.y;
+    t.base_lo = (a.x << 8) + 0x00800080u;
+    t.base_hi = (a.y << 8) + 0x00800080u;
+    return t;
+  };
+  uint2 h1[NT];
   UpTerms t[NT];
   int cur_yi = INT_MIN, have1 = -1;
   int y_raw = P.y0 + oy_begin * P.dy;
@@ -367,7 +384,7 @@ __global__ void __launch_bounds__(128) packed_up_rows_px4_kernel(const __grid_co
     const uint32_t yf = P.linear ? 0u : (uint32_t)((y >> 8) & 255);
     if (yi != cur_yi) {
       const int r0 = min(max(yi, 0), P.sh - 1), r1 = min(max(yi + 1, 0), P.sh - 1);
-      uint32_t a[NT], b[NT];
+      uint2 a[NT], b[NT];
       if (r0 == have1) {
 #pragma unroll
         for (int k = 0; k < NT; ++k) a[k] = h1[k];
@@ -383,7 +400,7 @@ __global__ void __launch_bounds__(128) packed_up_rows_px4_kernel(const __grid_co
 #pragma unroll
       for (int k = 0; k < NT; ++k) {
         h1[k] = b[k];
-        t[k] = up_terms(a[k], b[k]);
+        t[k] = lane_terms(a[k], b[k]);
       }
       cur_yi = yi;
       have1 = r1;
