@@ -209,7 +209,8 @@ def simd_proxy_frames_per_s(threads, seconds=3.0):
     """What an optimised SIMD CPU library does with the same chain on this host: OpenCV's cvtColor(NV12 -> RGB) + bilinear
     resize + float normalise (AVX2 rows, one OpenCV thread per Python thread, the GIL released inside the calls). NOT the
     reference's arithmetic (OpenCV's fixed point differs in the last bits), so it is no parity arm -- it is the stand-in for the
-    AVX2 rows of the real libyuv, which the scalar oracle port lacks. Runs in a child interpreter (scripts/simd_proxy.py):
+    AVX2 rows of the real libyuv (the oracle port has its own AVX2 rows for the full-frame passes since late round 2; this stays as an
+    independent check of its speed). Runs in a child interpreter (scripts/simd_proxy.py):
     importing cv2 into a process that already holds torch + a CUDA context crashed on the GPU box. Returns (frames/s, what)
     or (None, why)."""
     import subprocess
@@ -600,13 +601,13 @@ def run_ours(args):
         per_thread = max(4, int(fps1 / th * args.cpu_seconds))
         fps, secs = cpu_frames_per_s(per_thread, th)
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": th, "kind": "port",
-                                "sample": "%d frames of the same workload (%d per thread x %d threads), %.1f s; restated scalar C, no hand-written SIMD"
+                                "sample": "%d frames of the same workload (%d per thread x %d threads), %.1f s; restated C with AVX2 rows for the full-frame passes (4:2:0 -> RGB, RGB24 -> ARGB, InterpolateRow), bit-identical to its scalar form"
                                           % (per_thread * th, per_thread, th, secs)}
         proxy, what = simd_proxy_frames_per_s(th)
         line["cpu_baseline"]["simd_proxy"] = {
             "value": proxy, "unit": "frames/s", "what": what,
-            "note": "stand-in for the AVX2 rows of the real libyuv (absent here): the scalar port above understates what a "
-                    "deployment of the reference reaches on this host by about this factor; not bit-comparable, no parity arm"}
+            "note": "an independent optimised CPU library on the same threads, as a sanity check of the port's speed (the real "
+                    "libyuv is absent here); not bit-comparable, no parity arm"}
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -779,8 +780,8 @@ def run_reference(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8 fixed-point -> f32", "data": "synthetic (seeded uniform bytes)",
             "config": {"workload": WORKLOAD, "frames_per_step": per_thread * th},
             "cpu_baseline": {"value": value, "unit": "frames/s", "cores": th, "kind": "port",
-                             "sample": sample + "; restated scalar C (no hand-written SIMD): a libyuv build with its AVX2 rows "
-                                                "would be a small integer factor faster"},
+                             "sample": sample + "; restated C with AVX2 rows for the full-frame passes (4:2:0 -> RGB, RGB24 -> ARGB, "
+                                                "InterpolateRow), bit-identical to its scalar form (tests/test_oracle_golden.py)"},
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)

@@ -112,6 +112,7 @@ int orc_I420Copy(const uint8_t* src_y, int src_stride_y, const uint8_t* src_u, i
                  int dst_stride_u, uint8_t* dst_v, int dst_stride_v, int width, int height);
 /* single-pixel helper exported for exhaustive tests (row_common.cc YuvPixel, kYuvI601Constants) */
 void orc_YuvPixel(uint8_t y, uint8_t u, uint8_t v, uint8_t* r, uint8_t* g, uint8_t* b);
+long orc_yuv_rows_selftest(void); /* vector rows vs scalar pixel on all 2^24 triples: differing values (0) */
 
 /* ---- libyuv scalers (scale.cc / scale_argb.cc / scale_uv.cc / scale_common.cc) */
 int orc_FixedDiv(int num, int div);

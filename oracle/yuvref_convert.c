@@ -24,7 +24,7 @@ static inline uint8_t clamp255(int32_t v) {
   return (uint8_t)(v > 255 ? 255 : v);
 }
 
-void orc_YuvPixel(uint8_t y, uint8_t u, uint8_t v, uint8_t* r, uint8_t* g, uint8_t* b) {
+static inline void yuv_pixel(uint8_t y, uint8_t u, uint8_t v, uint8_t* r, uint8_t* g, uint8_t* b) {
   uint32_t y32 = (uint32_t)y * 0x0101u;
   int32_t y1 = (int32_t)((uint32_t)(y32 * 18997u) >> 16) + (-1160);
   int32_t ui = (int32_t)u - 128; /* int8 wrap of (int8)u - 0x80 == u - 128 */
@@ -36,6 +36,133 @@ void orc_YuvPixel(uint8_t y, uint8_t u, uint8_t v, uint8_t* r, uint8_t* g, uint8
   *g = clamp255(g16 >> 6);
   *r = clamp255(r16 >> 6);
 }
+/* the exported form (tests call it for the 2^24-triple table); the walkers below use the inline one: an exported function
+ * of a -fPIC library is neither inlined nor vectorised (it may be interposed), and the timed CPU baseline spent most of a
+ * frame in that call */
+void orc_YuvPixel(uint8_t y, uint8_t u, uint8_t v, uint8_t* r, uint8_t* g, uint8_t* b) { yuv_pixel(y, u, v, r, g, b); }
+
+#ifdef __AVX2__
+#include <immintrin.h>
+/* Sixteen pixels of the same arithmetic in 16-bit lanes (what libyuv's own AVX2 rows do; used by the TIMED CPU baseline so that
+ * it is not a scalar straw man -- bench.py --impl reference). Exactness against yuv_pixel():
+ *   y1  = mulhi_epu16(y * 257, 18997) - 1160               : the unsigned 16 x 16 -> high 16 product IS (y32 * 18997) >> 16;
+ *   g16, r16 stay inside int16 for every input; b16 = y1 + 128 (u - 128) can reach 34092 -- the saturating add clips it to
+ *   32767, and both 32767 >> 6 and 34092 >> 6 exceed 255, so the final clamp gives 255 either way;
+ *   >> 6 is an arithmetic shift in both forms, packus saturates to 0..255 like clamp255().
+ * orc_yuv_rows_selftest() below compares the two forms on all 2^24 (y, u, v) triples (tests/test_oracle_golden.py).
+ * uv16: 8 chroma pairs as bytes u0 v0 u1 v1 ... (one pair per two pixels). Writes r, g, b for 16 pixels. */
+static inline void yuv16_avx2(const uint8_t* py, __m128i uv16, __m128i* r8, __m128i* g8, __m128i* b8) {
+  const __m256i y = _mm256_cvtepu8_epi16(_mm_loadu_si128((const __m128i*)py));
+  const __m256i y1 = _mm256_sub_epi16(_mm256_mulhi_epu16(_mm256_mullo_epi16(y, _mm256_set1_epi16(257)),
+                                                          _mm256_set1_epi16((short)18997)),
+                                      _mm256_set1_epi16(1160));
+  const __m256i uv = _mm256_broadcastsi128_si256(uv16);
+  /* lane 0: pairs 0..3 for pixels 0..7, lane 1: pairs 4..7 for pixels 8..15; every pair feeds two 16-bit lanes */
+  const __m256i mu = _mm256_setr_epi8(0, -1, 0, -1, 2, -1, 2, -1, 4, -1, 4, -1, 6, -1, 6, -1,
+                                      8, -1, 8, -1, 10, -1, 10, -1, 12, -1, 12, -1, 14, -1, 14, -1);
+  const __m256i mv = _mm256_setr_epi8(1, -1, 1, -1, 3, -1, 3, -1, 5, -1, 5, -1, 7, -1, 7, -1,
+                                      9, -1, 9, -1, 11, -1, 11, -1, 13, -1, 13, -1, 15, -1, 15, -1);
+  const __m256i c128 = _mm256_set1_epi16(128);
+  const __m256i ui = _mm256_sub_epi16(_mm256_shuffle_epi8(uv, mu), c128);
+  const __m256i vi = _mm256_sub_epi16(_mm256_shuffle_epi8(uv, mv), c128);
+  const __m256i b16 = _mm256_adds_epi16(y1, _mm256_slli_epi16(ui, 7));
+  const __m256i g16 = _mm256_sub_epi16(y1, _mm256_add_epi16(_mm256_mullo_epi16(ui, _mm256_set1_epi16(25)),
+                                                            _mm256_mullo_epi16(vi, _mm256_set1_epi16(52))));
+  const __m256i r16 = _mm256_add_epi16(y1, _mm256_mullo_epi16(vi, _mm256_set1_epi16(102)));
+  const __m256i r = _mm256_srai_epi16(r16, 6), g = _mm256_srai_epi16(g16, 6), b = _mm256_srai_epi16(b16, 6);
+  /* packus works inside 128-bit lanes: (lo lane of r | lo lane of g ...) -> bring pixels 0..15 of one channel together */
+  const __m256i rg = _mm256_permute4x64_epi64(_mm256_packus_epi16(r, g), 0xD8); /* r0..15 | g0..15 */
+  const __m256i bb = _mm256_permute4x64_epi64(_mm256_packus_epi16(b, b), 0xD8); /* b0..15 | b0..15 */
+  *r8 = _mm256_castsi256_si128(rg);
+  *g8 = _mm256_extracti128_si256(rg, 1);
+  *b8 = _mm256_castsi256_si128(bb);
+}
+/* 16 pixels r, g, b -> 48 interleaved bytes */
+static inline void store_rgb48(uint8_t* d, __m128i r, __m128i g, __m128i b) {
+  const __m128i r0 = _mm_setr_epi8(0, -1, -1, 1, -1, -1, 2, -1, -1, 3, -1, -1, 4, -1, -1, 5);
+  const __m128i g0 = _mm_setr_epi8(-1, 0, -1, -1, 1, -1, -1, 2, -1, -1, 3, -1, -1, 4, -1, -1);
+  const __m128i b0 = _mm_setr_epi8(-1, -1, 0, -1, -1, 1, -1, -1, 2, -1, -1, 3, -1, -1, 4, -1);
+  const __m128i r1 = _mm_setr_epi8(-1, -1, 6, -1, -1, 7, -1, -1, 8, -1, -1, 9, -1, -1, 10, -1);
+  const __m128i g1 = _mm_setr_epi8(5, -1, -1, 6, -1, -1, 7, -1, -1, 8, -1, -1, 9, -1, -1, 10);
+  const __m128i b1 = _mm_setr_epi8(-1, 5, -1, -1, 6, -1, -1, 7, -1, -1, 8, -1, -1, 9, -1, -1);
+  const __m128i r2 = _mm_setr_epi8(-1, 11, -1, -1, 12, -1, -1, 13, -1, -1, 14, -1, -1, 15, -1, -1);
+  const __m128i g2 = _mm_setr_epi8(-1, -1, 11, -1, -1, 12, -1, -1, 13, -1, -1, 14, -1, -1, 15, -1);
+  const __m128i b2 = _mm_setr_epi8(10, -1, -1, 11, -1, -1, 12, -1, -1, 13, -1, -1, 14, -1, -1, 15);
+  _mm_storeu_si128((__m128i*)d, _mm_or_si128(_mm_or_si128(_mm_shuffle_epi8(r, r0), _mm_shuffle_epi8(g, g0)), _mm_shuffle_epi8(b, b0)));
+  _mm_storeu_si128((__m128i*)(d + 16), _mm_or_si128(_mm_or_si128(_mm_shuffle_epi8(r, r1), _mm_shuffle_epi8(g, g1)), _mm_shuffle_epi8(b, b1)));
+  _mm_storeu_si128((__m128i*)(d + 32), _mm_or_si128(_mm_or_si128(_mm_shuffle_epi8(r, r2), _mm_shuffle_epi8(g, g2)), _mm_shuffle_epi8(b, b2)));
+}
+static inline void store_rgba64(uint8_t* d, __m128i r, __m128i g, __m128i b) {
+  const __m128i a = _mm_set1_epi8(-1);
+  const __m128i rg_lo = _mm_unpacklo_epi8(r, g), rg_hi = _mm_unpackhi_epi8(r, g);
+  const __m128i ba_lo = _mm_unpacklo_epi8(b, a), ba_hi = _mm_unpackhi_epi8(b, a);
+  _mm_storeu_si128((__m128i*)d, _mm_unpacklo_epi16(rg_lo, ba_lo));
+  _mm_storeu_si128((__m128i*)(d + 16), _mm_unpackhi_epi16(rg_lo, ba_lo));
+  _mm_storeu_si128((__m128i*)(d + 32), _mm_unpacklo_epi16(rg_hi, ba_hi));
+  _mm_storeu_si128((__m128i*)(d + 48), _mm_unpackhi_epi16(rg_hi, ba_hi));
+}
+/* the chroma pairs of pixels x .. x+15 as u0 v0 u1 v1 ...; uv_pix 1: two planes, 2: interleaved (either order) */
+static inline __m128i load_uv16(const uint8_t* pu, const uint8_t* pv, int x, int uv_pix) {
+  if (uv_pix == 1) return _mm_unpacklo_epi8(_mm_loadl_epi64((const __m128i*)(pu + (x >> 1))), _mm_loadl_epi64((const __m128i*)(pv + (x >> 1))));
+  if (pv == pu + 1) return _mm_loadu_si128((const __m128i*)(pu + x));                /* U first: x >> 1 pairs of 2 bytes */
+  const __m128i vu = _mm_loadu_si128((const __m128i*)(pv + x));                      /* V first: swap the bytes of every pair */
+  return _mm_shuffle_epi8(vu, _mm_setr_epi8(1, 0, 3, 2, 5, 4, 7, 6, 9, 8, 11, 10, 13, 12, 15, 14));
+}
+/* -> number of leading pixels of the row done 16 at a time (0 when this layout has no vector form) */
+static int yuv_row_avx2(const uint8_t* py, const uint8_t* pu, const uint8_t* pv, int uv_pix, uint8_t* d, int width, int bpp) {
+  if (uv_pix == 2 && pv != pu + 1 && pu != pv + 1) return 0; /* two separate pixel-stride-2 buffers: scalar */
+  int x = 0;
+  for (; x + 16 <= width; x += 16) {
+    __m128i r, g, b;
+    yuv16_avx2(py + x, load_uv16(pu, pv, x, uv_pix), &r, &g, &b);
+    if (bpp == 3) store_rgb48(d + 3 * x, r, g, b);
+    else store_rgba64(d + 4 * x, r, g, b);
+  }
+  return x;
+}
+#else
+static int yuv_row_avx2(const uint8_t* py, const uint8_t* pu, const uint8_t* pv, int uv_pix, uint8_t* d, int width, int bpp) {
+  (void)py; (void)pu; (void)pv; (void)uv_pix; (void)d; (void)width; (void)bpp;
+  return 0;
+}
+#endif
+
+/* Both forms over all 2^24 (y, u, v) triples -> number of differing channel values (0 expected; also 0 without AVX2, where
+ * nothing is compared). */
+long orc_yuv_rows_selftest(void) {
+  long bad = 0;
+  uint8_t ys[16], us[8], vs[8], out[64], r, g, b;
+  for (int u = 0; u < 256; ++u)
+    for (int v = 0; v < 256; ++v)
+      for (int y0 = 0; y0 < 256; y0 += 16) {
+        for (int k = 0; k < 16; ++k) ys[k] = (uint8_t)(y0 + k);
+        for (int k = 0; k < 8; ++k) { us[k] = (uint8_t)u; vs[k] = (uint8_t)(v ^ (k & 1 ? 0x55 : 0)); }
+        if (yuv_row_avx2(ys, us, vs, 1, out, 16, 3) != 16) return 0;
+        for (int k = 0; k < 16; ++k) {
+          yuv_pixel(ys[k], us[k >> 1], vs[k >> 1], &r, &g, &b);
+          bad += (out[3 * k] != r) + (out[3 * k + 1] != g) + (out[3 * k + 2] != b);
+        }
+      }
+  return bad;
+}
+
+/* one row, BPP and the chroma pixel stride as compile-time constants so that the compiler can unroll and vectorise */
+#define ORC_ROW_FN(NAME, BPP, UVPIX)                                                                                  \
+  static void NAME(const uint8_t* restrict py, const uint8_t* restrict pu, const uint8_t* restrict pv,                \
+                   uint8_t* restrict d, int width) {                                                                  \
+    for (int x = 0; x < width; ++x) {                                                                                 \
+      uint8_t r, g, b;                                                                                                \
+      yuv_pixel(py[x], pu[(x >> 1) * (UVPIX)], pv[(x >> 1) * (UVPIX)], &r, &g, &b);                                   \
+      d[(BPP) * x] = r;                                                                                               \
+      d[(BPP) * x + 1] = g;                                                                                           \
+      d[(BPP) * x + 2] = b;                                                                                           \
+      if ((BPP) == 4) d[(BPP) * x + 3] = 255;                                                                         \
+    }                                                                                                                 \
+  }
+ORC_ROW_FN(row_rgb_planar, 3, 1)
+ORC_ROW_FN(row_rgb_semi, 3, 2)
+ORC_ROW_FN(row_rgba_planar, 4, 1)
+ORC_ROW_FN(row_rgba_semi, 4, 2)
 
 /* Generic 4:2:0 -> packed RGB(A) walker. Chroma is nearest: pixel (x,y) uses
  * sample (x>>1, y>>1) (NV12ToRGB24Row_C / I422ToRGB24Row_C + the `if (y & 1)`
@@ -54,14 +181,32 @@ static int yuv420_to_packed(const uint8_t* src_y, int sy, const uint8_t* src_u, 
     const uint8_t* pu = src_u + (ptrdiff_t)(y >> 1) * suv;
     const uint8_t* pv = src_v + (ptrdiff_t)(y >> 1) * suv;
     uint8_t* d = dst + (ptrdiff_t)y * dstride;
-    for (int x = 0; x < width; ++x) {
-      uint8_t r, g, b;
-      orc_YuvPixel(py[x], pu[(x >> 1) * uv_pix], pv[(x >> 1) * uv_pix], &r, &g, &b);
-      d[0] = r;
-      d[1] = g;
-      d[2] = b;
-      if (bpp == 4) d[3] = 255;
-      d += bpp;
+    {  /* sixteen pixels at a time where the layout allows, the rest of the row with the scalar form */
+      const int done = yuv_row_avx2(py, pu, pv, uv_pix, d, width, bpp);
+      if (done) {
+        for (int x = done; x < width; ++x) {
+          uint8_t r, g, b;
+          yuv_pixel(py[x], pu[(x >> 1) * uv_pix], pv[(x >> 1) * uv_pix], &r, &g, &b);
+          d[bpp * x] = r; d[bpp * x + 1] = g; d[bpp * x + 2] = b;
+          if (bpp == 4) d[bpp * x + 3] = 255;
+        }
+        continue;
+      }
+    }
+    if (bpp == 3 && uv_pix == 1) row_rgb_planar(py, pu, pv, d, width);
+    else if (bpp == 3 && uv_pix == 2) row_rgb_semi(py, pu, pv, d, width);
+    else if (bpp == 4 && uv_pix == 1) row_rgba_planar(py, pu, pv, d, width);
+    else if (bpp == 4 && uv_pix == 2) row_rgba_semi(py, pu, pv, d, width);
+    else {
+      for (int x = 0; x < width; ++x) {
+        uint8_t r, g, b;
+        yuv_pixel(py[x], pu[(x >> 1) * uv_pix], pv[(x >> 1) * uv_pix], &r, &g, &b);
+        d[0] = r;
+        d[1] = g;
+        d[2] = b;
+        if (bpp == 4) d[3] = 255;
+        d += bpp;
+      }
     }
   }
   return 0;
@@ -242,7 +387,16 @@ int orc_RGB24ToARGB(const uint8_t* src, int src_stride, uint8_t* dst, int dst_st
   for (int y = 0; y < height; ++y) {
     const uint8_t* s = src + (ptrdiff_t)y * src_stride;
     uint8_t* d = dst + (ptrdiff_t)y * dst_stride;
-    for (int x = 0; x < width; ++x) {
+    int x = 0;
+#ifdef __AVX2__
+    { /* four pixels per shuffle (a 16-byte load needs 16 readable bytes: stop six pixels before the end of the row) */
+      const __m128i m = _mm_setr_epi8(0, 1, 2, -1, 3, 4, 5, -1, 6, 7, 8, -1, 9, 10, 11, -1);
+      const __m128i a = _mm_set1_epi32((int)0xFF000000u);
+      for (; x + 6 <= width; x += 4, s += 12, d += 16)
+        _mm_storeu_si128((__m128i*)d, _mm_or_si128(_mm_shuffle_epi8(_mm_loadu_si128((const __m128i*)s), m), a));
+    }
+#endif
+    for (; x < width; ++x) {
       d[0] = s[0];
       d[1] = s[1];
       d[2] = s[2];

@@ -17,6 +17,9 @@
 #include <string.h>
 
 #include "yuvref.h"
+#ifdef __AVX2__
+#include <immintrin.h>
+#endif
 
 #define ABS(v) ((v) < 0 ? -(v) : (v))
 
@@ -99,11 +102,31 @@ static void interpolate_row(uint8_t* dst, const uint8_t* src, ptrdiff_t src_stri
     memcpy(dst, src, (size_t)width);
     return;
   }
+  int x = 0;
+#ifdef __AVX2__
+  /* 32 bytes at a time in 16-bit lanes: a * y0 + b * y1 + 128 <= 65408 fits; avg_epu8 IS (a + b + 1) >> 1 */
   if (y1 == 128) {
-    for (int x = 0; x < width; ++x) dst[x] = (uint8_t)((src[x] + src1[x] + 1) >> 1);
+    for (; x + 32 <= width; x += 32)
+      _mm256_storeu_si256((__m256i*)(dst + x), _mm256_avg_epu8(_mm256_loadu_si256((const __m256i*)(src + x)),
+                                                               _mm256_loadu_si256((const __m256i*)(src1 + x))));
+  } else {
+    const __m256i w0 = _mm256_set1_epi16((short)y0), w1 = _mm256_set1_epi16((short)y1), rnd = _mm256_set1_epi16(128);
+    const __m256i z = _mm256_setzero_si256();
+    for (; x + 32 <= width; x += 32) {
+      const __m256i a = _mm256_loadu_si256((const __m256i*)(src + x)), b = _mm256_loadu_si256((const __m256i*)(src1 + x));
+      const __m256i lo = _mm256_srli_epi16(_mm256_add_epi16(_mm256_add_epi16(_mm256_mullo_epi16(_mm256_unpacklo_epi8(a, z), w0),
+                                                                             _mm256_mullo_epi16(_mm256_unpacklo_epi8(b, z), w1)), rnd), 8);
+      const __m256i hi = _mm256_srli_epi16(_mm256_add_epi16(_mm256_add_epi16(_mm256_mullo_epi16(_mm256_unpackhi_epi8(a, z), w0),
+                                                                             _mm256_mullo_epi16(_mm256_unpackhi_epi8(b, z), w1)), rnd), 8);
+      _mm256_storeu_si256((__m256i*)(dst + x), _mm256_packus_epi16(lo, hi)); /* unpack / pack pair up inside each 128-bit lane */
+    }
+  }
+#endif
+  if (y1 == 128) {
+    for (; x < width; ++x) dst[x] = (uint8_t)((src[x] + src1[x] + 1) >> 1);
     return;
   }
-  for (int x = 0; x < width; ++x) dst[x] = (uint8_t)((src[x] * y0 + src1[x] * y1 + 128) >> 8);
+  for (; x < width; ++x) dst[x] = (uint8_t)((src[x] * y0 + src1[x] * y1 + 128) >> 8);
 }
 
 /* Column filters. blender 0: ScaleFilterCols_C (8-bit plane, x86 BLENDER:

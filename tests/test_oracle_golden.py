@@ -171,3 +171,59 @@ def test_yuv_to_rgb_agrees_with_opencv_as_an_independent_witness(O):
                         cv2.COLOR_YUV2RGB_YV12: cv2.COLOR_YUV2RGB_I420, cv2.COLOR_YUV2RGB_I420: cv2.COLOR_YUV2RGB_YV12}[code]
         wrong = cv2.cvtColor(frame.reshape(H * 3 // 2, W), swapped_code)
         assert np.abs(ours.reshape(H, W, 3).astype(np.int32) - wrong.astype(np.int32)).max() > 20
+
+
+def test_vector_rows_equal_the_scalar_restatement(O, tmp_path):
+    """The oracle's AVX2 rows (4:2:0 -> RGB / RGBA, RGB24 -> ARGB, InterpolateRow: what makes the timed CPU baseline more than a
+    scalar straw man) against its scalar restatement: (1) the conversion on all 2^24 (y, u, v) triples inside the library,
+    (2) whole chains and the ...ToABGR rows against a second build of the same sources WITHOUT AVX2 (-march=x86-64), at
+    sizes with and without row tails."""
+    import ctypes as C
+    import glob
+    import os
+    import shutil
+    import subprocess
+    L = O.lib()
+    L.orc_yuv_rows_selftest.restype = C.c_long
+    assert L.orc_yuv_rows_selftest() == 0
+    here = os.path.dirname(os.path.abspath(O.__file__))
+    cc = os.environ.get("CC") or shutil.which("gcc") or "gcc"
+    so = str(tmp_path / "liborc_scalar.so")
+    srcs = sorted(glob.glob(os.path.join(here, "*.c")))
+    subprocess.check_call([cc, "-O2", "-march=x86-64", "-ffp-contract=off", "-fPIC", "-std=c11", "-shared", "-o", so] + srcs)
+    S = C.CDLL(so)
+    S.orc_run_batch.argtypes = L.orc_run_batch.argtypes
+    S.orc_run_batch.restype = L.orc_run_batch.restype
+    S.orc_yuv_rows_selftest.restype = C.c_long
+    assert S.orc_yuv_rows_selftest() == 0      # (nothing to compare there: documents that this build has no vector rows)
+    rng = np.random.default_rng(5)
+    norm = (O.OP_NORMALIZE, 0, 0, 0, 0, 127.5, 127.5)
+    for fmt in (O.FMT_NV12, O.FMT_NV21, O.FMT_YV12, O.FMT_YV21):
+        for (W, H, dw, dh) in [(1920, 1080, 224, 224), (642, 362, 300, 200), (646, 360, 640, 352), (36, 22, 20, 11), (14, 10, 9, 7),
+                               (320, 240, 500, 333)]:
+            ops = [(O.OP_CSC, O.FMT_RGB), (O.OP_RESIZE, dw, dh), norm]
+            frames = rng.integers(0, 256, size=(2, O.frame_bytes(W, H, fmt)), dtype=np.uint8)
+            descs = O.make_descs(ops)
+            dims = (C.c_int * 4)(1, dh, dw, 3)
+            outs = []
+            for lib in (L, S):
+                out = np.zeros((2, 1, dh, dw, 3), dtype=np.float32)
+                st = lib.orc_run_batch(descs, len(ops), frames.ctypes.data, frames.shape[1], W, H, fmt, out.ctypes.data,
+                                       out[0].nbytes, O.DT_F32, dims, 4, 2)
+                assert st == 0
+                outs.append(out)
+            assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32)), (fmt, W, H, dw, dh)
+    # RGBA rows (…ToABGR): semi-planar in both orders
+    vp, ci = C.c_void_p, C.c_int
+    for name in ("orc_NV12ToABGR", "orc_NV21ToABGR"):
+        for (W, H) in [(1920, 8), (50, 6), (16, 2), (15, 3)]:
+            y = rng.integers(0, 256, size=W * H, dtype=np.uint8)
+            uv = rng.integers(0, 256, size=2 * ((W + 1) // 2) * ((H + 1) // 2), dtype=np.uint8)
+            res = []
+            for lib in (L, S):
+                f = getattr(lib, name)
+                f.argtypes = [vp, ci, vp, ci, vp, ci, ci, ci]
+                out = np.zeros(W * H * 4, dtype=np.uint8)
+                assert f(y.ctypes.data, W, uv.ctypes.data, 2 * ((W + 1) // 2), out.ctypes.data, W * 4, W, H) == 0
+                res.append(out)
+            assert np.array_equal(res[0], res[1]), (name, W, H)
