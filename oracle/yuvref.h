@@ -20,6 +20,13 @@
  * YUV->RGB, Normalize numerics, plane-scaler special cases and rotate direction
  * are NOT pinned by any reference test: for those this file is the frozen spec
  * ("parity unpinned").
+ *
+ * VECTOR ROWS: the three full-frame passes of the timed CPU baseline (4:2:0 ->
+ * RGB / RGBA, RGB24 -> ARGB, InterpolateRow) also exist as AVX2 rows when the
+ * library is built with AVX2 (the default, -march=x86-64-v3). The scalar forms
+ * stay the definition; the vector forms are compared with them on all 2^24
+ * (y, u, v) triples (orc_yuv_rows_selftest) and through whole chains against a
+ * no-AVX2 build of the same sources (tests/test_oracle_golden.py).
  */
 #ifndef BAND_ORACLE_YUVREF_H_
 #define BAND_ORACLE_YUVREF_H_

@@ -137,3 +137,13 @@ def test_no_cpu_fallback_without_device():
     except B.BandError:
         return  # tensor / processor creation refused: loud failure
     assert st != B.kBandOk and out is None
+
+
+def test_no_alloc_scratch_size_is_the_headers():
+    """The Python shim's constant and include/bandcu.h agree on the static scratch size of bandcu_two_stage_run_noalloc."""
+    import re
+    from band_b200 import cuda_shim as S
+    text = open(os.path.join(ROOT, "include", "bandcu.h")).read()
+    m = re.search(r"#define\s+BANDCU_NOALLOC_SCRATCH_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", text)
+    assert m, "BANDCU_NOALLOC_SCRATCH_BYTES not found in include/bandcu.h"
+    assert int(m.group(1)) << int(m.group(2)) == S.NOALLOC_SCRATCH_BYTES == 8 << 20
